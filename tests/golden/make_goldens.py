@@ -212,8 +212,12 @@ def case_variants_train():
 def case_variants_md():
     # orthorhombic version of the variants rows (ghost expansion helper wants a rectangular box); no G3 quirk-free
     # shortcut: G3 rows are present, so the "Rjk > Rcut skips G4" branch (Structure.cpp:1129-1132) is exercised.
+    # G4 rows: one Rc / fc type and eta-major order with >= 2 rows per eta -- the only patterns for which the
+    # reference's row-to-row memoisation in Get_Forces (Structure.cpp:656-698) yields the intended derivative
+    # (SURVEY.md appendix C #4); fc type 1 and non-integer xi are still covered.
     v = variants_config()
-    cfg = synth.Config("variants_md", 10, synth.lattice_tio2((2, 2, 3)), 1, G2=v.G2, G4=v.G4, hidden=[6, 5], rcut=4.5,
+    g4 = [[4.5, 1.0, 0.05, 1.0, 1.0], [4.5, 1.0, 0.05, 2.5, -1.0], [4.5, 1.0, 0.2, 3.0, 1.0], [4.5, 1.0, 0.2, 1.7, 1.0]]
+    cfg = synth.Config("variants_md", 10, synth.lattice_tio2((2, 2, 3)), 1, G2=v.G2, G4=g4, hidden=[6, 5], rcut=4.5,
                        sigma=0.05, G1=v.G1, G3=v.G3)
     nt = {}
     for z in cfg.elements:
