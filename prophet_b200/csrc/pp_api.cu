@@ -1,0 +1,885 @@
+// C ABI of the prophet_b200 device layer (include/prophet_b200.h): context, set-up, training epoch, MD step.
+#include "../../include/prophet_b200.h"
+#include "pp_common.cuh"
+#include "pp_kernels.h"
+#include "pp_comm.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <map>
+
+// ---------------------------------------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+void pp_set_error(const char* fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* pp_last_error(void) { return g_err; }
+extern "C" int pp_version(void) { return 100; }
+
+// growable device buffer
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t n, size_t keep, cudaStream_t st)
+  {
+    if (n <= cap) return 0;
+    size_t ncap = std::max(n, cap + cap / 2);
+    T* q = nullptr;
+    PP_CUDA(cudaMalloc(&q, ncap * sizeof(T)));
+    if (keep && p) PP_CUDA(cudaMemcpyAsync(q, p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    if (p) {
+      PP_CUDA(cudaStreamSynchronize(st));
+      PP_CUDA(cudaFree(p));
+    }
+    p = q;
+    cap = ncap;
+    return 0;
+  }
+  void release()
+  {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct NetHost {
+  bool set = false;
+  int n_layers = 0, P = 0, p_off = 0, n_nodes = 0;
+  std::vector<int> sizes, tf;
+  std::vector<double> params, mean, scale;
+  DevBuf<double> d_mean, d_scale;
+  DevBuf<int> d_tf;
+  NetDev dev;
+};
+
+struct pp_context {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  long long launches = 0;
+  double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+  bool spec_set = false;
+  DescSpec spec;
+  DescSpec* d_spec = nullptr;
+  DevBuf<int> d_overflow;
+
+  NetHost nets[PP_MAX_ELEM];
+  int P_total = 0;
+  DevBuf<double> d_params;          // all elements, concatenated
+  double out_mean = 0.0, out_scale = 1.0;
+  DevBuf<double> d_tanh_table;
+
+  // ---- training set ----
+  int n_struct = 0;
+  long long n_atoms = 0;
+  int desc_cap = 128;
+  std::vector<long long> h_struct_atom0{0};
+  std::vector<double> h_FtoA, h_target;
+  std::vector<int> h_mxyz, h_tag, h_elem, h_atom_struct;
+  std::vector<double> h_frac;
+  std::vector<int> h_rows[PP_MAX_ELEM];
+  DevBuf<long long> d_struct_atom0;
+  DevBuf<double> d_FtoA, d_target, d_frac, d_G, d_E_atom, d_E_struct, d_cstruct;
+  DevBuf<int> d_mxyz, d_tag, d_elem, d_atom_struct;
+  DevBuf<int> d_rows[PP_MAX_ELEM];
+  DevBuf<double> d_partial, d_result, d_stat_partial, d_stat_sums;
+  DevBuf<long long> d_count;
+  std::vector<double> h_result;
+
+  // ---- MD ----
+  std::vector<int> type_to_elem;
+  int md_cap = 128;
+  int md_nlocal = 0, md_ntotal = 0;
+  long long md_nneigh = 0;
+  DevBuf<double> d_x, d_f, d_Gmd, d_dEdG, d_eatom;
+  DevBuf<int> d_md_elem, d_neigh;
+  DevBuf<long long> d_neigh_off;
+  DevBuf<int> d_md_rows[PP_MAX_ELEM];
+  int md_rows_n[PP_MAX_ELEM] = {0, 0, 0, 0};
+  std::vector<int> h_md_elem;
+
+  PPComm comm;
+};
+
+static int tick(pp_context* c, int i) { PP_CUDA(cudaEventRecord(c->ev[i], c->stream)); return 0; }
+static int tock(pp_context* c, int i0, int i1, int which)
+{
+  PP_CUDA(cudaEventSynchronize(c->ev[i1]));
+  float ms = 0;
+  PP_CUDA(cudaEventElapsedTime(&ms, c->ev[i0], c->ev[i1]));
+  c->phase_ms[which] = ms;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+extern "C" int pp_create(int device, int fp_mode, pp_context** out)
+{
+  PP_REQUIRE(out != nullptr, "pp_create: out is NULL");
+  PP_REQUIRE(fp_mode == 64, "pp_create: fp_mode %d not implemented (only 64)", fp_mode);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  PP_REQUIRE(e == cudaSuccess && ndev > 0, "pp_create: no CUDA device available (%s); this library has no CPU fallback",
+             e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  PP_REQUIRE(device >= 0 && device < ndev, "pp_create: device %d out of range (have %d)", device, ndev);
+  PP_CUDA(cudaSetDevice(device));
+  pp_context* c = new pp_context();
+  c->device = device;
+  PP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 4; i++) PP_CUDA(cudaEventCreate(&c->ev[i]));
+  PP_CUDA(cudaMalloc(&c->d_spec, sizeof(DescSpec)));
+  if (c->d_overflow.ensure(1, 0, c->stream)) return 1;
+  std::vector<double> table;
+  ppk_make_tanh_table(table);
+  if (c->d_tanh_table.ensure(table.size(), 0, c->stream)) return 1;
+  PP_CUDA(cudaMemcpy(c->d_tanh_table.p, table.data(), table.size() * sizeof(double), cudaMemcpyHostToDevice));
+  *out = c;
+  return 0;
+}
+
+extern "C" void pp_destroy(pp_context* c)
+{
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->comm.destroy();
+  // DevBuf members are plain pointers: release explicitly
+  c->d_overflow.release(); c->d_params.release(); c->d_tanh_table.release();
+  c->d_struct_atom0.release(); c->d_FtoA.release(); c->d_target.release(); c->d_frac.release(); c->d_G.release();
+  c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
+  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release();
+  c->d_stat_partial.release(); c->d_stat_sums.release(); c->d_count.release();
+  c->d_x.release(); c->d_f.release(); c->d_Gmd.release(); c->d_dEdG.release(); c->d_eatom.release();
+  c->d_md_elem.release(); c->d_neigh.release(); c->d_neigh_off.release();
+  for (int e = 0; e < PP_MAX_ELEM; e++) {
+    c->d_rows[e].release(); c->d_md_rows[e].release();
+    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release();
+  }
+  if (c->d_spec) cudaFree(c->d_spec);
+  for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+extern "C" long long pp_kernel_launches(pp_context* c) { return c ? c->launches : 0; }
+extern "C" double pp_last_phase_ms(pp_context* c, int which) { return (c && which >= 0 && which < 8) ? c->phase_ms[which] : 0.0; }
+extern "C" void* pp_stream(pp_context* c) { return c ? (void*)c->stream : nullptr; }
+
+// ---------------------------------------------------------------------------------------------------------
+// Structure::init_G / Allocate_G / init_type_G_map (Structure.cpp:779-960, 1491-1512)
+extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const double* G1, int nG2, const double* G2,
+                                  int nG3, const double* G3, int nG4, const double* G4, double Rcut)
+{
+  PP_REQUIRE(c, "null context");
+  PP_REQUIRE(n_elem >= 1 && n_elem <= PP_MAX_ELEM, "pp_set_descriptors: %d elements (max %d)", n_elem, PP_MAX_ELEM);
+  PP_REQUIRE(nG1 >= 0 && nG2 >= 0 && nG3 >= 0 && nG4 >= 0, "pp_set_descriptors: negative row count");
+  PP_REQUIRE(nG1 + nG2 <= PP_MAX_PAIR_ROWS, "pp_set_descriptors: %d pair rows (max %d)", nG1 + nG2, PP_MAX_PAIR_ROWS);
+  PP_REQUIRE(nG4 <= PP_MAX_G4_ROWS, "pp_set_descriptors: %d G4 rows (max %d)", nG4, PP_MAX_G4_ROWS);
+  PP_REQUIRE(nG3 <= PP_MAX_G3_ROWS, "pp_set_descriptors: %d G3 rows (max %d)", nG3, PP_MAX_G3_ROWS);
+  PP_REQUIRE(nG3 == 0, "pp_set_descriptors: G3 rows are not implemented on the GPU path yet");
+  PP_REQUIRE(Rcut > 0, "pp_set_descriptors: Rcut must be positive");
+  PP_REQUIRE(c->n_struct == 0, "pp_set_descriptors: structures already added; call pp_clear_structures first");
+  DescSpec& S = c->spec;
+  memset(&S, 0, sizeof(S));
+  S.n_elem = n_elem; S.nG1 = nG1; S.nG2 = nG2; S.nG3 = nG3; S.nG4 = nG4;
+  S.npair = nG1 + nG2; S.ntrip = nG3 + nG4;
+  S.NG = n_elem * S.npair + n_elem * (n_elem + 1) / 2 * S.ntrip;
+  S.Rcut = Rcut;
+  for (int r = 0; r < nG1; r++) {
+    S.pair_rc[r] = G1[2 * r]; S.pair_fc[r] = (int)G1[2 * r + 1]; S.pair_eta[r] = 0; S.pair_rs[r] = 0;
+  }
+  for (int r = 0; r < nG2; r++) {
+    S.pair_rc[nG1 + r] = G2[4 * r]; S.pair_fc[nG1 + r] = (int)G2[4 * r + 1];
+    S.pair_eta[nG1 + r] = G2[4 * r + 2]; S.pair_rs[nG1 + r] = G2[4 * r + 3];
+  }
+  for (int r = 0; r < nG3; r++) {
+    S.g3_rc[r] = G3[5 * r]; S.g3_fc[r] = (int)G3[5 * r + 1]; S.g3_eta[r] = G3[5 * r + 2];
+    S.g3_xi[r] = G3[5 * r + 3]; S.g3_lam[r] = G3[5 * r + 4];
+  }
+  // factorise the G4 rows into radial keys (Rc, fc, eta) and angular keys (xi, lambda), first-seen order
+  S.NR = 0; S.NA = 0;
+  for (int r = 0; r < nG4; r++) {
+    const double* row = G4 + 5 * r;
+    int ri = -1, ai = -1;
+    for (int k = 0; k < S.NR; k++)
+      if (S.rad_rc[k] == row[0] && S.rad_fc[k] == (int)row[1] && S.rad_eta[k] == row[2]) ri = k;
+    if (ri < 0) {
+      PP_REQUIRE(S.NR < PP_MAX_RAD, "pp_set_descriptors: more than %d distinct (Rc, fc, eta) among G4 rows", PP_MAX_RAD);
+      ri = S.NR++;
+      S.rad_rc[ri] = row[0]; S.rad_fc[ri] = (int)row[1]; S.rad_eta[ri] = row[2];
+    }
+    for (int k = 0; k < S.NA; k++)
+      if (S.ang_xi[k] == row[3] && S.ang_lam[k] == row[4]) ai = k;
+    if (ai < 0) {
+      PP_REQUIRE(S.NA < PP_MAX_ANG, "pp_set_descriptors: more than %d distinct (xi, lambda) among G4 rows", PP_MAX_ANG);
+      ai = S.NA++;
+      S.ang_xi[ai] = row[3]; S.ang_lam[ai] = row[4];
+      S.ang_pref[ai] = pow(2.0, 1.0 - row[3]);                         // Structure.cpp:811-813
+      bool is_int = (row[3] == (double)(int)row[3]) && row[3] >= 0;     // Structure.h:257 (negative: 1/base path)
+      S.ang_xi_int[ai] = is_int ? (int)row[3] : -1;
+      PP_REQUIRE(row[3] >= 0 || !(row[3] == (double)(int)row[3]), "pp_set_descriptors: negative integer xi not supported");
+    }
+    S.g4_rad[r] = ri; S.g4_ang[r] = ai;
+  }
+  if (S.NR == 0) S.NR = 1;   // keeps shared-memory strides non-degenerate when there are no G4 rows
+  int index = 0;
+  for (int i = 0; i < n_elem; i++)
+    for (int j = i; j < n_elem; j++) {
+      S.trip_base[i][j] = S.trip_base[j][i] = S.npair * n_elem + index;
+      index += S.ntrip;
+    }
+  PP_CUDA(cudaMemcpy(c->d_spec, &S, sizeof(S), cudaMemcpyHostToDevice));
+  c->spec_set = true;
+  return 0;
+}
+
+extern "C" int pp_num_descriptors(pp_context* c) { return (c && c->spec_set) ? c->spec.NG : -1; }
+
+// ---------------------------------------------------------------------------------------------------------
+static int rebuild_param_layout(pp_context* c)
+{
+  int off = 0;
+  for (int e = 0; e < PP_MAX_ELEM; e++) {
+    if (!c->nets[e].set) continue;
+    c->nets[e].p_off = off;
+    off += c->nets[e].P;
+  }
+  c->P_total = off;
+  if (c->d_params.ensure((size_t)std::max(off, 1), 0, c->stream)) return 1;
+  for (int e = 0; e < PP_MAX_ELEM; e++) {
+    NetHost& n = c->nets[e];
+    if (!n.set) continue;
+    PP_CUDA(cudaMemcpyAsync(c->d_params.p + n.p_off, n.params.data(), n.P * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    n.dev.params = c->d_params.p + n.p_off;
+  }
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* sizes, const int* node_transfer,
+                              const double* params, const double* in_mean, const double* in_scale)
+{
+  PP_REQUIRE(c && c->spec_set, "pp_set_network: call pp_set_descriptors first");
+  PP_REQUIRE(elem >= 0 && elem < c->spec.n_elem, "pp_set_network: element index %d out of range", elem);
+  PP_REQUIRE(n_layers >= 1 && n_layers <= PP_MAX_LAYERS, "pp_set_network: %d weight layers (max %d)", n_layers, PP_MAX_LAYERS);
+  PP_REQUIRE(sizes[0] == c->spec.NG, "pp_set_network: input width %d != number of descriptors %d", sizes[0], c->spec.NG);
+  PP_REQUIRE(sizes[n_layers] == 1, "pp_set_network: the output layer must have one node");
+  NetHost& n = c->nets[elem];
+  n.n_layers = n_layers;
+  n.sizes.assign(sizes, sizes + n_layers + 1);
+  n.P = 0; n.n_nodes = 0;
+  memset(&n.dev, 0, sizeof(n.dev));
+  n.dev.n_layers = n_layers;
+  for (int l = 0; l <= n_layers; l++) n.dev.sizes[l] = sizes[l];
+  for (int l = 0; l < n_layers; l++) {
+    PP_REQUIRE(sizes[l + 1] >= 1, "pp_set_network: empty layer");
+    n.dev.w_off[l] = n.P;
+    n.dev.node_off[l] = n.n_nodes;
+    n.P += sizes[l + 1] * (sizes[l] + 1);
+    n.n_nodes += sizes[l + 1];
+  }
+  n.dev.P = n.P;
+  n.tf.assign(node_transfer, node_transfer + n.n_nodes);
+  for (int i = 0; i < n.n_nodes; i++) PP_REQUIRE(n.tf[i] >= 0 && n.tf[i] <= 8, "pp_set_network: unknown transfer id %d", n.tf[i]);
+  PP_REQUIRE(n.tf[n.n_nodes - 1] == PP_TF_LINEAR, "pp_set_network: the output node must be linear (NN.cpp:76)");
+  n.params.assign(params, params + n.P);
+  n.mean.assign(in_mean, in_mean + sizes[0]);
+  n.scale.assign(in_scale, in_scale + sizes[0]);
+  if (n.d_mean.ensure(sizes[0], 0, c->stream) || n.d_scale.ensure(sizes[0], 0, c->stream) || n.d_tf.ensure(n.n_nodes, 0, c->stream)) return 1;
+  PP_CUDA(cudaMemcpy(n.d_mean.p, n.mean.data(), sizes[0] * sizeof(double), cudaMemcpyHostToDevice));
+  PP_CUDA(cudaMemcpy(n.d_scale.p, n.scale.data(), sizes[0] * sizeof(double), cudaMemcpyHostToDevice));
+  PP_CUDA(cudaMemcpy(n.d_tf.p, n.tf.data(), n.n_nodes * sizeof(int), cudaMemcpyHostToDevice));
+  n.dev.mean = n.d_mean.p; n.dev.scale = n.d_scale.p; n.dev.tf = n.d_tf.p;
+  n.set = true;
+  return rebuild_param_layout(c);
+}
+
+extern "C" int pp_set_output_scaling(pp_context* c, double out_mean, double out_scale)
+{
+  PP_REQUIRE(c, "null context");
+  c->out_mean = out_mean;
+  c->out_scale = out_scale;
+  return 0;
+}
+
+extern "C" int pp_num_parameters(pp_context* c) { return c ? c->P_total : -1; }
+
+static int nets_ready(pp_context* c)
+{
+  PP_REQUIRE(c && c->spec_set, "descriptors not set");
+  for (int e = 0; e < c->spec.n_elem; e++) PP_REQUIRE(c->nets[e].set, "no network set for element index %d", e);
+  return 0;
+}
+
+extern "C" int pp_set_parameters(pp_context* c, const double* params)
+{
+  if (nets_ready(c)) return 1;
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    NetHost& n = c->nets[e];
+    std::copy(params + n.p_off, params + n.p_off + n.P, n.params.begin());
+  }
+  PP_CUDA(cudaMemcpyAsync(c->d_params.p, params, c->P_total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int pp_get_parameters(pp_context* c, double* params)
+{
+  if (nets_ready(c)) return 1;
+  PP_CUDA(cudaMemcpyAsync(params, c->d_params.p, c->P_total * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int pp_set_input_scaling(pp_context* c, int elem, const double* in_mean, const double* in_scale)
+{
+  PP_REQUIRE(c && elem >= 0 && elem < PP_MAX_ELEM && c->nets[elem].set, "pp_set_input_scaling: no network for element %d", elem);
+  NetHost& n = c->nets[elem];
+  int NG = n.sizes[0];
+  n.mean.assign(in_mean, in_mean + NG);
+  n.scale.assign(in_scale, in_scale + NG);
+  PP_CUDA(cudaMemcpy(n.d_mean.p, n.mean.data(), NG * sizeof(double), cudaMemcpyHostToDevice));
+  PP_CUDA(cudaMemcpy(n.d_scale.p, n.scale.data(), NG * sizeof(double), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" int pp_get_input_scaling(pp_context* c, int elem, double* in_mean, double* in_scale)
+{
+  PP_REQUIRE(c && elem >= 0 && elem < PP_MAX_ELEM && c->nets[elem].set, "pp_get_input_scaling: no network for element %d", elem);
+  NetHost& n = c->nets[elem];
+  std::copy(n.mean.begin(), n.mean.end(), in_mean);
+  std::copy(n.scale.begin(), n.scale.end(), in_scale);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Structure::Set_Convert + Normalize (Structure.cpp:1159-1279), host arithmetic identical to the reference
+// (this translation unit is compiled with -ffp-contract=off for host code).
+extern "C" int pp_cart_to_frac(const double* cell, const double* cart, int n, double* frac)
+{
+  PP_REQUIRE(cell && cart && frac && n >= 0, "pp_cart_to_frac: bad arguments");
+  // FtoA = transpose(cell); AtoF = inverse by cofactors (Structure.h:180-197)
+  double m[3][3];
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) m[j][i] = cell[3 * i + j];
+  double det = m[0][0] * (m[1][1] * m[2][2] - m[2][1] * m[1][2]) - m[0][1] * (m[1][0] * m[2][2] - m[1][2] * m[2][0]) +
+                        m[0][2] * (m[1][0] * m[2][1] - m[1][1] * m[2][0]);
+  PP_REQUIRE(det != 0, "Non-invertible unit cell");
+  double inv = 1 / det;
+  double A[3][3];
+  A[0][0] = (m[1][1] * m[2][2] - m[2][1] * m[1][2]) * inv;
+  A[0][1] = (m[0][2] * m[2][1] - m[0][1] * m[2][2]) * inv;
+  A[0][2] = (m[0][1] * m[1][2] - m[0][2] * m[1][1]) * inv;
+  A[1][0] = (m[1][2] * m[2][0] - m[1][0] * m[2][2]) * inv;
+  A[1][1] = (m[0][0] * m[2][2] - m[0][2] * m[2][0]) * inv;
+  A[1][2] = (m[1][0] * m[0][2] - m[0][0] * m[1][2]) * inv;
+  A[2][0] = (m[1][0] * m[2][1] - m[2][0] * m[1][1]) * inv;
+  A[2][1] = (m[2][0] * m[0][1] - m[0][0] * m[2][1]) * inv;
+  A[2][2] = (m[0][0] * m[1][1] - m[1][0] * m[0][1]) * inv;
+  for (int i = 0; i < n; i++) {
+    const double* p = cart + 3 * (size_t)i;
+    for (int r = 0; r < 3; r++) {
+      double v = A[r][0] * p[0] + A[r][1] * p[1] + A[r][2] * p[2];
+      if (v < 0) v += 1;
+      else if (v > 1) v -= 1;
+      frac[3 * (size_t)i + r] = v;
+    }
+  }
+  return 0;
+}
+
+static PeriodicArgs periodic_args(pp_context* c)
+{
+  PeriodicArgs a;
+  memset(&a, 0, sizeof(a));
+  a.spec = c->d_spec;
+  a.atom_struct = c->d_atom_struct.p;
+  a.struct_atom0 = c->d_struct_atom0.p;
+  a.FtoA = c->d_FtoA.p;
+  a.mxyz = c->d_mxyz.p;
+  a.frac = c->d_frac.p;
+  a.elem = c->d_elem.p;
+  a.G = c->d_G.p;
+  a.overflow = c->d_overflow.p;
+  return a;
+}
+
+extern "C" int pp_add_structures(pp_context* c, int n_struct, const int* natoms, const double* cells, const double* frac,
+                                 const int* elem, const double* targets, const int* tags)
+{
+  PP_REQUIRE(c && c->spec_set, "pp_add_structures: call pp_set_descriptors first");
+  PP_REQUIRE(n_struct >= 0, "pp_add_structures: negative count");
+  if (n_struct == 0) return 0;
+  PP_CUDA(cudaSetDevice(c->device));
+  const DescSpec& S = c->spec;
+  const int s0 = c->n_struct;
+  const long long a0 = c->n_atoms;
+  long long add_atoms = 0;
+  for (int s = 0; s < n_struct; s++) {
+    PP_REQUIRE(natoms[s] > 0, "pp_add_structures: structure %d has %d atoms", s, natoms[s]);
+    add_atoms += natoms[s];
+  }
+  for (long long i = 0; i < add_atoms; i++)
+    PP_REQUIRE(elem[i] >= 0 && elem[i] < S.n_elem, "pp_add_structures: element index %d out of range", elem[i]);
+  // host mirrors
+  c->h_frac.insert(c->h_frac.end(), frac, frac + 3 * add_atoms);
+  c->h_elem.insert(c->h_elem.end(), elem, elem + add_atoms);
+  for (int s = 0; s < n_struct; s++) {
+    const double* cell = cells + 9 * (size_t)s;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) c->h_FtoA.push_back(cell[3 * j + i]);   // FtoA = cell^T
+    // Structure.cpp:1300-1302 with the norms of Set_Convert (:1168-1173)
+    for (int v = 0; v < 3; v++) {
+      double nrm = sqrt(pow(cell[3 * v], 2) + pow(cell[3 * v + 1], 2) + pow(cell[3 * v + 2], 2));
+      PP_REQUIRE(nrm > 0, "pp_add_structures: zero lattice vector");
+      c->h_mxyz.push_back((int)ceil(1.1 * S.Rcut / nrm));
+    }
+    c->h_target.push_back(targets[s]);
+    c->h_tag.push_back(tags[s]);
+    for (int i = 0; i < natoms[s]; i++) c->h_atom_struct.push_back(s0 + s);
+    c->h_struct_atom0.push_back(c->h_struct_atom0.back() + natoms[s]);
+  }
+  const int ns = s0 + n_struct;
+  const long long na = a0 + add_atoms;
+  cudaStream_t st = c->stream;
+  if (c->d_struct_atom0.ensure(ns + 1, s0 + 1, st) || c->d_FtoA.ensure(9 * (size_t)ns, 9 * (size_t)s0, st) ||
+      c->d_mxyz.ensure(3 * (size_t)ns, 3 * (size_t)s0, st) || c->d_target.ensure(ns, s0, st) || c->d_tag.ensure(ns, s0, st) ||
+      c->d_frac.ensure(3 * (size_t)na, 3 * (size_t)a0, st) || c->d_elem.ensure(na, a0, st) ||
+      c->d_atom_struct.ensure(na, a0, st) || c->d_G.ensure((size_t)na * S.NG, (size_t)a0 * S.NG, st) ||
+      c->d_E_atom.ensure(na, 0, st) || c->d_E_struct.ensure(ns, 0, st) || c->d_cstruct.ensure(ns, 0, st))
+    return 1;
+  PP_CUDA(cudaMemcpyAsync(c->d_struct_atom0.p, c->h_struct_atom0.data(), (ns + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_FtoA.p + 9 * (size_t)s0, c->h_FtoA.data() + 9 * (size_t)s0, 9 * (size_t)n_struct * sizeof(double), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_mxyz.p + 3 * (size_t)s0, c->h_mxyz.data() + 3 * (size_t)s0, 3 * (size_t)n_struct * sizeof(int), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_target.p + s0, c->h_target.data() + s0, n_struct * sizeof(double), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_tag.p + s0, c->h_tag.data() + s0, n_struct * sizeof(int), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_frac.p + 3 * (size_t)a0, frac, 3 * (size_t)add_atoms * sizeof(double), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_elem.p + a0, elem, add_atoms * sizeof(int), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_atom_struct.p + a0, c->h_atom_struct.data() + a0, add_atoms * sizeof(int), cudaMemcpyHostToDevice, st));
+  c->n_struct = ns;
+  c->n_atoms = na;
+  // per-element row lists (structure-major)
+  for (int e = 0; e < S.n_elem; e++) {
+    size_t before = c->h_rows[e].size();
+    for (long long i = 0; i < add_atoms; i++) if (elem[i] == e) c->h_rows[e].push_back((int)(a0 + i));
+    size_t after = c->h_rows[e].size();
+    if (c->d_rows[e].ensure(std::max<size_t>(after, 1), before, st)) return 1;
+    if (after > before)
+      PP_CUDA(cudaMemcpyAsync(c->d_rows[e].p + before, c->h_rows[e].data() + before, (after - before) * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
+  // descriptors of the new atoms
+  PeriodicArgs a = periodic_args(c);
+  a.n_atoms = add_atoms;
+  a.atom_begin = a0;
+  if (tick(c, 0)) return 1;
+  if (ppk_desc_periodic(S, a, &c->desc_cap, st, &c->launches)) return 1;
+  if (tick(c, 1)) return 1;
+  PP_CUDA(cudaStreamSynchronize(st));
+  return tock(c, 0, 1, 0);
+}
+
+extern "C" int pp_clear_structures(pp_context* c)
+{
+  PP_REQUIRE(c, "null context");
+  c->n_struct = 0;
+  c->n_atoms = 0;
+  c->h_struct_atom0.assign(1, 0);
+  c->h_FtoA.clear(); c->h_target.clear(); c->h_mxyz.clear(); c->h_tag.clear(); c->h_elem.clear();
+  c->h_atom_struct.clear(); c->h_frac.clear();
+  for (int e = 0; e < PP_MAX_ELEM; e++) c->h_rows[e].clear();
+  return 0;
+}
+
+extern "C" int pp_num_structures(pp_context* c) { return c ? c->n_struct : -1; }
+extern "C" long long pp_num_atoms(pp_context* c) { return c ? c->n_atoms : -1; }
+
+extern "C" int pp_get_descriptors(pp_context* c, int s, double* G_out)
+{
+  PP_REQUIRE(c && s >= 0 && s < c->n_struct, "pp_get_descriptors: structure %d out of range", s);
+  const int NG = c->spec.NG;
+  const long long a0 = c->h_struct_atom0[s];
+  const int n = (int)(c->h_struct_atom0[s + 1] - a0);
+  std::vector<double> tmp((size_t)n * NG);
+  PP_CUDA(cudaMemcpyAsync(tmp.data(), c->d_G.p + (size_t)a0 * NG, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < n; i++)
+    for (int g = 0; g < NG; g++) G_out[(size_t)g * n + i] = tmp[(size_t)i * NG + g];
+  return 0;
+}
+
+extern "C" int pp_get_neighbors(pp_context* c, int s, int* neigh_offset, int* neigh_j, int* image_offset, int* image_t,
+                                int* n_pairs, int* n_images)
+{
+  PP_REQUIRE(c && s >= 0 && s < c->n_struct, "pp_get_neighbors: structure %d out of range", s);
+  const long long a0 = c->h_struct_atom0[s];
+  const int n = (int)(c->h_struct_atom0[s + 1] - a0);
+  cudaStream_t st = c->stream;
+  DevBuf<int> d_counts, d_offsets, d_j, d_t;
+  if (d_counts.ensure(n, 0, st) || d_offsets.ensure(n + 1, 0, st)) return 1;
+  PeriodicArgs a = periodic_args(c);
+  int cap = c->desc_cap;
+  std::vector<int> counts(n), offsets(n + 1, 0);
+  int rc = 1;
+  do {
+    PP_CUDA(cudaMemsetAsync(a.overflow, 0, sizeof(int), st));
+    if (ppk_neighbors_periodic(c->spec, a, s, n, 0, d_counts.p, nullptr, nullptr, nullptr, cap, st, &c->launches)) break;
+    if (cudaMemcpyAsync(counts.data(), d_counts.p, n * sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess) break;
+    if (cudaStreamSynchronize(st) != cudaSuccess) break;
+    int mx = 0;
+    for (int i = 0; i < n; i++) { offsets[i + 1] = offsets[i] + counts[i]; mx = std::max(mx, counts[i]); }
+    while (cap < mx) cap *= 2;
+    if (cap > ppk_max_cap(c->spec, false)) { pp_set_error("pp_get_neighbors: too many neighbour images for shared memory"); break; }
+    const int total = offsets[n];
+    if (d_j.ensure(std::max(total, 1), 0, st) || d_t.ensure(std::max(total, 1), 0, st)) break;
+    if (cudaMemcpyAsync(d_offsets.p, offsets.data(), (n + 1) * sizeof(int), cudaMemcpyHostToDevice, st) != cudaSuccess) break;
+    if (ppk_neighbors_periodic(c->spec, a, s, n, 1, d_counts.p, d_offsets.p, d_j.p, d_t.p, cap, st, &c->launches)) break;
+    std::vector<int> hj(total), ht(total);
+    if (total) {
+      if (cudaMemcpyAsync(hj.data(), d_j.p, total * sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess) break;
+      if (cudaMemcpyAsync(ht.data(), d_t.p, total * sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess) break;
+    }
+    if (cudaStreamSynchronize(st) != cudaSuccess) break;
+    // (j, image) pairs -> unique-j list + per-pair image lists, the layout of Structure::firstneigh / trans_indices
+    int np = 0, ni = 0;
+    for (int i = 0; i < n; i++) {
+      if (neigh_offset) neigh_offset[i] = np;
+      int last_j = -1;
+      for (int p = offsets[i]; p < offsets[i + 1]; p++) {
+        if (hj[p] != last_j) {
+          if (neigh_j) { neigh_j[np] = hj[p]; image_offset[np] = ni; }
+          np++;
+          last_j = hj[p];
+        }
+        if (image_t) image_t[ni] = ht[p];
+        ni++;
+      }
+    }
+    if (neigh_offset) neigh_offset[n] = np;
+    if (image_offset && neigh_j) image_offset[np] = ni;
+    if (n_pairs) *n_pairs = np;
+    if (n_images) *n_images = ni;
+    rc = 0;
+  } while (0);
+  d_counts.release(); d_offsets.release(); d_j.release(); d_t.release();
+  if (rc && !g_err[0]) pp_set_error("pp_get_neighbors: CUDA failure (%s)", cudaGetErrorString(cudaGetLastError()));
+  return rc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Potential::Precondition, input part (Potential.cpp:404-455)
+extern "C" int pp_precondition(pp_context* c, int input_precondition)
+{
+  if (nets_ready(c)) return 1;
+  PP_CUDA(cudaSetDevice(c->device));
+  const int NG = c->spec.NG;
+  const int n_cta = 64;
+  cudaStream_t st = c->stream;
+  if (c->d_stat_partial.ensure((size_t)n_cta * NG, 0, st) || c->d_stat_sums.ensure(2 * (size_t)NG, 0, st) || c->d_count.ensure(1, 0, st)) return 1;
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    std::vector<double> mean(NG, 0.0), var(NG, 1.0);
+    if (input_precondition) {
+      const int M = (int)c->h_rows[e].size();
+      PP_CUDA(cudaMemsetAsync(c->d_count.p, 0, sizeof(long long), st));
+      if (ppk_column_stats(c->d_G.p, NG, c->d_rows[e].p, M, c->d_atom_struct.p, c->d_tag.p, nullptr, 0, c->d_stat_partial.p, n_cta,
+                           c->d_stat_sums.p, c->d_count.p, st, &c->launches)) return 1;
+      std::vector<double> buf(NG + 1);
+      long long cnt = 0;
+      PP_CUDA(cudaMemcpyAsync(buf.data(), c->d_stat_sums.p, NG * sizeof(double), cudaMemcpyDeviceToHost, st));
+      PP_CUDA(cudaMemcpyAsync(&cnt, c->d_count.p, sizeof(long long), cudaMemcpyDeviceToHost, st));
+      PP_CUDA(cudaStreamSynchronize(st));
+      buf[NG] = (double)cnt;
+      if (c->comm.allreduce_host(buf.data(), NG + 1, st)) return 1;    // Potential.cpp:419-420
+      double count = buf[NG];
+      for (int k = 0; k < NG; k++) mean[k] = count != 0 ? buf[k] / count : buf[k];
+      PP_CUDA(cudaMemcpyAsync(c->d_stat_sums.p + NG, mean.data(), NG * sizeof(double), cudaMemcpyHostToDevice, st));
+      if (ppk_column_stats(c->d_G.p, NG, c->d_rows[e].p, M, c->d_atom_struct.p, c->d_tag.p, c->d_stat_sums.p + NG, 1, c->d_stat_partial.p,
+                           n_cta, c->d_stat_sums.p, c->d_count.p, st, &c->launches)) return 1;
+      PP_CUDA(cudaMemcpyAsync(buf.data(), c->d_stat_sums.p, NG * sizeof(double), cudaMemcpyDeviceToHost, st));
+      PP_CUDA(cudaStreamSynchronize(st));
+      if (c->comm.allreduce_host(buf.data(), NG, st)) return 1;        // Potential.cpp:442
+      for (int k = 0; k < NG; k++) {
+        var[k] = buf[k];
+        if (count != 0) {
+          var[k] = sqrt(var[k] / count);
+          if (var[k] < 1e-5) var[k] = 1e-5;
+        }
+      }
+    }
+    if (pp_set_input_scaling(c, e, mean.data(), var.data())) return 1;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+static MlpArgs mlp_args_train(pp_context* c, int e)
+{
+  MlpArgs a;
+  memset(&a, 0, sizeof(a));
+  a.net = c->nets[e].dev;
+  a.G = c->d_G.p;
+  a.rows = c->spec.n_elem == 1 ? nullptr : c->d_rows[e].p;
+  a.M = (int)c->h_rows[e].size();
+  a.atom_struct = c->d_atom_struct.p;
+  a.cstruct = c->d_cstruct.p;
+  a.out_scale = c->out_scale;
+  a.E_atom = c->d_E_atom.p;
+  a.partial = c->d_partial.p;
+  a.P_total = c->P_total;
+  a.p_off = c->nets[e].p_off;
+  a.tanh_table = c->d_tanh_table.p;
+  return a;
+}
+
+static int forward_all(pp_context* c)
+{
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    MlpArgs a = mlp_args_train(c, e);
+    if (ppk_mlp_launch(PP_MLP_FORWARD, a, c->stream, &c->launches)) return 1;
+  }
+  StructArgs sa;
+  sa.n_struct = c->n_struct;
+  sa.struct_atom0 = c->d_struct_atom0.p;
+  sa.E_atom = c->d_E_atom.p;
+  sa.target = c->d_target.p;
+  sa.tag = c->d_tag.p;
+  sa.out_mean = c->out_mean;
+  sa.out_scale = c->out_scale;
+  sa.E_struct = c->d_E_struct.p;
+  sa.cstruct = c->d_cstruct.p;
+  sa.result_tail = c->d_result.p + c->P_total;
+  return ppk_struct_errors(sa, c->stream, &c->launches);
+}
+
+static int epoch_buffers(pp_context* c)
+{
+  const int n_cta = ppk_mlp_max_ctas();
+  if (c->d_partial.ensure((size_t)n_cta * std::max(c->P_total, 1), 0, c->stream)) return 1;
+  if (c->d_result.ensure((size_t)c->P_total + 3, 0, c->stream)) return 1;
+  return 0;
+}
+
+extern "C" int pp_epoch_device(pp_context* c)
+{
+  if (nets_ready(c)) return 1;
+  PP_REQUIRE(c->n_struct > 0, "pp_epoch: no structures");
+  PP_CUDA(cudaSetDevice(c->device));
+  if (epoch_buffers(c)) return 1;
+  if (tick(c, 0)) return 1;
+  if (forward_all(c)) return 1;
+  if (tick(c, 1)) return 1;
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    MlpArgs a = mlp_args_train(c, e);
+    if (ppk_mlp_launch(PP_MLP_TRAIN, a, c->stream, &c->launches)) return 1;
+  }
+  if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_max_ctas(), c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
+  if (tick(c, 2)) return 1;
+  if (c->comm.allreduce_device(c->d_result.p, c->P_total + 3, c->stream)) return 1;
+  if (tick(c, 3)) return 1;
+  return 0;
+}
+
+extern "C" int pp_epoch_result_dev(pp_context* c, double** result_dev, int* n)
+{
+  PP_REQUIRE(c && result_dev && n, "pp_epoch_result_dev: bad arguments");
+  if (epoch_buffers(c)) return 1;
+  *result_dev = c->d_result.p;
+  *n = c->P_total + 3;
+  return 0;
+}
+
+extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out, double* sse, double* vsse, long long* nval)
+{
+  if (nets_ready(c)) return 1;
+  if (params_in) {
+    for (int e = 0; e < c->spec.n_elem; e++) {
+      NetHost& n = c->nets[e];
+      std::copy(params_in + n.p_off, params_in + n.p_off + n.P, n.params.begin());
+    }
+    PP_CUDA(cudaMemcpyAsync(c->d_params.p, params_in, c->P_total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  }
+  if (pp_epoch_device(c)) return 1;
+  c->h_result.resize((size_t)c->P_total + 3);
+  PP_CUDA(cudaMemcpyAsync(c->h_result.data(), c->d_result.p, c->h_result.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  tock(c, 0, 1, 1); tock(c, 1, 2, 2); tock(c, 2, 3, 3);
+  if (grad_out) std::copy(c->h_result.begin(), c->h_result.begin() + c->P_total, grad_out);
+  if (sse) *sse = c->h_result[c->P_total];
+  if (vsse) *vsse = c->h_result[c->P_total + 1];
+  if (nval) *nval = (long long)llround(c->h_result[c->P_total + 2]);
+  return 0;
+}
+
+extern "C" int pp_evaluate(pp_context* c, double* E_out)
+{
+  if (nets_ready(c)) return 1;
+  PP_REQUIRE(c->n_struct > 0, "pp_evaluate: no structures");
+  PP_CUDA(cudaSetDevice(c->device));
+  if (epoch_buffers(c)) return 1;
+  if (forward_all(c)) return 1;
+  PP_CUDA(cudaMemcpyAsync(E_out, c->d_E_struct.p, c->n_struct * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int pp_get_atom_energies(pp_context* c, int s, double* E_atom_out)
+{
+  PP_REQUIRE(c && s >= 0 && s < c->n_struct, "pp_get_atom_energies: structure %d out of range", s);
+  const long long a0 = c->h_struct_atom0[s];
+  const int n = (int)(c->h_struct_atom0[s + 1] - a0);
+  PP_CUDA(cudaMemcpyAsync(E_atom_out, c->d_E_atom.p + a0, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// LAMMPS pair_style nn (pair_nn.cpp:112-188)
+extern "C" int pp_md_set_types(pp_context* c, int ntypes, const int* type_to_elem)
+{
+  PP_REQUIRE(c && c->spec_set, "pp_md_set_types: descriptors not set");
+  PP_REQUIRE(ntypes >= 1, "pp_md_set_types: ntypes must be >= 1");
+  c->type_to_elem.assign(type_to_elem, type_to_elem + ntypes + 1);
+  for (int t = 1; t <= ntypes; t++)
+    PP_REQUIRE(c->type_to_elem[t] >= 0 && c->type_to_elem[t] < c->spec.n_elem, "pp_md_set_types: type %d maps to element %d", t, c->type_to_elem[t]);
+  return 0;
+}
+
+static int md_upload_atoms(pp_context* c, const double* x, const int* type, int nlocal, int nghost)
+{
+  const int ntotal = nlocal + nghost;
+  cudaStream_t st = c->stream;
+  const int NG = c->spec.NG;
+  if (c->d_x.ensure(3 * (size_t)ntotal, 0, st) || c->d_f.ensure(3 * (size_t)ntotal, 0, st) || c->d_md_elem.ensure(ntotal, 0, st) ||
+      c->d_Gmd.ensure((size_t)std::max(nlocal, 1) * NG, 0, st) || c->d_dEdG.ensure((size_t)std::max(nlocal, 1) * NG, 0, st) ||
+      c->d_eatom.ensure(std::max(nlocal, 1), 0, st))
+    return 1;
+  c->h_md_elem.resize(ntotal);
+  const int ntypes = (int)c->type_to_elem.size() - 1;
+  for (int i = 0; i < ntotal; i++) {
+    PP_REQUIRE(type[i] >= 1 && type[i] <= ntypes, "pp_md: atom %d has type %d outside 1..%d", i, type[i], ntypes);
+    c->h_md_elem[i] = c->type_to_elem[type[i]];
+  }
+  PP_CUDA(cudaMemcpyAsync(c->d_x.p, x, 3 * (size_t)ntotal * sizeof(double), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemcpyAsync(c->d_md_elem.p, c->h_md_elem.data(), ntotal * sizeof(int), cudaMemcpyHostToDevice, st));
+  // per-element lists of local atoms
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    std::vector<int> rows;
+    for (int i = 0; i < nlocal; i++) if (c->h_md_elem[i] == e) rows.push_back(i);
+    c->md_rows_n[e] = (int)rows.size();
+    if (c->d_md_rows[e].ensure(std::max<size_t>(rows.size(), 1), 0, st)) return 1;
+    if (!rows.empty()) {
+      PP_CUDA(cudaMemcpyAsync(c->d_md_rows[e].p, rows.data(), rows.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+      PP_CUDA(cudaStreamSynchronize(st));   // rows is a local
+    }
+  }
+  c->md_nlocal = nlocal;
+  c->md_ntotal = ntotal;
+  return 0;
+}
+
+static int md_run(pp_context* c)
+{
+  cudaStream_t st = c->stream;
+  const int nlocal = c->md_nlocal;
+  MdArgs a;
+  memset(&a, 0, sizeof(a));
+  a.spec = c->d_spec;
+  a.nlocal = nlocal;
+  a.x = c->d_x.p;
+  a.elem = c->d_md_elem.p;
+  a.neigh_offsets = c->d_neigh_off.p;
+  a.neigh = c->d_neigh.p;
+  a.G = c->d_Gmd.p;
+  a.dEdG = c->d_dEdG.p;
+  a.f = c->d_f.p;
+  a.overflow = c->d_overflow.p;
+  if (tick(c, 0)) return 1;
+  if (ppk_md_desc(c->spec, a, &c->md_cap, st, &c->launches)) return 1;
+  if (tick(c, 1)) return 1;
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    MlpArgs m;
+    memset(&m, 0, sizeof(m));
+    m.net = c->nets[e].dev;
+    m.G = c->d_Gmd.p;
+    m.rows = c->spec.n_elem == 1 ? nullptr : c->d_md_rows[e].p;
+    m.M = c->md_rows_n[e];
+    m.out_scale = c->out_scale;
+    m.E_atom = c->d_eatom.p;
+    m.dEdG = c->d_dEdG.p;
+    m.tanh_table = c->d_tanh_table.p;
+    if (ppk_mlp_launch(PP_MLP_INPUT_GRAD, m, st, &c->launches)) return 1;
+  }
+  if (tick(c, 2)) return 1;
+  if (ppk_md_force(c->spec, a, c->md_cap, st, &c->launches)) return 1;
+  if (tick(c, 3)) return 1;
+  return 0;
+}
+
+extern "C" int pp_md_compute(pp_context* c, const double* x, const int* type, int nlocal, int nghost,
+                             const long long* neigh_offsets, const int* neigh_flat,
+                             double* f_inout, double* eatom_out, double* etotal_out, double* G_out, double* dEdG_out)
+{
+  if (nets_ready(c)) return 1;
+  PP_REQUIRE(!c->type_to_elem.empty(), "pp_md_compute: call pp_md_set_types first");
+  PP_REQUIRE(nlocal >= 0 && nghost >= 0 && x && type && neigh_offsets, "pp_md_compute: bad arguments");
+  PP_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int ntotal = nlocal + nghost;
+  const int NG = c->spec.NG;
+  if (md_upload_atoms(c, x, type, nlocal, nghost)) return 1;
+  const long long nn = neigh_offsets[nlocal];
+  for (long long p = 0; p < nn; p++) PP_REQUIRE(neigh_flat[p] >= 0 && neigh_flat[p] < ntotal, "pp_md_compute: neighbour index %d out of range", neigh_flat[p]);
+  if (c->d_neigh_off.ensure(nlocal + 1, 0, st) || c->d_neigh.ensure(std::max<long long>(nn, 1), 0, st)) return 1;
+  PP_CUDA(cudaMemcpyAsync(c->d_neigh_off.p, neigh_offsets, (nlocal + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+  if (nn) PP_CUDA(cudaMemcpyAsync(c->d_neigh.p, neigh_flat, nn * sizeof(int), cudaMemcpyHostToDevice, st));
+  c->md_nneigh = nn;
+  PP_CUDA(cudaMemsetAsync(c->d_f.p, 0, 3 * (size_t)ntotal * sizeof(double), st));
+  if (md_run(c)) return 1;
+  std::vector<double> f(3 * (size_t)ntotal), ea(std::max(nlocal, 1));
+  PP_CUDA(cudaMemcpyAsync(f.data(), c->d_f.p, f.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  PP_CUDA(cudaMemcpyAsync(ea.data(), c->d_eatom.p, nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (G_out) PP_CUDA(cudaMemcpyAsync(G_out, c->d_Gmd.p, (size_t)nlocal * NG * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (dEdG_out) PP_CUDA(cudaMemcpyAsync(dEdG_out, c->d_dEdG.p, (size_t)nlocal * NG * sizeof(double), cudaMemcpyDeviceToHost, st));
+  PP_CUDA(cudaStreamSynchronize(st));
+  tock(c, 0, 1, 4); tock(c, 1, 2, 5); tock(c, 2, 3, 6);
+  if (f_inout) for (size_t i = 0; i < f.size(); i++) f_inout[i] += f[i];
+  double et = 0.0;
+  for (int i = 0; i < nlocal; i++) { et += ea[i]; if (eatom_out) eatom_out[i] = ea[i]; }
+  if (etotal_out) *etotal_out = et + c->out_mean;      // pair_nn.cpp:175-179
+  return 0;
+}
+
+extern "C" int pp_md_build_neighbors(pp_context*, const double*, const int*, int, int, double)
+{
+  pp_set_error("pp_md_build_neighbors: not implemented yet");
+  return 1;
+}
+extern "C" int pp_md_get_neighbors(pp_context*, long long*, int*, long long*)
+{
+  pp_set_error("pp_md_get_neighbors: not implemented yet");
+  return 1;
+}
+extern "C" int pp_md_step(pp_context*, const double*, double*, double*, double*)
+{
+  pp_set_error("pp_md_step: not implemented yet");
+  return 1;
+}
+extern "C" int pp_md_step_device(pp_context*, const double*, double*, double*)
+{
+  pp_set_error("pp_md_step_device: not implemented yet");
+  return 1;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+extern "C" int pp_comm_unique_id(void* id) { return PPComm::unique_id(id); }
+extern "C" int pp_comm_init(pp_context* c, int nranks, int rank, const void* id)
+{
+  PP_REQUIRE(c, "null context");
+  PP_CUDA(cudaSetDevice(c->device));
+  return c->comm.init(nranks, rank, id);
+}
+extern "C" int pp_comm_rank(pp_context* c) { return c ? c->comm.rank : 0; }
+extern "C" int pp_comm_size(pp_context* c) { return c ? c->comm.nranks : 1; }

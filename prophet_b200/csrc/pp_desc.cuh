@@ -1,0 +1,519 @@
+// Descriptor (G1/G2/G4) and force-chain-rule device code shared by the periodic (training) and the
+// LAMMPS-list (MD) kernels.
+//
+// Replaces Structure::Set_Neighbor (Structure.cpp:1287-1381), Structure::Calc_G (:974-1147) and the
+// non-periodic branch of Structure::Get_Forces (:429-713).
+//
+// Design (B200, FP64-FMA bound -- see DESIGN.md):
+//   * one warp per central atom; its neighbour entries (unit vector, R, element, per-radial-key factors
+//     A_r(R) = exp(-eta_r R^2) fc_r(R)) are staged in shared memory, sorted by element;
+//   * G4 is factorised over a (radial key) x (angular key) grid so that one (j,k) pair costs
+//     3 FMA (cos) + a few multiplies (integer powers of 1 + lam c) + NR*NA FMAs, instead of NR*NA exps;
+//   * every UNORDERED pair is visited once (the reference visits both orders, Structure.cpp:1027-1066; the
+//     factor 2 is applied at the end); lanes own entry a and walk partners b on a circulant schedule
+//     b = (a + t) mod m, which balances the triangle and -- in the force kernel -- makes the shared-memory
+//     read-modify-write of the partner's force conflict-free without atomics;
+//   * accumulators live in registers ([NR_T][NA_T] per lane) and are reduced across the warp once per
+//     element-pair block.
+#pragma once
+#include "pp_common.cuh"
+
+// ---------------------------------------------------------------------------------------------------------
+// per-warp shared-memory views
+struct WarpNbr {
+  double *ux, *uy, *uz, *R;   // [cap] unit vector i->entry and distance
+  double *A;                  // [NR][cap]   radial factors of the G4 grid
+  double *dA;                 // [NR][cap]   dA/dR (force kernels only)
+  double *fx, *fy, *fz;       // [cap]       force-gradient accumulated on entries by partner lanes (force only)
+  double *sx, *sy, *sz, *sR;  // [cap]       staging (pre-sort)
+  int *elem, *selem;          // [cap]
+  int *idx, *sidx;            // [cap]       neighbour atom index (MD scatter / hook)
+  double *buf;                // [max(NG, ...)] G row (desc) or dE/dG row (force)
+  double *cell;               // [PP_MAX_RAD*PP_MAX_ANG] reduced grid cells
+  int n;                      // entries
+  int start[PP_MAX_ELEM + 1]; // element block boundaries after the sort
+};
+
+__host__ __device__ inline size_t pp_warp_smem_bytes(int cap, int NR, int NG, bool force)
+{
+  size_t d = 0;
+  d += 4 * (size_t)cap;                 // ux uy uz R
+  d += 4 * (size_t)cap;                 // staging
+  d += (size_t)NR * cap;                // A
+  if (force) d += (size_t)NR * cap + 3 * (size_t)cap;
+  d += (size_t)NG;
+  d += PP_MAX_RAD * PP_MAX_ANG;
+  size_t bytes = d * sizeof(double) + 4 * (size_t)cap * sizeof(int);
+  return (bytes + 15) & ~(size_t)15;
+}
+
+__device__ inline void pp_warp_views(WarpNbr& w, unsigned char* base, int cap, int NR, int NG, bool force)
+{
+  double* p = reinterpret_cast<double*>(base);
+  w.ux = p; p += cap; w.uy = p; p += cap; w.uz = p; p += cap; w.R = p; p += cap;
+  w.sx = p; p += cap; w.sy = p; p += cap; w.sz = p; p += cap; w.sR = p; p += cap;
+  w.A = p; p += (size_t)NR * cap;
+  if (force) { w.dA = p; p += (size_t)NR * cap; w.fx = p; p += cap; w.fy = p; p += cap; w.fz = p; p += cap; }
+  else { w.dA = nullptr; w.fx = w.fy = w.fz = nullptr; }
+  w.buf = p; p += NG;
+  w.cell = p; p += PP_MAX_RAD * PP_MAX_ANG;
+  int* q = reinterpret_cast<int*>(p);
+  w.elem = q; q += cap; w.selem = q; q += cap; w.idx = q; q += cap; w.sidx = q; q += cap;
+  w.n = 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K1a: periodic image scan for central atom i of one structure, reference arithmetic and order
+// (Structure.cpp:1316-1352): for j ascending, for image t ascending:
+//   del = (pos[j] + T_t) - pos[i]  (fractional)  ->  To_Cart  ->  distance;  keep 0.01 < d <= Rcut.
+// No FMA contraction: the kept set must be bit-identical to the reference's SSE2 build.
+// Entries are appended to the staging arrays (sx,sy,sz,sR,selem,sidx) in order; sidx packs j, and the
+// image index goes to `timg` when the caller wants it (parity hook).  Returns the count (may exceed cap: then
+// nothing beyond cap is stored).
+__device__ inline int pp_scan_periodic(WarpNbr& w, int cap, int lane, const double* __restrict__ frac,
+                                       const int* __restrict__ elem, int natom, int i, const double* F,
+                                       int mx, int my, int mz, double Rcut, int* timg)
+{
+  const int ny = 2 * my + 1, nz = 2 * mz + 1;
+  const int nT = (2 * mx + 1) * ny * nz;
+  const long long ncand = (long long)natom * nT;
+  const double ix = frac[3 * i], iy = frac[3 * i + 1], iz = frac[3 * i + 2];
+  int count = 0;
+  for (long long c0 = 0; c0 < ncand; c0 += 32) {
+    long long c = c0 + lane;
+    bool keep = false;
+    double dx = 0, dy = 0, dz = 0, d = 0;
+    int j = 0, t = 0;
+    if (c < ncand) {
+      j = (int)(c / nT);
+      t = (int)(c - (long long)j * nT);
+      int tx = t / (ny * nz) - mx;
+      int rem = t % (ny * nz);
+      int ty = rem / nz - my;
+      int tz = rem % nz - mz;
+      double fx = __dsub_rn(__dadd_rn(frac[3 * j], (double)tx), ix);
+      double fy = __dsub_rn(__dadd_rn(frac[3 * j + 1], (double)ty), iy);
+      double fz = __dsub_rn(__dadd_rn(frac[3 * j + 2], (double)tz), iz);
+      dx = __dadd_rn(__dadd_rn(__dmul_rn(F[0], fx), __dmul_rn(F[1], fy)), __dmul_rn(F[2], fz));
+      dy = __dadd_rn(__dadd_rn(__dmul_rn(F[3], fx), __dmul_rn(F[4], fy)), __dmul_rn(F[5], fz));
+      dz = __dadd_rn(__dadd_rn(__dmul_rn(F[6], fx), __dmul_rn(F[7], fy)), __dmul_rn(F[8], fz));
+      d = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+      keep = (d > 0.01) && (d <= Rcut);
+    }
+    unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (keep) {
+      int pos = count + __popc(m & ((1u << lane) - 1u));
+      if (pos < cap) {
+        w.sx[pos] = dx; w.sy[pos] = dy; w.sz[pos] = dz; w.sR[pos] = d;
+        w.selem[pos] = elem[j];
+        w.sidx[pos] = j;
+        if (timg) timg[pos] = t;
+      }
+    }
+    count += __popc(m);
+  }
+  return count;
+}
+
+// K1b: LAMMPS-list gather (Structure.cpp:1080-1096): skip j == i, skip R > Rcut.
+__device__ inline int pp_gather_list(WarpNbr& w, int cap, int lane, const double* __restrict__ x,
+                                     const int* __restrict__ elem_of_atom, int i, const int* __restrict__ list,
+                                     int nlist, double Rcut)
+{
+  const double ix = x[3 * (size_t)i], iy = x[3 * (size_t)i + 1], iz = x[3 * (size_t)i + 2];
+  int count = 0;
+  for (int p0 = 0; p0 < nlist; p0 += 32) {
+    int p = p0 + lane;
+    bool keep = false;
+    double dx = 0, dy = 0, dz = 0, d = 0;
+    int j = 0;
+    if (p < nlist) {
+      j = list[p];
+      dx = __dsub_rn(x[3 * (size_t)j], ix);
+      dy = __dsub_rn(x[3 * (size_t)j + 1], iy);
+      dz = __dsub_rn(x[3 * (size_t)j + 2], iz);
+      d = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+      keep = (j != i) && !(d > Rcut);
+    }
+    unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (keep) {
+      int pos = count + __popc(m & ((1u << lane) - 1u));
+      if (pos < cap) {
+        w.sx[pos] = dx; w.sy[pos] = dy; w.sz[pos] = dz; w.sR[pos] = d;
+        w.selem[pos] = elem_of_atom[j];
+        w.sidx[pos] = j;
+      }
+    }
+    count += __popc(m);
+  }
+  return count;
+}
+
+// Stable counting sort of the staged entries by element, then unit vectors and radial factors.
+template <bool FORCE>
+__device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, int n)
+{
+  const int n_elem = S->n_elem;
+  w.n = n;
+  __syncwarp();
+  // destination index of every staged entry
+  int base = 0;
+  for (int e = 0; e < n_elem; e++) {
+    w.start[e] = base;
+    int cnt = 0;
+    for (int p0 = 0; p0 < n; p0 += 32) {
+      int p = p0 + lane;
+      bool is_e = (p < n) && (n_elem == 1 || w.selem[p] == e);
+      unsigned m = __ballot_sync(0xffffffffu, is_e);
+      if (is_e) {
+        int dst = base + cnt + __popc(m & ((1u << lane) - 1u));
+        double R = w.sR[p];
+        double inv = 1.0 / R;
+        w.ux[dst] = w.sx[p] * inv; w.uy[dst] = w.sy[p] * inv; w.uz[dst] = w.sz[p] * inv;
+        w.R[dst] = R;
+        w.elem[dst] = e;
+        w.idx[dst] = w.sidx[p];
+      }
+      cnt += __popc(m);
+    }
+    base += cnt;
+  }
+  for (int e = n_elem; e <= PP_MAX_ELEM; e++) w.start[e] = base;
+  __syncwarp();
+  // radial factors of the G4 grid: A_r = exp(-eta_r R^2) fc_r(R)  (0 beyond the row's own Rc: fc returns 0)
+  const int NR = S->NR;
+  for (int p = lane; p < n; p += 32) {
+    double R = w.R[p];
+    for (int r = 0; r < NR; r++) {
+      double rc = S->rad_rc[r], eta = S->rad_eta[r];
+      int fs = S->rad_fc[r];
+      double ex = exp(-eta * (R * R));
+      double f = pp_fc(R / rc, fs);
+      w.A[(size_t)r * cap + p] = ex * f;
+      if (FORCE) w.dA[(size_t)r * cap + p] = ex * (pp_dfc(rc, R, fs) - 2.0 * R * eta * f);
+    }
+    if (FORCE) { w.fx[p] = 0.0; w.fy[p] = 0.0; w.fz[p] = 0.0; }
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// (1 + lam c)^xi for the angular keys [a0, a0+NA_T) of the grid (Structure.h:251-296).  Raw power, without
+// the 2^(1-xi) prefactor.  Integer xi: square-and-multiply with a warp-uniform exponent (no divergence);
+// non-integer xi: the reference's binomial series with its 1e-8 stopping rule and pow() fallback.
+__device__ __forceinline__ double pp_ipow(double x, int e)
+{
+  double r = (e & 1) ? x : 1.0;
+  e >>= 1;
+  while (e) {
+    x *= x;
+    if (e & 1) r *= x;
+    e >>= 1;
+  }
+  return r;
+}
+
+__device__ inline double pp_series_pow(double th, double xi)
+{
+  // th = lam*c > -1
+  double alpha = xi * th;
+  int term = 1;
+  double result = 1.0;
+  while (fabs(alpha) > 1e-8) {
+    result += alpha;
+    double tay = term < 300 ? 1.0 / (double)(term + 1) : 0.0;
+    alpha *= tay * th * (xi - term);
+    ++term;
+  }
+  if (term >= 250) return pow(1.0 + th, xi);
+  return result + alpha;
+}
+
+// Angular keys of one grid chunk, hoisted into registers once per block.
+template <int NA_T>
+struct AngKeys {
+  double lam[NA_T];
+  double xi[NA_T];
+  int xe[NA_T];      // integer exponent; -1 = non-integer xi (series); -2 = padding (value 0)
+};
+
+template <int NA_T>
+__device__ __forceinline__ void pp_load_ang(const DescSpec* __restrict__ S, int a0, AngKeys<NA_T>& K)
+{
+#pragma unroll
+  for (int a = 0; a < NA_T; a++) {
+    int ga = a0 + a;
+    bool ok = ga < S->NA;
+    K.lam[a] = ok ? S->ang_lam[ga] : 0.0;
+    K.xi[a] = ok ? S->ang_xi[ga] : 0.0;
+    K.xe[a] = ok ? S->ang_xi_int[ga] : -2;
+  }
+}
+
+template <int NA_T>
+__device__ __forceinline__ void pp_angular(const AngKeys<NA_T>& K, double c, double (&p)[NA_T])
+{
+#pragma unroll
+  for (int a = 0; a < NA_T; a++) {
+    double x = fma(K.lam[a], c, 1.0);
+    int xe = K.xe[a];
+    double v = 0.0;
+    if (xe >= 0) v = pp_ipow(x, xe);
+    else if (xe == -1 && x > 0.0) v = pp_series_pow(K.lam[a] * c, K.xi[a]);
+    p[a] = (x > 0.0) ? v : 0.0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// G1/G2 rows of one central atom (Structure.cpp:1005-1014 / 1097-1106), accumulated into w.buf[slot].
+__device__ inline void pp_pair_rows_desc(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S)
+{
+  const int npair = S->npair;
+  for (int e = 0; e < S->n_elem; e++) {
+    const int s = w.start[e], m = w.start[e + 1] - s;
+    for (int r = 0; r < npair; r++) {
+      double rc = S->pair_rc[r], eta = S->pair_eta[r], rs = S->pair_rs[r];
+      int fs = S->pair_fc[r];
+      bool g1 = r < S->nG1;
+      double acc = 0.0;
+      for (int a = lane; a < m; a += 32) {
+        double R = w.R[s + a];
+        double f = pp_fc(R / rc, fs);
+        if (!g1) { double d = R - rs; f *= exp(-eta * (d * d)); }
+        acc += f;
+      }
+      acc = pp_warp_sum(acc);
+      if (lane == 0) w.buf[npair * e + r] = acc;
+    }
+  }
+  __syncwarp();
+}
+
+// G4 rows for the element-pair block (e1 <= e2), grid chunk [r0,r0+NR_T) x [a0,a0+NA_T).
+// skip_rjk: the non-periodic branch skips the pair when G3 rows exist and Rjk > Rcut (Structure.cpp:1129-1132).
+template <int NR_T, int NA_T>
+__device__ inline void pp_g4_block_desc(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
+                                        int e1, int e2, int r0, int a0, bool skip_rjk)
+{
+  const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
+  const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
+  const bool same = (e1 == e2);
+  const double rcut2 = S->Rcut * S->Rcut;
+  double acc[NR_T][NA_T];
+#pragma unroll
+  for (int r = 0; r < NR_T; r++)
+#pragma unroll
+    for (int a = 0; a < NA_T; a++) acc[r][a] = 0.0;
+  AngKeys<NA_T> K;
+  pp_load_ang<NA_T>(S, a0, K);
+  const int NR = S->NR;
+  const double* Arow[NR_T];     // padded radial keys alias the last valid row; their own-entry factor is 0
+#pragma unroll
+  for (int r = 0; r < NR_T; r++) Arow[r] = w.A + (size_t)min(r0 + r, NR - 1) * cap;
+
+  for (int a = lane; a < m1; a += 32) {
+    const int ja = s1 + a;
+    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+    double Aa[NR_T];
+#pragma unroll
+    for (int r = 0; r < NR_T; r++) Aa[r] = (r0 + r < NR) ? Arow[r][ja] : 0.0;
+    // partner schedule: same block -> circulant half ring; cross block -> every entry of block 2
+    int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    for (int t = 0; t < nt; t++) {
+      int jb;
+      if (same) { int b = a + t + 1; if (b >= m1) b -= m1; jb = s1 + b; }
+      else jb = s2 + t;
+      double c = ax * w.ux[jb] + ay * w.uy[jb] + az * w.uz[jb];
+      if (skip_rjk) {
+        double Rb = w.R[jb];
+        double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c;
+        if (rjk2 > rcut2) continue;
+      }
+      double p[NA_T];
+      pp_angular<NA_T>(K, c, p);
+#pragma unroll
+      for (int r = 0; r < NR_T; r++) {
+        double tr = Aa[r] * Arow[r][jb];
+#pragma unroll
+        for (int q = 0; q < NA_T; q++) acc[r][q] = fma(p[q], tr, acc[r][q]);
+      }
+    }
+  }
+  // warp reduction of the grid cells; factor 2 = both (j,k) orders of the reference
+#pragma unroll
+  for (int r = 0; r < NR_T; r++)
+#pragma unroll
+    for (int q = 0; q < NA_T; q++) {
+      double v = pp_warp_sum(acc[r][q]);
+      if (lane == 0) w.cell[r * NA_T + q] = 2.0 * v;
+    }
+  __syncwarp();
+  const int base = S->trip_base[e1][e2] + S->nG3;
+  for (int row = lane; row < S->nG4; row += 32) {
+    int rr = S->g4_rad[row] - r0, qq = S->g4_ang[row] - a0;
+    if (rr >= 0 && rr < NR_T && qq >= 0 && qq < NA_T) w.buf[base + row] = S->ang_pref[S->g4_ang[row]] * w.cell[rr * NA_T + qq];
+  }
+  __syncwarp();
+}
+
+template <int NR_T, int NA_T>
+__device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
+{
+  for (int g = lane; g < S->NG; g += 32) w.buf[g] = 0.0;
+  __syncwarp();
+  if (S->npair) pp_pair_rows_desc(w, cap, lane, S);
+  if (S->nG4) {
+    for (int e1 = 0; e1 < S->n_elem; e1++)
+      for (int e2 = e1; e2 < S->n_elem; e2++)
+        for (int r0 = 0; r0 < S->NR; r0 += NR_T)
+          for (int a0 = 0; a0 < S->NA; a0 += NA_T) pp_g4_block_desc<NR_T, NA_T>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Force chain rule, G1/G2 rows (Structure.cpp:449-481): gradient of sum_r w_r G_r wrt each entry's position
+// is (dE/dR) * u; accumulated into the lane's own entries fx/fy/fz.
+__device__ inline void pp_pair_rows_force(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S)
+{
+  const int npair = S->npair;
+  for (int p = lane; p < w.n; p += 32) {
+    double R = w.R[p];
+    int e = w.elem[p];
+    double dEdR = 0.0;
+    for (int r = 0; r < npair; r++) {
+      double rc = S->pair_rc[r];
+      if (R >= rc) continue;
+      int fs = S->pair_fc[r];
+      double wt = w.buf[npair * e + r];
+      if (r < S->nG1) {
+        dEdR += wt * pp_dfc(rc, R, fs);
+      } else {
+        double eta = S->pair_eta[r], d = R - S->pair_rs[r];
+        dEdR += wt * exp(-eta * d * d) * (pp_dfc(rc, R, fs) - 2.0 * eta * d * pp_fc(R / rc, fs));
+      }
+    }
+    w.fx[p] += dEdR * w.ux[p]; w.fy[p] += dEdR * w.uy[p]; w.fz[p] += dEdR * w.uz[p];
+  }
+  __syncwarp();
+}
+
+// Force chain rule, G4 rows (Structure.cpp:645-708), factorised:
+//   Phi = sum_pairs sum_{r,q} W[r][q] P_q(c) A_r(Ra) A_r(Rb),   W = 2 * 2^(1-xi) * dE/dG(row)
+//   dPhi/dRa = sum_r S_r dA_r(Ra) A_r(Rb),  S_r = sum_q W[r][q] P_q
+//   dPhi/dc  = sum_r T_r  A_r(Ra) A_r(Rb),  T_r = sum_q W[r][q] P'_q,  P'_q = xi lam P_q / (1 + lam c)
+//   grad_a = dPhi/dRa u_a + dPhi/dc (u_b - c u_a)/Ra   (and a<->b)
+// The lane accumulates grad_a of its own entry in registers; grad_b goes to shared memory, conflict-free because
+// at any step the active lanes hold distinct b.
+template <int NR_T, int NA_T>
+__device__ inline void pp_g4_block_force(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
+                                         int e1, int e2, int r0, int a0, bool skip_rjk)
+{
+  const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
+  const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
+  if (m1 == 0 || m2 == 0) return;
+  const bool same = (e1 == e2);
+  const double rcut2 = S->Rcut * S->Rcut;
+  // weights of the grid chunk for this element pair
+  for (int i = lane; i < NR_T * NA_T; i += 32) w.cell[i] = 0.0;
+  __syncwarp();
+  const int base = S->trip_base[e1][e2] + S->nG3;
+  for (int row = lane; row < S->nG4; row += 32) {
+    int rr = S->g4_rad[row] - r0, qq = S->g4_ang[row] - a0;
+    // rows sharing a grid cell (duplicated rows) are summed by one lane at a time
+    if (rr >= 0 && rr < NR_T && qq >= 0 && qq < NA_T)
+      atomicAdd(&w.cell[rr * NA_T + qq], 2.0 * S->ang_pref[S->g4_ang[row]] * w.buf[base + row]);
+  }
+  __syncwarp();
+  double W[NR_T][NA_T];
+#pragma unroll
+  for (int r = 0; r < NR_T; r++)
+#pragma unroll
+    for (int q = 0; q < NA_T; q++) W[r][q] = w.cell[r * NA_T + q];
+  AngKeys<NA_T> K;
+  pp_load_ang<NA_T>(S, a0, K);
+  double xil[NA_T];   // xi*lam per angular key
+#pragma unroll
+  for (int q = 0; q < NA_T; q++) xil[q] = K.xi[q] * K.lam[q];
+  const int NR = S->NR;
+  const double *Arow[NR_T], *dArow[NR_T];
+#pragma unroll
+  for (int r = 0; r < NR_T; r++) {
+    Arow[r] = w.A + (size_t)min(r0 + r, NR - 1) * cap;
+    dArow[r] = w.dA + (size_t)min(r0 + r, NR - 1) * cap;
+  }
+
+  // lanes active per pass: distinct partner indices require #lanes <= m2 in cross blocks
+  const int width = same ? 32 : (m2 < 32 ? m2 : 32);
+  const int npass = (m1 + width - 1) / width;
+  const int nt_max = same ? (m1 >> 1) : m2;
+  for (int pass = 0; pass < npass; pass++) {
+    const int a = pass * width + lane;
+    const bool act = (lane < width) && (a < m1);
+    const int ja = s1 + (act ? a : 0);
+    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+    const double invRa = 1.0 / Ra;
+    double Aa[NR_T], dAa[NR_T];
+#pragma unroll
+    for (int r = 0; r < NR_T; r++) {
+      bool ok = (r0 + r < NR);
+      Aa[r] = ok ? Arow[r][ja] : 0.0;
+      dAa[r] = ok ? dArow[r][ja] : 0.0;
+    }
+    double gx = 0.0, gy = 0.0, gz = 0.0;
+    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    for (int t = 0; t < nt_max; t++) {
+      if (act && t < nt) {
+        int jb;
+        if (same) { int b = a + t + 1; if (b >= m1) b -= m1; jb = s1 + b; }
+        else { int b = lane + t; if (b >= m2) b -= m2; jb = s2 + b; }
+        const double bx = w.ux[jb], by = w.uy[jb], bz = w.uz[jb], Rb = w.R[jb];
+        double c = ax * bx + ay * by + az * bz;
+        bool skip = false;
+        if (skip_rjk) { double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c; skip = rjk2 > rcut2; }
+        if (!skip) {
+          double p[NA_T], dp[NA_T];
+          pp_angular<NA_T>(K, c, p);
+#pragma unroll
+          for (int q = 0; q < NA_T; q++) {
+            double x = fma(K.lam[q], c, 1.0);
+            dp[q] = (x > 0.0) ? xil[q] * p[q] / x : 0.0;
+          }
+          double dRa = 0.0, dRb = 0.0, dc = 0.0;
+#pragma unroll
+          for (int r = 0; r < NR_T; r++) {
+            double Sr = 0.0, Tr = 0.0;
+#pragma unroll
+            for (int q = 0; q < NA_T; q++) { Sr = fma(W[r][q], p[q], Sr); Tr = fma(W[r][q], dp[q], Tr); }
+            double Ab = Arow[r][jb];
+            double dAb = dArow[r][jb];
+            dRa = fma(Sr * dAa[r], Ab, dRa);
+            dRb = fma(Sr * Aa[r], dAb, dRb);
+            dc = fma(Tr * Aa[r], Ab, dc);
+          }
+          const double ca = dc * invRa, cb = dc / Rb;
+          gx += dRa * ax + ca * (bx - c * ax);
+          gy += dRa * ay + ca * (by - c * ay);
+          gz += dRa * az + ca * (bz - c * az);
+          w.fx[jb] += dRb * bx + cb * (ax - c * bx);
+          w.fy[jb] += dRb * by + cb * (ay - c * by);
+          w.fz[jb] += dRb * bz + cb * (az - c * bz);
+        }
+      }
+      __syncwarp();
+    }
+    if (act) { w.fx[ja] += gx; w.fy[ja] += gy; w.fz[ja] += gz; }
+    __syncwarp();
+  }
+}
+
+template <int NR_T, int NA_T>
+__device__ inline void pp_force_entries(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
+{
+  if (S->npair) pp_pair_rows_force(w, cap, lane, S);
+  if (S->nG4) {
+    for (int e1 = 0; e1 < S->n_elem; e1++)
+      for (int e2 = e1; e2 < S->n_elem; e2++)
+        for (int r0 = 0; r0 < S->NR; r0 += NR_T)
+          for (int a0 = 0; a0 < S->NA; a0 += NA_T) pp_g4_block_force<NR_T, NA_T>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
+  }
+}

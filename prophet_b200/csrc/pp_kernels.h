@@ -1,0 +1,97 @@
+// Internal kernel-launcher interface between pp_api.cu and the kernel translation units.
+#pragma once
+#include "pp_common.cuh"
+
+// ---- descriptors / forces -------------------------------------------------------------------------------
+struct PeriodicArgs {
+  const DescSpec* spec;            // device
+  long long n_atoms;               // atoms handled by this launch
+  long long atom_begin;            // first (global) atom of this launch
+  const int* atom_struct;          // [total atoms] structure index
+  const long long* struct_atom0;   // [n_struct+1]
+  const double* FtoA;              // [n_struct][9]   Structure::FtoA = cell^T (Structure.cpp:1186)
+  const int* mxyz;                 // [n_struct][3]   image search box (Structure.cpp:1300-1302)
+  const double* frac;              // [total atoms][3]
+  const int* elem;                 // [total atoms]
+  double* G;                       // [total atoms][NG]
+  int cap;
+  int* overflow;
+};
+
+struct MdArgs {
+  const DescSpec* spec;
+  int nlocal;
+  const double* x;                 // [ntotal][3]
+  const int* elem;                 // [ntotal] element index
+  const long long* neigh_offsets;  // [nlocal+1]
+  const int* neigh;                // flat full list
+  double* G;                       // [nlocal][NG]     (desc)
+  const double* dEdG;              // [nlocal][NG]     (force)
+  double* f;                       // [ntotal][3]      (force, accumulated)
+  int cap;
+  int* overflow;
+};
+
+int ppk_desc_periodic(const DescSpec& hs, PeriodicArgs a, int* cap_io, cudaStream_t st, long long* launches);
+int ppk_neighbors_periodic(const DescSpec& hs, PeriodicArgs a, int s, int natom, int pass, int* counts, const int* offsets,
+                           int* out_j, int* out_t, int cap, cudaStream_t st, long long* launches);
+int ppk_max_cap(const DescSpec& hs, bool force);
+int ppk_md_desc(const DescSpec& hs, MdArgs a, int* cap_io, cudaStream_t st, long long* launches);
+int ppk_md_force(const DescSpec& hs, MdArgs a, int cap, cudaStream_t st, long long* launches);
+
+// ---- per-element MLP --------------------------------------------------------------------------------------
+struct NetDev {
+  int n_layers;                       // weight layers (hidden + output)
+  int sizes[PP_MAX_LAYERS + 1];       // sizes[0] = NG ... sizes[n_layers] = 1
+  int w_off[PP_MAX_LAYERS];           // offset of layer l's [n_out][n_in+1] block in the flat parameter vector
+  int node_off[PP_MAX_LAYERS];        // offset of layer l's nodes in the transfer-id list
+  int P;
+  const double* params;               // device, this element's parameters
+  const int* tf;                      // device, transfer id per node
+  const double* mean;                 // device [NG]
+  const double* scale;                // device [NG]
+};
+
+enum { PP_MLP_FORWARD = 0, PP_MLP_TRAIN = 1, PP_MLP_INPUT_GRAD = 2 };
+
+struct MlpArgs {
+  NetDev net;
+  const double* G;                    // [atoms][NG]
+  const int* rows;                    // [M] atom indices of this element (nullptr = identity)
+  int M;
+  const int* atom_struct;             // [atoms]                    (train)
+  const double* cstruct;              // [n_struct] 2*Err*out_scale (train)
+  double out_scale;
+  double* E_atom;                     // [atoms]  out (forward)
+  double* dEdG;                       // [atoms][NG] out (input grad)
+  double* partial;                    // [n_cta][P_total] out (train); this element's slice starts at p_off
+  int P_total, p_off;
+  const double* tanh_table;           // [1001 + 4000]
+};
+
+// returns the number of CTAs the train launch will use (rows of `partial`)
+int ppk_mlp_max_ctas(void);
+int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
+
+// per-structure energies / errors (Potential.cpp:641-668)
+struct StructArgs {
+  int n_struct;
+  const long long* struct_atom0;
+  const double* E_atom;
+  const double* target;
+  const int* tag;
+  double out_mean, out_scale;
+  double* E_struct;     // [n_struct]
+  double* cstruct;      // [n_struct]
+  double* result_tail;  // [3] sse, vsse, nval
+};
+int ppk_struct_errors(const StructArgs& a, cudaStream_t st, long long* launches);
+int ppk_reduce_partials(const double* partial, int n_cta, int P, double* grad, cudaStream_t st, long long* launches);
+
+// preconditioning column statistics (Structure::mean / variance, Structure.cpp:1443-1476)
+// pass 0: sums[k] = sum G[a][k]; pass 1: sums[k] = sum (G[a][k]-mean[k])^2 ; over atoms in rows[] whose structure is 'train'
+int ppk_column_stats(const double* G, int NG, const int* rows, int M, const int* atom_struct, const int* tag,
+                     const double* mean, int pass, double* partial, int n_cta, double* sums, long long* count,
+                     cudaStream_t st, long long* launches);
+
+void ppk_make_tanh_table(std::vector<double>& table);
