@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""Benchmark of the PROPhet Behler-Parrinello hot path on B200 (see DESIGN.md section "Measurement").
+
+    python bench.py --gpus N --steps K --warmup W            # this repository's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU code on the host cores
+
+Headline metric (BASELINE.json): training structures/sec/epoch on config C2 (10 000 synthetic 64-atom Si
+structures per GPU, 50 descriptors, net 50-40-40-1 tanh).  A "step" is one training epoch = the body of
+Potential::train's loop (Potential.cpp:626-672): per-element MLP forward, per-structure error, backprop to all
+parameters, gradient reduction (+ NCCL allreduce for N > 1).
+  value : descriptors and parameters resident in HBM, device-timed (CUDA events on the library's stream)
+  e2e   : the same epoch through the C-ABI call pp_epoch with pinned HOST buffers: parameters host->device and
+          [gradient, SSE, vSSE, nval] device->host inside the timed region, followed by the host optimizer step
+Inputs (256 MB of FP64 descriptors per GPU) are larger than the 126 MB L2, so no explicit flush is needed.
+"""
+import argparse
+import json
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "training structures/sec/epoch"
+UNIT = "structures/s"
+N_STRUCT_PER_GPU = 10000
+
+
+# ------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, gpu_index=0):
+        self.rows = []
+        self.gpu = gpu_index
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smmax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); smmax.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for k, name in enumerate(names):
+                if len(r) > 4 + k and r[4 + k].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smmax) if smmax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_c2(ctx, capi, synth, rank, n_struct, batch=1000):
+    """Generate this rank's C2 shard (structure ids rank*n_struct ...) and push it through pp_add_structures."""
+    cfg = synth.config_c2(n_struct)
+    t_desc = 0.0
+    for first in range(0, n_struct, batch):
+        cnt = min(batch, n_struct - first)
+        b = synth.make_batch(cfg, rank * n_struct + first, cnt)
+        frac = np.empty_like(b["cart"])
+        n = cfg.natoms
+        for k in range(cnt):   # Structure::Set_Convert + Normalize through the C ABI (host arithmetic)
+            frac[k * n:(k + 1) * n] = capi.cart_to_frac(b["cells"][k], b["cart"][k * n:(k + 1) * n])
+        ctx.add_structures(b["natoms"], b["cells"], frac, np.zeros(cnt * n, dtype=np.int32), b["targets"], b["tags"])
+        t_desc += ctx.phase_ms(0)
+    return cfg, t_desc
+
+
+# ------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    from prophet_b200 import capi, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if rank == 0 and world != 1:
+            print("warning: WORLD_SIZE=%d but --gpus %d" % (world, args.gpus), file=sys.stderr)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (this benchmark has no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        os.environ.setdefault("PP_NCCL_LIB", _torch_nccl_path())
+
+    ctx = capi.Context(local_rank)
+    n_struct = args.structures
+    cfg = synth.config_c2(n_struct)
+    ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+    net = synth.random_network(cfg, 14, 1)
+    ctx.set_network(0, net["sizes"], net["params"], np.zeros(cfg.NG), np.ones(cfg.NG))
+    t0 = time.time()
+    cfg, desc_ms = make_c2(ctx, capi, synth, rank, n_struct)
+    setup_wall = time.time() - t0
+    if world > 1:
+        if rank == 0:
+            uid = torch.tensor(list(capi.Context.comm_unique_id()), dtype=torch.uint8, device="cuda")
+        else:
+            uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        dist.broadcast(uid, 0)
+        ctx.comm_init(world, rank, bytes(uid.cpu().tolist()))
+    ctx.precondition(True)
+
+    P = ctx.n_params
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    x_pin = torch.empty(P, dtype=torch.float64).pin_memory()
+    g_pin = torch.empty(P, dtype=torch.float64).pin_memory()
+    x_pin.copy_(torch.from_numpy(net["params"]))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    launches0 = ctx.kernel_launches
+    # ---- value: device-resident epochs -------------------------------------------------------------------
+    for _ in range(args.warmup):
+        ctx.epoch_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
+    launches_before = ctx.kernel_launches
+    ev0.record(stream)
+    for _ in range(args.steps):
+        ctx.epoch_device()
+    ev1.record(stream)
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1)
+    launches_timed = ctx.kernel_launches - launches_before
+    # per-phase device times of one more (untimed) epoch for the roofline of the dominant kernel
+    fwd_ms, bwd_ms, coll_ms = [], [], []
+    for _ in range(max(3, min(args.steps, 10))):
+        ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
+        fwd_ms.append(ctx.phase_ms(1)); bwd_ms.append(ctx.phase_ms(2)); coll_ms.append(ctx.phase_ms(3))
+    # ---- e2e: host buffers through pp_epoch, host->device params and device->host results every step ---------
+    opt = _host_optimizer(P)
+    for _ in range(args.warmup):
+        ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sse, vsse, nval = ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
+        opt.step(x_pin, g_pin)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+
+    times = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = [float(v) for v in times.cpu()]
+    total_struct = n_struct * world
+    ms_per_step = dev_ms / args.steps
+    value = total_struct / (ms_per_step * 1e-3)
+    e2e_value = total_struct / (e2e_ms * 1e-3 / args.steps)
+
+    if rank == 0:
+        atoms = n_struct * cfg.natoms
+        sizes = [int(v) for v in net["sizes"]]
+        F = 2 * sum(a * b for a, b in zip(sizes[:-1], sizes[1:]))
+        train_flops_atom = 3 * F - 2 * sizes[0] * sizes[1]
+        bwd = float(np.median(bwd_ms))
+        peaks = _fp64_peaks()
+        achieved = train_flops_atom * atoms / (bwd * 1e-3) / 1e12
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C2: %d x 64-atom Si per GPU, 50 descriptors (10 G2 + 40 G4), net 50-40-40-1 tanh, one epoch"
+                                   % n_struct, "structures_total": total_struct, "parallelism": "dp%d" % world,
+                       "l2": "inputs (%.0f MB FP64 descriptors per GPU) larger than L2, no flush" % (atoms * cfg.NG * 8 / 1e6)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * P, "d2h_bytes_per_step": 8 * (P + 3),
+                    "includes": "pp_epoch with pinned host buffers + host Rprop step"},
+            "gpu_launches": int(launches_timed),
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "mlp_kernel<TRAIN> (FP64 DMMA: forward recompute + backprop + weight gradients)",
+                         "achieved": achieved, "peak": peaks["fp64_dmma_tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["fp64_dmma_tflops"],
+                         "peak_source": peaks["source"], "algorithmic_flops_per_atom": train_flops_atom, "atoms_per_launch": atoms,
+                         "kernel_ms": bwd, "traffic": None,
+                         "hbm_view": {"algorithmic_bytes_per_atom": 8 * cfg.NG, "achieved_gbs": 8 * cfg.NG * atoms / (bwd * 1e-3) / 1e9,
+                                      "peak_gbs": _measured_hbm()}},
+            "phases_ms": {"forward": float(np.median(fwd_ms)), "backward_reduce": bwd, "collective": float(np.median(coll_ms))},
+            "setup": {"descriptor_kernel_ms_total": desc_ms, "structures_per_s_kernel": n_struct / (desc_ms * 1e-3),
+                      "wall_s_including_generation": setup_wall},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = reference_epoch_rate(cores=1, structures_per_core=args.cpu_sample, iters=6)
+        print(json.dumps(out))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+class _host_optimizer:
+    """Host-side optimizer step for the e2e loop.  Uses the C++ host library's Rprop when it is built."""
+
+    def __init__(self, P):
+        self.impl = None
+        try:
+            from prophet_b200 import hostapi
+            self.impl = hostapi.Rprop(P)
+        except Exception:
+            self.impl = None
+
+    def step(self, x_pin, g_pin):
+        if self.impl is not None:
+            self.impl.step_ptr(x_pin.data_ptr(), g_pin.data_ptr())
+
+
+def _torch_nccl_path():
+    import glob
+    import torch
+    base = os.path.dirname(os.path.dirname(torch.__file__))
+    for pat in ("nvidia/nccl/lib/libnccl.so.2", "torch/lib/libnccl.so.2"):
+        hits = glob.glob(os.path.join(base, pat))
+        if hits:
+            return hits[0]
+    return "libnccl.so.2"
+
+
+def _measured_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)["hbm_gbs"]
+    except Exception:
+        return 6650.0
+
+
+def _fp64_peaks():
+    """FP64 peaks are not in MEASURED_PEAKS.json (HBM and bf16 only); tools/peaks_microbench.cu measured them on this
+    pool's B200 (profiles/r01_peaks_microbench.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_peaks_microbench.json")) as f:
+            d = json.load(f)
+        return {"fp64_dmma_tflops": d["fp64_dmma_m8n8k4_tflops"], "fp64_fma_tflops": d["fp64_fma_tflops"],
+                "source": "measured: tools/peaks_microbench.cu on B200 (profiles/r01_peaks_microbench.json)"}
+    except Exception:
+        return {"fp64_dmma_tflops": 37.0, "fp64_fma_tflops": 33.5, "source": "fallback constants"}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# The reference's own CPU implementation (oracle/_ref/PROPhet = unmodified reference CLI, built by oracle/build_ref.sh)
+def _write_ref_case(cwd, synth, first, count, iters):
+    cfg = synth.config_c2(count)
+    structs = [synth.make_structure(cfg, first + s) for s in range(count)]
+    synth.write_prophet_xml(os.path.join(cwd, "PROPhet.xml"), structs)
+    synth.write_input_file(os.path.join(cwd, "input_file"), cfg, niterations=iters, extra=("seed = 1",))
+
+
+def _run_ref_timed(cwd, iters):
+    """Run the reference CLI with line-buffered stdout and time the iteration lines (Nprint = 1)."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "PROPhet")
+    cmd = ["stdbuf", "-oL", exe, "-in", "input_file", "-train"] if shutil.which("stdbuf") else [exe, "-in", "input_file", "-train"]
+    p = subprocess.Popen(cmd, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    stamps = []
+    it_line = re.compile(r"^\d+\s+[-+0-9.eE]+\s+[-+0-9.eE]+(\s+[-+0-9.eE]+)?\s*$")   # Optimizer.cpp:980-988
+    for line in p.stdout:
+        if it_line.match(line):
+            stamps.append(time.perf_counter())
+    p.wait()
+    return stamps
+
+
+def reference_epoch_rate(cores, structures_per_core, iters, steps=None, warmup=0):
+    """structures/s/epoch of the reference: `cores` independent serial processes on disjoint shards (the reference's
+    own round-robin split, Setup.cpp:582, without the microsecond-scale Reduce/Bcast; no MPI in this image)."""
+    from prophet_b200 import synth
+    exe = os.path.join(ROOT, "oracle", "_ref", "PROPhet")
+    if not os.path.exists(exe):
+        return {"value": None, "unit": UNIT, "cores": cores, "kind": "reference", "sample": "oracle/_ref/PROPhet missing"}
+    dirs = []
+    results = [None] * cores
+    try:
+        for c in range(cores):
+            d = tempfile.mkdtemp(prefix="ppref_%d_" % c)
+            dirs.append(d)
+            _write_ref_case(d, synth, c * structures_per_core, structures_per_core, iters)
+
+        def work(c):
+            results[c] = _run_ref_timed(dirs[c], iters)
+
+        threads = [threading.Thread(target=work, args=(c,)) for c in range(cores)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+    finally:
+        for d in dirs:
+            shutil.rmtree(d, ignore_errors=True)
+    # per-process epoch time from the gaps between iteration lines (skip `warmup` gaps)
+    rates, epoch_ms = [], []
+    for st in results:
+        if not st or len(st) < 2 + warmup:
+            continue
+        gaps = np.diff(st)[warmup:]
+        if steps:
+            gaps = gaps[:steps]
+        dt = float(np.mean(gaps))
+        epoch_ms.append(dt * 1e3)
+        rates.append(structures_per_core / dt)
+    value = float(np.sum(rates)) if rates else None
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": "%d processes x %d C2 structures, %d epochs each, unmodified reference CLI (oracle/_ref/PROPhet -train), "
+                      "epoch time from iteration-line timestamps" % (cores, structures_per_core, iters),
+            "epoch_ms_per_process": float(np.mean(epoch_ms)) if epoch_ms else None}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_core = args.cpu_sample
+    iters = args.warmup + args.steps + 1
+    r = reference_epoch_rate(cores, per_core, iters, steps=args.steps, warmup=args.warmup)
+    ms = r.get("epoch_ms_per_process")
+    out = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic",
+           "config": {"workload": "C2: 64-atom Si, 50 descriptors (10 G2 + 40 G4), net 50-40-40-1 tanh, one epoch; "
+                                  "bounded sample of %d structures per host core" % per_core, "parallelism": "cpu x%d" % cores},
+           "cpu_baseline": r,
+           "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--structures", type=int, default=N_STRUCT_PER_GPU, help="structures per GPU (C2 = 10000)")
+    ap.add_argument("--cpu-sample", type=int, default=24, help="structures per host core for the CPU arm")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -55,6 +55,8 @@ struct NetHost {
   std::vector<double> params, mean, scale;
   DevBuf<double> d_mean, d_scale;
   DevBuf<int> d_tf;
+  DevBuf<unsigned char> d_dw_tiles;
+  int tile_atoms = 0;
   NetDev dev;
 };
 
@@ -92,6 +94,10 @@ struct pp_context {
   DevBuf<double> d_partial, d_result, d_stat_partial, d_stat_sums;
   DevBuf<long long> d_count;
   std::vector<double> h_result;
+  // fused single-pass epoch: tiles of whole structures
+  bool tiles_dirty = true, fused_ok = false;
+  int n_fused_tiles = 0;
+  DevBuf<int> d_tile_struct0;
 
   // ---- MD ----
   std::vector<int> type_to_elem;
@@ -159,8 +165,9 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_md_elem.release(); c->d_neigh.release(); c->d_neigh_off.release();
   for (int e = 0; e < PP_MAX_ELEM; e++) {
     c->d_rows[e].release(); c->d_md_rows[e].release();
-    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release();
+    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release();
   }
+  c->d_tile_struct0.release();
   if (c->d_spec) cudaFree(c->d_spec);
   for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -228,6 +235,53 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
     S.g4_rad[r] = ri; S.g4_ang[r] = ai;
   }
   if (S.NR == 0) S.NR = 1;   // keeps shared-memory strides non-degenerate when there are no G4 rows
+  // Order the angular keys so that powers of two of the same lambda form chains x -> x^2 -> x^4 ... and build the
+  // evaluation program (pp_desc.cuh, AngKeys): a chain key costs only its squarings relative to the previous key.
+  {
+    const int NA = S.NA;
+    std::vector<int> order(NA);
+    for (int k = 0; k < NA; k++) order[k] = k;
+    auto is_pow2 = [&](int k) { int e = S.ang_xi_int[k]; return e >= 1 && (e & (e - 1)) == 0 && e <= 1024; };
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
+      bool px = is_pow2(x), py = is_pow2(y);
+      if (px != py) return px;
+      if (S.ang_lam[x] != S.ang_lam[y]) return S.ang_lam[x] > S.ang_lam[y];
+      return S.ang_xi[x] < S.ang_xi[y];
+    });
+    DescSpec T = S;
+    std::vector<int> newpos(NA);
+    for (int k = 0; k < NA; k++) {
+      int o = order[k];
+      newpos[o] = k;
+      S.ang_xi[k] = T.ang_xi[o]; S.ang_lam[k] = T.ang_lam[o]; S.ang_pref[k] = T.ang_pref[o]; S.ang_xi_int[k] = T.ang_xi_int[o];
+    }
+    for (int r = 0; r < nG4; r++) S.g4_ang[r] = newpos[T.g4_ang[r]];
+    auto ilog2 = [](int v) { int l = 0; while (v > 1) { v >>= 1; l++; } return l; };
+    for (int k = 0; k < NA; k++) {
+      int e = S.ang_xi_int[k];
+      int prog;
+      if (e < 0) prog = 3;
+      else if (!(e >= 1 && (e & (e - 1)) == 0 && e <= 1024)) prog = 2;
+      else {
+        bool fresh = (k % 4 == 0) || (S.ang_prog[k - 1] & 3) != 1 || S.ang_lam[k - 1] != S.ang_lam[k];
+        int ns = fresh ? ilog2(e) : ilog2(e / S.ang_xi_int[k - 1]);
+        if (ns > 5) prog = 2;
+        else prog = 1 | (fresh ? 4 : 0) | (ns << 3);
+      }
+      S.ang_prog[k] = prog;
+    }
+  }
+  // squared-distance thresholds equivalent to the reference's tests on d = sqrt(d2) (Structure.cpp:1337)
+  {
+    auto thr = [](double r) {
+      double y = r * r;
+      while (sqrt(y) > r) y = nextafter(y, 0.0);
+      while (sqrt(nextafter(y, INFINITY)) <= r) y = nextafter(y, INFINITY);
+      return y;
+    };
+    S.scan_d2_hi = thr(Rcut);
+    S.scan_d2_lo = thr(0.01);
+  }
   int index = 0;
   for (int i = 0; i < n_elem; i++)
     for (int j = i; j < n_elem; j++) {
@@ -296,6 +350,16 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
   PP_CUDA(cudaMemcpy(n.d_scale.p, n.scale.data(), sizes[0] * sizeof(double), cudaMemcpyHostToDevice));
   PP_CUDA(cudaMemcpy(n.d_tf.p, n.tf.data(), n.n_nodes * sizeof(int), cudaMemcpyHostToDevice));
   n.dev.mean = n.d_mean.p; n.dev.scale = n.d_scale.p; n.dev.tf = n.d_tf.p;
+  {
+    n.tile_atoms = ppk_mlp_tile_atoms(n.dev);
+    PP_REQUIRE(n.tile_atoms > 0, "pp_set_network: network too large for shared memory");
+    int nt = ppk_mlp_num_dw_tiles(n.dev, nullptr);
+    std::vector<unsigned char> tiles((size_t)std::max(nt, 1) * ppk_mlp_dw_tile_bytes());
+    ppk_mlp_num_dw_tiles(n.dev, tiles.data());
+    if (n.d_dw_tiles.ensure(tiles.size(), 0, c->stream)) return 1;
+    PP_CUDA(cudaMemcpy(n.d_dw_tiles.p, tiles.data(), tiles.size(), cudaMemcpyHostToDevice));
+  }
+  c->tiles_dirty = true;
   n.set = true;
   return rebuild_param_layout(c);
 }
@@ -462,6 +526,7 @@ extern "C" int pp_add_structures(pp_context* c, int n_struct, const int* natoms,
   PP_CUDA(cudaMemcpyAsync(c->d_atom_struct.p + a0, c->h_atom_struct.data() + a0, add_atoms * sizeof(int), cudaMemcpyHostToDevice, st));
   c->n_struct = ns;
   c->n_atoms = na;
+  c->tiles_dirty = true;
   // per-element row lists (structure-major)
   for (int e = 0; e < S.n_elem; e++) {
     size_t before = c->h_rows[e].size();
@@ -487,6 +552,7 @@ extern "C" int pp_clear_structures(pp_context* c)
   PP_REQUIRE(c, "null context");
   c->n_struct = 0;
   c->n_atoms = 0;
+  c->tiles_dirty = true;
   c->h_struct_atom0.assign(1, 0);
   c->h_FtoA.clear(); c->h_target.clear(); c->h_mxyz.clear(); c->h_tag.clear(); c->h_elem.clear();
   c->h_atom_struct.clear(); c->h_frac.clear();
@@ -631,7 +697,43 @@ static MlpArgs mlp_args_train(pp_context* c, int e)
   a.P_total = c->P_total;
   a.p_off = c->nets[e].p_off;
   a.tanh_table = c->d_tanh_table.p;
+  a.dw_tiles = c->nets[e].d_dw_tiles.p;
+  a.n_tiles = c->n_fused_tiles;
+  a.tile_struct0 = c->d_tile_struct0.p;
+  a.struct_atom0 = c->d_struct_atom0.p;
+  a.target = c->d_target.p;
+  a.tag = c->d_tag.p;
+  a.out_mean = c->out_mean;
+  a.E_struct = c->d_E_struct.p;
   return a;
+}
+
+// Single-element systems whose structures each fit one MLP tile take the fused single-pass epoch: tiles are
+// runs of whole consecutive structures, packed greedily up to the tile size.
+static int prepare_fused_tiles(pp_context* c)
+{
+  if (!c->tiles_dirty) return 0;
+  c->tiles_dirty = false;
+  c->fused_ok = false;
+  c->n_fused_tiles = 0;
+  if (c->spec.n_elem != 1 || !c->nets[0].set || c->n_struct == 0) return 0;
+  const int TM = c->nets[0].tile_atoms;
+  std::vector<int> t0;
+  t0.push_back(0);
+  int used = 0;
+  for (int s = 0; s < c->n_struct; s++) {
+    const int n = (int)(c->h_struct_atom0[s + 1] - c->h_struct_atom0[s]);
+    if (n > TM) return 0;
+    if (used + n > TM) { t0.push_back(s); used = 0; }
+    used += n;
+  }
+  t0.push_back(c->n_struct);
+  if (c->d_tile_struct0.ensure(t0.size(), 0, c->stream)) return 1;
+  PP_CUDA(cudaMemcpyAsync(c->d_tile_struct0.p, t0.data(), t0.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  c->n_fused_tiles = (int)t0.size() - 1;
+  c->fused_ok = true;
+  return 0;
 }
 
 static int forward_all(pp_context* c)
@@ -657,7 +759,7 @@ static int forward_all(pp_context* c)
 static int epoch_buffers(pp_context* c)
 {
   const int n_cta = ppk_mlp_max_ctas();
-  if (c->d_partial.ensure((size_t)n_cta * std::max(c->P_total, 1), 0, c->stream)) return 1;
+  if (c->d_partial.ensure((size_t)n_cta * (c->P_total + 3), 0, c->stream)) return 1;
   if (c->d_result.ensure((size_t)c->P_total + 3, 0, c->stream)) return 1;
   return 0;
 }
@@ -668,14 +770,23 @@ extern "C" int pp_epoch_device(pp_context* c)
   PP_REQUIRE(c->n_struct > 0, "pp_epoch: no structures");
   PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
+  if (prepare_fused_tiles(c)) return 1;
   if (tick(c, 0)) return 1;
-  if (forward_all(c)) return 1;
-  if (tick(c, 1)) return 1;
-  for (int e = 0; e < c->spec.n_elem; e++) {
-    MlpArgs a = mlp_args_train(c, e);
-    if (ppk_mlp_launch(PP_MLP_TRAIN, a, c->stream, &c->launches)) return 1;
+  if (c->fused_ok) {
+    // one pass: forward, per-structure error and backward in the same kernel; loss terms ride in the partials' tail
+    if (tick(c, 1)) return 1;
+    MlpArgs a = mlp_args_train(c, 0);
+    if (ppk_mlp_launch(PP_MLP_FUSED, a, c->stream, &c->launches)) return 1;
+    if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_max_ctas(), c->P_total + 3, c->P_total + 3, c->d_result.p, c->stream, &c->launches)) return 1;
+  } else {
+    if (forward_all(c)) return 1;
+    if (tick(c, 1)) return 1;
+    for (int e = 0; e < c->spec.n_elem; e++) {
+      MlpArgs a = mlp_args_train(c, e);
+      if (ppk_mlp_launch(PP_MLP_TRAIN, a, c->stream, &c->launches)) return 1;
+    }
+    if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_max_ctas(), c->P_total + 3, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
   }
-  if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_max_ctas(), c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
   if (tick(c, 2)) return 1;
   if (c->comm.allreduce_device(c->d_result.p, c->P_total + 3, c->stream)) return 1;
   if (tick(c, 3)) return 1;
@@ -810,6 +921,7 @@ static int md_run(pp_context* c)
     m.E_atom = c->d_eatom.p;
     m.dEdG = c->d_dEdG.p;
     m.tanh_table = c->d_tanh_table.p;
+    m.dw_tiles = c->nets[e].d_dw_tiles.p;
     if (ppk_mlp_launch(PP_MLP_INPUT_GRAD, m, st, &c->launches)) return 1;
   }
   if (tick(c, 2)) return 1;

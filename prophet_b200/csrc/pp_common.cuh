@@ -54,6 +54,8 @@ struct DescSpec {
   int rad_fc[PP_MAX_RAD];
   double ang_xi[PP_MAX_ANG], ang_lam[PP_MAX_ANG], ang_pref[PP_MAX_ANG];   // pref = 2^(1-xi)
   int ang_xi_int[PP_MAX_ANG];     // xi as integer exponent, or -1 when xi is not an integer (binomial series)
+  int ang_prog[PP_MAX_ANG];       // evaluation program word, see pp_desc.cuh (AngKeys)
+  double scan_d2_hi, scan_d2_lo;  // squared-distance thresholds equivalent to d <= Rcut and d > 0.01 on d = sqrt(d2)
   int g4_rad[PP_MAX_G4_ROWS], g4_ang[PP_MAX_G4_ROWS];
   // slot of the first triplet row for element pair (e1,e2): Structure::init_type_G_map (Structure.cpp:1500-1510)
   int trip_base[PP_MAX_ELEM][PP_MAX_ELEM];

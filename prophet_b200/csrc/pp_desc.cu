@@ -28,7 +28,7 @@ desc_periodic_kernel(PeriodicArgs a)
 #pragma unroll
   for (int k = 0; k < 9; k++) Fm[k] = F[k];
   const int* m = a.mxyz + 3 * (size_t)s;
-  int n = pp_scan_periodic(w, a.cap, lane, a.frac + 3 * a0, a.elem + a0, natom, i, Fm, m[0], m[1], m[2], S->Rcut, nullptr);
+  int n = pp_scan_periodic(w, a.cap, lane, a.frac + 3 * a0, a.elem + a0, natom, i, Fm, m[0], m[1], m[2], S, nullptr);
   if (n > a.cap) {
     if (lane == 0) atomicMax(a.overflow, n);
     return;
@@ -59,7 +59,7 @@ neighbors_periodic_kernel(PeriodicArgs a, int s, int pass, int* counts, const in
   for (int k = 0; k < 9; k++) Fm[k] = a.FtoA[9 * (size_t)s + k];
   const int* m = a.mxyz + 3 * (size_t)s;
   int* timg = w.idx;   // unused by the scan itself: receives the image index
-  int n = pp_scan_periodic(w, a.cap, lane, a.frac + 3 * a0, a.elem + a0, natom, i, Fm, m[0], m[1], m[2], S->Rcut, timg);
+  int n = pp_scan_periodic(w, a.cap, lane, a.frac + 3 * a0, a.elem + a0, natom, i, Fm, m[0], m[1], m[2], S, timg);
   if (pass == 0) {
     if (lane == 0) counts[i] = n;
     if (n > a.cap && lane == 0) atomicMax(a.overflow, n);

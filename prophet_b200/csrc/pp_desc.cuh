@@ -72,45 +72,51 @@ __device__ inline void pp_warp_views(WarpNbr& w, unsigned char* base, int cap, i
 // nothing beyond cap is stored).
 __device__ inline int pp_scan_periodic(WarpNbr& w, int cap, int lane, const double* __restrict__ frac,
                                        const int* __restrict__ elem, int natom, int i, const double* F,
-                                       int mx, int my, int mz, double Rcut, int* timg)
+                                       int mx, int my, int mz, const DescSpec* __restrict__ S, int* timg)
 {
-  const int ny = 2 * my + 1, nz = 2 * mz + 1;
-  const int nT = (2 * mx + 1) * ny * nz;
-  const long long ncand = (long long)natom * nT;
+  const int ny = 2 * my + 1, nz = 2 * mz + 1, nyz = ny * nz;
+  const int nT = (2 * mx + 1) * nyz;
   const double ix = frac[3 * i], iy = frac[3 * i + 1], iz = frac[3 * i + 2];
+  // d2 thresholds equivalent to the reference's tests on d = sqrt(d2) (correctly rounded sqrt is monotonic):
+  //   d <= Rcut  <=>  d2 <= d2_hi ;  d > 0.01  <=>  d2 > d2_lo      (computed on the host, pp_set_descriptors)
+  const double d2_hi = S->scan_d2_hi, d2_lo = S->scan_d2_lo;
+  const float inv_nyz = 1.0f / (float)nyz, inv_nz = 1.0f / (float)nz;
+  // candidate c = j*nT + t, visited 32 at a time in order; (j,t) advanced incrementally (no integer division)
+  int j = lane / nT, t = lane - j * nT;
+  const int dj = 32 / nT, dt = 32 - dj * nT;
   int count = 0;
-  for (long long c0 = 0; c0 < ncand; c0 += 32) {
-    long long c = c0 + lane;
+  for (;;) {
     bool keep = false;
-    double dx = 0, dy = 0, dz = 0, d = 0;
-    int j = 0, t = 0;
-    if (c < ncand) {
-      j = (int)(c / nT);
-      t = (int)(c - (long long)j * nT);
-      int tx = t / (ny * nz) - mx;
-      int rem = t % (ny * nz);
-      int ty = rem / nz - my;
-      int tz = rem % nz - mz;
-      double fx = __dsub_rn(__dadd_rn(frac[3 * j], (double)tx), ix);
-      double fy = __dsub_rn(__dadd_rn(frac[3 * j + 1], (double)ty), iy);
-      double fz = __dsub_rn(__dadd_rn(frac[3 * j + 2], (double)tz), iz);
+    double dx = 0, dy = 0, dz = 0, d2 = 0;
+    if (j < natom) {
+      const int tx = (int)(((float)t + 0.5f) * inv_nyz);
+      const int rem = t - tx * nyz;
+      const int ty = (int)(((float)rem + 0.5f) * inv_nz);
+      const int tz = rem - ty * nz;
+      const double fx = __dsub_rn(__dadd_rn(frac[3 * j], (double)(tx - mx)), ix);
+      const double fy = __dsub_rn(__dadd_rn(frac[3 * j + 1], (double)(ty - my)), iy);
+      const double fz = __dsub_rn(__dadd_rn(frac[3 * j + 2], (double)(tz - mz)), iz);
       dx = __dadd_rn(__dadd_rn(__dmul_rn(F[0], fx), __dmul_rn(F[1], fy)), __dmul_rn(F[2], fz));
       dy = __dadd_rn(__dadd_rn(__dmul_rn(F[3], fx), __dmul_rn(F[4], fy)), __dmul_rn(F[5], fz));
       dz = __dadd_rn(__dadd_rn(__dmul_rn(F[6], fx), __dmul_rn(F[7], fy)), __dmul_rn(F[8], fz));
-      d = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
-      keep = (d > 0.01) && (d <= Rcut);
+      d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+      keep = (d2 > d2_lo) && (d2 <= d2_hi);
     }
-    unsigned m = __ballot_sync(0xffffffffu, keep);
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
     if (keep) {
-      int pos = count + __popc(m & ((1u << lane) - 1u));
+      const int pos = count + __popc(m & ((1u << lane) - 1u));
       if (pos < cap) {
-        w.sx[pos] = dx; w.sy[pos] = dy; w.sz[pos] = dz; w.sR[pos] = d;
+        w.sx[pos] = dx; w.sy[pos] = dy; w.sz[pos] = dz; w.sR[pos] = __dsqrt_rn(d2);
         w.selem[pos] = elem[j];
         w.sidx[pos] = j;
         if (timg) timg[pos] = t;
       }
     }
     count += __popc(m);
+    // advance by 32 candidates
+    j += dj; t += dt;
+    if (t >= nT) { t -= nT; j++; }
+    if (__shfl_sync(0xffffffffu, j, 0) >= natom) break;   // lane 0 holds the smallest candidate: warp-uniform exit
   }
   return count;
 }
@@ -230,11 +236,14 @@ __device__ inline double pp_series_pow(double th, double xi)
 }
 
 // Angular keys of one grid chunk, hoisted into registers once per block.
+// prog[a] (from DescSpec::ang_prog): bits 0-1 mode (0 padding, 1 power-of-two chain, 2 general integer, 3 series),
+// bit 2 "fresh" (start from x = 1 + lam c instead of the previous key's power), bits 3-5 number of squarings.
 template <int NA_T>
 struct AngKeys {
   double lam[NA_T];
   double xi[NA_T];
-  int xe[NA_T];      // integer exponent; -1 = non-integer xi (series); -2 = padding (value 0)
+  int xe[NA_T];
+  int prog[NA_T];
 };
 
 template <int NA_T>
@@ -246,21 +255,56 @@ __device__ __forceinline__ void pp_load_ang(const DescSpec* __restrict__ S, int 
     bool ok = ga < S->NA;
     K.lam[a] = ok ? S->ang_lam[ga] : 0.0;
     K.xi[a] = ok ? S->ang_xi[ga] : 0.0;
-    K.xe[a] = ok ? S->ang_xi_int[ga] : -2;
+    K.xe[a] = ok ? S->ang_xi_int[ga] : 0;
+    int pr = ok ? S->ang_prog[ga] : 0;
+    if (ok && a == 0) pr |= 4;            // a chunk always starts a fresh chain
+    K.prog[a] = pr;
   }
 }
 
-template <int NA_T>
-__device__ __forceinline__ void pp_angular(const AngKeys<NA_T>& K, double c, double (&p)[NA_T])
+// p[a] = (1 + lam_a c)^xi_a (0 where 1 + lam c <= 0); optionally dp[a] = d p[a] / dc = xi lam p / (1 + lam c).
+template <int NA_T, bool DERIV>
+__device__ __forceinline__ void pp_angular(const AngKeys<NA_T>& K, double c, double (&p)[NA_T], double (&dp)[NA_T])
 {
+  double run = 0.0, inv = 0.0;
 #pragma unroll
   for (int a = 0; a < NA_T; a++) {
-    double x = fma(K.lam[a], c, 1.0);
-    int xe = K.xe[a];
-    double v = 0.0;
-    if (xe >= 0) v = pp_ipow(x, xe);
-    else if (xe == -1 && x > 0.0) v = pp_series_pow(K.lam[a] * c, K.xi[a]);
-    p[a] = (x > 0.0) ? v : 0.0;
+    const int pr = K.prog[a];
+    const int mode = pr & 3;
+    double v = 0.0, d = 0.0;
+    if (mode == 1) {
+      if (pr & 4) {
+        run = fma(K.lam[a], c, 1.0);
+        run = run > 0.0 ? run : 0.0;
+        if (DERIV) inv = run > 0.0 ? 1.0 / run : 0.0;
+        const int xe = K.xe[a];
+        // first key of a chain: xi = 2^ns squarings from x
+        const int ns = (pr >> 3) & 7;
+        if (ns > 0) run *= run;
+        if (ns > 1) run *= run;
+        if (ns > 2) run *= run;
+        if (ns > 3) run *= run;
+        if (ns > 4) run *= run;
+        (void)xe;
+      } else {
+        const int ns = (pr >> 3) & 7;
+        if (ns > 0) run *= run;
+        if (ns > 1) run *= run;
+        if (ns > 2) run *= run;
+        if (ns > 3) run *= run;
+        if (ns > 4) run *= run;
+      }
+      v = run;
+      if (DERIV) d = K.xi[a] * K.lam[a] * v * inv;
+    } else if (mode >= 2) {
+      const double x = fma(K.lam[a], c, 1.0);
+      if (x > 0.0) {
+        v = (mode == 2) ? pp_ipow(x, K.xe[a]) : pp_series_pow(K.lam[a] * c, K.xi[a]);
+        if (DERIV) d = K.xi[a] * K.lam[a] * v / x;
+      }
+    }
+    p[a] = v;
+    if (DERIV) dp[a] = d;
   }
 }
 
@@ -330,7 +374,7 @@ __device__ inline void pp_g4_block_desc(WarpNbr& w, int cap, int lane, const Des
         if (rjk2 > rcut2) continue;
       }
       double p[NA_T];
-      pp_angular<NA_T>(K, c, p);
+      pp_angular<NA_T, false>(K, c, p, p);
 #pragma unroll
       for (int r = 0; r < NR_T; r++) {
         double tr = Aa[r] * Arow[r][jb];
@@ -431,9 +475,6 @@ __device__ inline void pp_g4_block_force(WarpNbr& w, int cap, int lane, const De
     for (int q = 0; q < NA_T; q++) W[r][q] = w.cell[r * NA_T + q];
   AngKeys<NA_T> K;
   pp_load_ang<NA_T>(S, a0, K);
-  double xil[NA_T];   // xi*lam per angular key
-#pragma unroll
-  for (int q = 0; q < NA_T; q++) xil[q] = K.xi[q] * K.lam[q];
   const int NR = S->NR;
   const double *Arow[NR_T], *dArow[NR_T];
 #pragma unroll
@@ -472,12 +513,7 @@ __device__ inline void pp_g4_block_force(WarpNbr& w, int cap, int lane, const De
         if (skip_rjk) { double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c; skip = rjk2 > rcut2; }
         if (!skip) {
           double p[NA_T], dp[NA_T];
-          pp_angular<NA_T>(K, c, p);
-#pragma unroll
-          for (int q = 0; q < NA_T; q++) {
-            double x = fma(K.lam[q], c, 1.0);
-            dp[q] = (x > 0.0) ? xil[q] * p[q] / x : 0.0;
-          }
+          pp_angular<NA_T, true>(K, c, p, dp);
           double dRa = 0.0, dRb = 0.0, dc = 0.0;
 #pragma unroll
           for (int r = 0; r < NR_T; r++) {

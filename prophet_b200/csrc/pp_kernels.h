@@ -52,7 +52,7 @@ struct NetDev {
   const double* scale;                // device [NG]
 };
 
-enum { PP_MLP_FORWARD = 0, PP_MLP_TRAIN = 1, PP_MLP_INPUT_GRAD = 2 };
+enum { PP_MLP_FORWARD = 0, PP_MLP_TRAIN = 1, PP_MLP_INPUT_GRAD = 2, PP_MLP_FUSED = 3 };
 
 struct MlpArgs {
   NetDev net;
@@ -64,13 +64,27 @@ struct MlpArgs {
   double out_scale;
   double* E_atom;                     // [atoms]  out (forward)
   double* dEdG;                       // [atoms][NG] out (input grad)
-  double* partial;                    // [n_cta][P_total] out (train); this element's slice starts at p_off
+  double* partial;                    // [n_cta][P_total+3] out (train); this element's slice starts at p_off;
+                                      //   fused mode also fills the 3 tail columns (sse, vsse, nval)
   int P_total, p_off;
   const double* tanh_table;           // [1001 + 4000]
+  const void* dw_tiles;               // device table of weight-gradient tiles (ppk_mlp_num_dw_tiles)
+  // fused single-pass epoch (single-element systems, tiles made of whole structures)
+  int n_tiles;
+  const int* tile_struct0;            // [n_tiles+1] first structure of each tile
+  const long long* struct_atom0;      // [n_struct+1]
+  const double* target;               // [n_struct]
+  const int* tag;                     // [n_struct]
+  double out_mean;
+  double* E_struct;                   // [n_struct] out
 };
 
 // returns the number of CTAs the train launch will use (rows of `partial`)
 int ppk_mlp_max_ctas(void);
+// atoms per tile the kernel will use for this net (0 = does not fit), and its weight-gradient tile table
+int ppk_mlp_tile_atoms(const NetDev& net);
+int ppk_mlp_num_dw_tiles(const NetDev& net, void* host_tiles_out);
+int ppk_mlp_dw_tile_bytes(void);
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
 
 // per-structure energies / errors (Potential.cpp:641-668)
@@ -86,7 +100,7 @@ struct StructArgs {
   double* result_tail;  // [3] sse, vsse, nval
 };
 int ppk_struct_errors(const StructArgs& a, cudaStream_t st, long long* launches);
-int ppk_reduce_partials(const double* partial, int n_cta, int P, double* grad, cudaStream_t st, long long* launches);
+int ppk_reduce_partials(const double* partial, int n_cta, int stride, int ncols, double* out, cudaStream_t st, long long* launches);
 
 // preconditioning column statistics (Structure::mean / variance, Structure.cpp:1443-1476)
 // pass 0: sums[k] = sum G[a][k]; pass 1: sums[k] = sum (G[a][k]-mean[k])^2 ; over atoms in rows[] whose structure is 'train'

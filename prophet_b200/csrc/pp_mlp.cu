@@ -20,27 +20,35 @@
 #include "pp_kernels.h"
 #include <cmath>
 
-#define MLP_WARPS 8
+#define MLP_WARPS 16
 #define MLP_THREADS (MLP_WARPS * 32)
-#define MLP_MAX_NT 16        // n-tiles (8 wide) per layer: layer width <= 128
-#define MLP_MAX_OWN 32       // dW tiles owned by one warp
-// the kernel is instantiated for NT in {8,16} and OWN in {12,32} (register budget)
+#define MLP_MAX_WIDTH 128    // widest hidden layer supported (16 n-tiles, 8 per warp of a pair)
 
+// Shared-memory plan of one CTA (all offsets in doubles unless stated).
 struct MlpPlan {
   int TM, L;
   int n[PP_MAX_LAYERS + 1];
-  int kpitch[PP_MAX_LAYERS];          // Hs_l / Ws_l pitch (doubles), l = 0..L-1
-  int dpitch[PP_MAX_LAYERS + 1];      // Ds_l pitch, l = 1..L-1
+  int kpitch[PP_MAX_LAYERS];          // pitch of layer l's input buffer (l = 0: raw descriptor tiles X) and of Ws_l
+  int dpitch[PP_MAX_LAYERS + 1];      // pitch of Ds_l (T' then delta), l = 1..L-1
   int ws_off[PP_MAX_LAYERS], hs_off[PP_MAX_LAYERS], ds_off[PP_MAX_LAYERS + 1];
-  int cvec_off, mean_off, scale_off, tf_off_bytes;
-  int tile_prefix[PP_MAX_LAYERS + 1]; // dW tiles of hidden weight layers l = 0..L-2
-  int n_tiles_per_cta_hint;
+  int x_off[2];                       // double-buffered raw descriptor tiles
+  int cvec_off, erow_off, mu_off, is_off, red_off;
+  int tf_off_bytes, desc_off_bytes;
+  int n_dw_tiles;
   size_t smem_bytes;
+};
+
+// one weight-gradient tile: dW_l[8 mi .. +8][8 ni .. +8] += delta_{l+1}^T [H_l, 1]
+struct DwTile {
+  int a_off;      // delta_{l+1} base + 8*mi          (doubles)
+  int b_off;      // H_l base + 8*ni  (layer 0: column offset inside an X buffer)
+  int dp, kp;     // pitches
+  int layer, mi, ni, pad;
 };
 
 __host__ __device__ static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-static bool make_plan(const NetDev& net, int TM, MlpPlan& p)
+static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>* tiles)
 {
   p.TM = TM;
   p.L = net.n_layers;
@@ -52,27 +60,45 @@ static bool make_plan(const NetDev& net, int TM, MlpPlan& p)
     int rows = (l == p.L - 1) ? 1 : round_up(p.n[l + 1], 8);
     off += (size_t)rows * p.kpitch[l];
   }
-  for (int l = 0; l < p.L; l++) { p.hs_off[l] = (int)off; off += (size_t)TM * p.kpitch[l]; }
+  for (int b = 0; b < 2; b++) { p.x_off[b] = (int)off; off += (size_t)TM * p.kpitch[0]; }
+  p.hs_off[0] = p.x_off[0];
+  for (int l = 1; l < p.L; l++) { p.hs_off[l] = (int)off; off += (size_t)TM * p.kpitch[l]; }
   for (int l = 1; l < p.L; l++) {
     p.dpitch[l] = round_up(p.n[l], 8) + 4;
     p.ds_off[l] = (int)off;
     off += (size_t)TM * p.dpitch[l];
   }
   p.cvec_off = (int)off; off += TM;
-  p.mean_off = (int)off; off += p.n[0];
-  p.scale_off = (int)off; off += p.n[0];
+  p.erow_off = (int)off; off += TM;
+  p.mu_off = (int)off; off += p.kpitch[0];
+  p.is_off = (int)off; off += p.kpitch[0];
+  p.red_off = (int)off; off += 3 * MLP_WARPS;
   p.tf_off_bytes = (int)(off * sizeof(double));
   int nodes = 0;
   for (int l = 1; l <= p.L; l++) nodes += p.n[l];
-  p.smem_bytes = off * sizeof(double) + (size_t)nodes * sizeof(int);
-  p.smem_bytes = (p.smem_bytes + 15) & ~(size_t)15;
+  size_t bytes = off * sizeof(double) + (size_t)nodes * sizeof(int);
+  bytes = (bytes + 15) & ~(size_t)15;
+  p.desc_off_bytes = (int)bytes;
   int t = 0;
   for (int l = 0; l < p.L - 1; l++) {
-    p.tile_prefix[l] = t;
-    t += (round_up(p.n[l + 1], 8) / 8) * (round_up(p.n[l] + 1, 8) / 8);
+    const int nm = round_up(p.n[l + 1], 8) / 8, nn = round_up(p.n[l] + 1, 8) / 8;
+    for (int mi = 0; mi < nm; mi++)
+      for (int ni = 0; ni < nn; ni++) {
+        if (tiles) {
+          DwTile d;
+          d.a_off = p.ds_off[l + 1] + 8 * mi;
+          d.b_off = (l == 0 ? 0 : p.hs_off[l]) + 8 * ni;
+          d.dp = p.dpitch[l + 1];
+          d.kp = p.kpitch[l];
+          d.layer = l; d.mi = mi; d.ni = ni; d.pad = 0;
+          tiles->push_back(d);
+        }
+        t++;
+      }
   }
-  for (int l = (p.L - 1 > 0 ? p.L - 1 : 0); l <= PP_MAX_LAYERS; l++) p.tile_prefix[l] = t;
-  return true;
+  p.n_dw_tiles = t;
+  bytes += (size_t)t * sizeof(DwTile);
+  p.smem_bytes = (bytes + 15) & ~(size_t)15;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -82,24 +108,37 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                : "+d"(c0), "+d"(c1)
                : "d"(a), "d"(b));
 }
+__device__ __forceinline__ void pair_barrier(int mt) { asm volatile("bar.sync %0, 64;" ::"r"(1 + mt) : "memory"); }
+__device__ __forceinline__ void cp_async16(void* dst, const void* src)
+{
+  unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(src));
+}
+__device__ __forceinline__ void cp_async8(void* dst, const void* src)
+{
+  unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
 // Transfer functions and derivatives: Neural_network_node (NN_node.h:144-254)
 __device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, const double* __restrict__ table)
 {
+  if (id == 1) {   // tanh with the reference's asymptotic branch beyond |x| > 6 (NN_node.h:193-206)
+    double ax = fabs(in);
+    double sgn = (in > 0.0) ? 1.0 : ((in < 0.0) ? -1.0 : 0.0);
+    double e = exp(-2.0 * ax);
+    if (ax > 6.0) {
+      deriv = 4.0 * e * (1.0 - 2.0 * e);
+      return sgn * (1.0 - 2.0 * e * (1.0 - e));
+    }
+    double r = 1.0 / (1.0 + e);
+    deriv = 4.0 * e * r * r;          // 1/cosh^2
+    return sgn * (1.0 - e) * r;       // tanh
+  }
   switch (id) {
     case 0: deriv = 1.0; return in;
-    case 1: {   // tanh with the reference's asymptotic branch beyond |x| > 6 (NN_node.h:193-206)
-      double ax = fabs(in);
-      double sgn = (in > 0.0) ? 1.0 : ((in < 0.0) ? -1.0 : 0.0);
-      double e = exp(-2.0 * ax);
-      if (ax > 6.0) {
-        deriv = 4.0 * e * (1.0 - 2.0 * e);
-        return sgn * (1.0 - 2.0 * e * (1.0 - e));
-      }
-      double r = 1.0 / (1.0 + e);
-      deriv = 4.0 * e * r * r;          // 1/cosh^2
-      return sgn * (1.0 - e) * r;       // tanh
-    }
     case 2: {   // cubic-spline table on [-17,17] (Tables.h:74-128, Tables.cpp:212-221)
       const double* X = table;
       const double* A = table + 1001;
@@ -140,30 +179,50 @@ __device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, 
   return 0.0;
 }
 
-// One DMMA GEMM for the 8 rows of m-tile `mt`:  C[8][N] = A[8][K] * B, with
-//   A(row,k)  = As[(8*mt+row)*apitch + k]
-//   B(k,n)    = BT ? Bs[k*bpitch + n] : Bs[n*bpitch + k]
-// K is padded to a multiple of 4 and N to a multiple of 8 by zero-filled shared memory.
-template <bool BT, int NT>
+// One DMMA GEMM for the 8 rows of m-tile `mt` and the n-tiles [nt0, nt0+ntc):  C[8][8 ntc] = A[8][K] * B, with
+//   A(row,k) = As[(8*mt+row)*apitch + k]            (NORM: (A - mu[k]) * is[k], the descriptor normalisation)
+//   B(k,n)   = BT ? Bs[k*bpitch + n] : Bs[n*bpitch + k]
+// K is padded to a multiple of 4 and N to a multiple of 8 by zero-filled shared memory.  The next k-step's
+// fragments are loaded before the current step's DMMAs are issued.
+template <bool BT, bool NORM, int NT>
 __device__ __forceinline__ void tile_gemm(double (&acc)[NT][2], const double* __restrict__ As, int apitch,
-                                          const double* __restrict__ Bs, int bpitch, int mt, int K4, int ntiles, int lane)
+                                          const double* __restrict__ Bs, int bpitch, int mt, int K4, int nt0, int ntc, int lane,
+                                          const double* __restrict__ mu, const double* __restrict__ is)
 {
   const int g = lane >> 2, q = lane & 3;
 #pragma unroll
   for (int nt = 0; nt < NT; nt++) { acc[nt][0] = 0.0; acc[nt][1] = 0.0; }
   const double* arow = As + (size_t)(8 * mt + g) * apitch + q;
-  for (int k0 = 0; k0 < K4; k0 += 4) {
-    const double a = arow[k0];
+  const double* bbase = BT ? Bs + (size_t)q * bpitch + 8 * nt0 + g : Bs + (size_t)(8 * nt0 + g) * bpitch + q;
+  const int bstep_k = BT ? 4 * bpitch : 4;
+  const int bstep_n = BT ? 8 : 8 * bpitch;
+  double a_cur = arow[0];
+  if (NORM) a_cur = (a_cur - mu[q]) * is[q];
+  double b_cur[NT];
 #pragma unroll
-    for (int nt = 0; nt < NT; nt++) {
-      if (nt < ntiles) {
-        const double b = BT ? Bs[(size_t)(k0 + q) * bpitch + 8 * nt + g] : Bs[(size_t)(8 * nt + g) * bpitch + k0 + q];
-        dmma884(acc[nt][0], acc[nt][1], a, b);
-      }
+  for (int nt = 0; nt < NT; nt++) b_cur[nt] = (nt < ntc) ? bbase[nt * bstep_n] : 0.0;
+  for (int k0 = 0; k0 < K4; k0 += 4) {
+    double a_nxt = 0.0, b_nxt[NT];
+    const bool more = (k0 + 4 < K4);
+    if (more) {
+      a_nxt = arow[k0 + 4];
+      if (NORM) a_nxt = (a_nxt - mu[k0 + 4 + q]) * is[k0 + 4 + q];
     }
+    const double* bk = bbase + (size_t)(k0 / 4 + 1) * bstep_k;
+#pragma unroll
+    for (int nt = 0; nt < NT; nt++) b_nxt[nt] = (more && nt < ntc) ? bk[nt * bstep_n] : 0.0;
+#pragma unroll
+    for (int nt = 0; nt < NT; nt++)
+      if (nt < ntc) dmma884(acc[nt][0], acc[nt][1], a_cur, b_cur[nt]);
+    a_cur = a_nxt;
+#pragma unroll
+    for (int nt = 0; nt < NT; nt++) b_cur[nt] = b_nxt[nt];
   }
 }
 
+// MODE: PP_MLP_FORWARD (energies only), PP_MLP_TRAIN (two-phase backward: c per structure given),
+//       PP_MLP_INPUT_GRAD (dE/dG, MD), PP_MLP_FUSED (single pass: forward, per-structure error, backward; needs
+//       tiles made of whole structures of a single-element system)
 template <int MODE, int NT, int OWN>
 __global__ void __launch_bounds__(MLP_THREADS, 1)
 mlp_kernel(MlpArgs a, MlpPlan p)
@@ -171,10 +230,13 @@ mlp_kernel(MlpArgs a, MlpPlan p)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sm = reinterpret_cast<double*>(smem_raw);
   int* tfs = reinterpret_cast<int*>(smem_raw + p.tf_off_bytes);
+  const DwTile* dwt = reinterpret_cast<const DwTile*>(smem_raw + p.desc_off_bytes);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, q = lane & 3;
   const int L = p.L, TM = p.TM, NG = p.n[0];
   const NetDev& net = a.net;
+  constexpr bool BACKWARD = (MODE != PP_MLP_FORWARD);
+  constexpr bool GRADW = (MODE == PP_MLP_TRAIN || MODE == PP_MLP_FUSED);
 
   // ---- one-time staging: weights (zero padded), constant columns, transfer ids, input scaling ----------------
   for (int l = 0; l < L; l++) {
@@ -182,16 +244,23 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     const int rows = (l == L - 1) ? 1 : round_up(n_out, 8);
     double* Ws = sm + p.ws_off[l];
     const double* src = net.params + net.w_off[l];
-    for (int i = tid; i < rows * kp; i += MLP_THREADS) {
-      int r = i / kp, k = i - r * kp;
-      Ws[i] = (r < n_out && k <= n_in) ? src[(size_t)r * (n_in + 1) + k] : 0.0;
-    }
-    double* Hs = sm + p.hs_off[l];
-    for (int i = tid; i < TM * kp; i += MLP_THREADS) {
-      int k = i % kp;
-      Hs[i] = (k == n_in) ? 1.0 : 0.0;
-    }
-    if (l >= 1) {
+    for (int r = warp; r < rows; r += MLP_WARPS)
+      for (int k = lane; k < kp; k += 32) Ws[r * kp + k] = (r < n_out && k <= n_in) ? src[(size_t)r * (n_in + 1) + k] : 0.0;
+    if (l == 0) {
+      // raw descriptor tiles: pad column NG holds 1 (the bias input), the rest 0; mu/is make (x - mu)*is the identity there
+      for (int b = 0; b < 2; b++) {
+        double* X = sm + p.x_off[b];
+        for (int r = warp; r < TM; r += MLP_WARPS)
+          for (int k = lane; k < kp; k += 32) X[r * kp + k] = (k == n_in) ? 1.0 : 0.0;
+      }
+      for (int k = tid; k < kp; k += MLP_THREADS) {
+        sm[p.mu_off + k] = (k < NG) ? net.mean[k] : 0.0;
+        sm[p.is_off + k] = (k < NG) ? 1.0 / net.scale[k] : (k == NG ? 1.0 : 0.0);
+      }
+    } else {
+      double* Hs = sm + p.hs_off[l];
+      for (int r = warp; r < TM; r += MLP_WARPS)
+        for (int k = lane; k < kp; k += 32) Hs[r * kp + k] = (k == n_in) ? 1.0 : 0.0;
       double* Ds = sm + p.ds_off[l];
       for (int i = tid; i < TM * p.dpitch[l]; i += MLP_THREADS) Ds[i] = 0.0;
     }
@@ -200,196 +269,279 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     int nodes = 0;
     for (int l = 1; l <= L; l++) nodes += p.n[l];
     for (int i = tid; i < nodes; i += MLP_THREADS) tfs[i] = net.tf[i];
-    for (int i = tid; i < NG; i += MLP_THREADS) { sm[p.mean_off + i] = net.mean[i]; sm[p.scale_off + i] = net.scale[i]; }
+    const int nwords = p.n_dw_tiles * (int)(sizeof(DwTile) / sizeof(int));
+    int* dst = reinterpret_cast<int*>(smem_raw + p.desc_off_bytes);
+    const int* srcw = reinterpret_cast<const int*>(a.dw_tiles);
+    for (int i = tid; i < nwords; i += MLP_THREADS) dst[i] = srcw[i];
   }
-  __syncthreads();
+  const double* mu = sm + p.mu_off;
+  const double* is = sm + p.is_off;
 
-  // ---- parameter-gradient accumulators (TRAIN) ---------------------------------------------------------------
+  // ---- parameter-gradient accumulators ------------------------------------------------------------------------
   double dW[OWN][2];
-  double dwout = 0.0;     // thread t <= n_{L-1}: gradient of output-node parameter t
-  const int n_dw_tiles = p.tile_prefix[L - 1 > 0 ? L - 1 : 0];
+  double dwout = 0.0;                         // thread t <= n_{L-1}: gradient of output-node parameter t
+  double sse_w = 0.0, vsse_w = 0.0, nval_w = 0.0;   // FUSED: per-warp loss terms (lane 0)
 #pragma unroll
   for (int t = 0; t < OWN; t++) { dW[t][0] = 0.0; dW[t][1] = 0.0; }
 
   double* cvec = sm + p.cvec_off;
-  const int n_tiles = (a.M + TM - 1) / TM;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int row0 = tile * TM;
-    const int nvalid = min(TM, a.M - row0);
-    // ---- load + normalise inputs: (G - mean)/scale with the reference's exact-zero guard (NN.cpp:648-654) ----
-    {
-      double* H0 = sm + p.hs_off[0];
-      const int kp = p.kpitch[0];
-      for (int i = tid; i < TM * NG; i += MLP_THREADS) {
-        int r = i / NG, k = i - r * NG;
-        double v = 0.0;
-        if (r < nvalid) {
-          size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
-          double d = a.G[atom * NG + k] - sm[p.mean_off + k];
-          v = (d == 0.0) ? 0.0 : d / sm[p.scale_off + k];
-        }
-        H0[r * kp + k] = v;
-      }
-      if (MODE != PP_MLP_FORWARD) {
-        for (int r = tid; r < TM; r += MLP_THREADS) {
-          double c = 0.0;
-          if (r < nvalid) {
-            size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
-            c = (MODE == PP_MLP_TRAIN) ? a.cstruct[a.atom_struct[atom]] : a.out_scale;
-          }
-          cvec[r] = c;
-        }
+  double* erow = sm + p.erow_off;
+  const int n_tiles = (MODE == PP_MLP_FUSED) ? a.n_tiles : (a.M + TM - 1) / TM;
+  const int kp0 = p.kpitch[0];
+  const bool vec16 = (NG & 1) == 0;
+
+  // tile geometry
+  auto tile_rows = [&](int tile, int& row0, int& nvalid) {
+    if (MODE == PP_MLP_FUSED) {
+      const long long r0 = a.struct_atom0[a.tile_struct0[tile]];
+      row0 = (int)r0;
+      nvalid = (int)(a.struct_atom0[a.tile_struct0[tile + 1]] - r0);
+    } else {
+      row0 = tile * TM;
+      nvalid = min(TM, a.M - row0);
+    }
+  };
+  // asynchronous copy of one tile's raw descriptor rows into X[buf]
+  auto issue_load = [&](int tile, int buf) {
+    int row0, nvalid;
+    tile_rows(tile, row0, nvalid);
+    double* X = sm + p.x_off[buf];
+    for (int r = warp; r < TM; r += MLP_WARPS) {
+      double* dst = X + (size_t)r * kp0;
+      if (r < nvalid) {
+        const size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
+        const double* src = a.G + atom * NG;
+        if (vec16) { for (int c = lane; c < (NG >> 1); c += 32) cp_async16(dst + 2 * c, src + 2 * c); }
+        else { for (int c = lane; c < NG; c += 32) cp_async8(dst + c, src + c); }
+      } else {
+        for (int c = lane; c < NG; c += 32) dst[c] = 0.0;
       }
     }
-    __syncthreads();
+    cp_async_commit();
+  };
 
-    // ---- forward through the hidden layers; each warp owns whole m-tiles (8 atoms) --------------------------
-    for (int mt = warp; mt < TM / 8; mt += MLP_WARPS) {
+  int buf = 0;
+  if ((int)blockIdx.x < n_tiles) issue_load(blockIdx.x, 0);
+  __syncthreads();
+
+  const int mt = warp >> 1, half = warp & 1;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
+    int row0, nvalid;
+    tile_rows(tile, row0, nvalid);
+    cp_async_wait_all();
+    __syncthreads();
+    if (tile + (int)gridDim.x < n_tiles) issue_load(tile + gridDim.x, buf ^ 1);
+    const double* X = sm + p.x_off[buf];
+    if (MODE == PP_MLP_TRAIN || MODE == PP_MLP_INPUT_GRAD) {
+      for (int r = tid; r < TM; r += MLP_THREADS) {
+        double c = 0.0;
+        if (r < nvalid) {
+          const size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
+          c = (MODE == PP_MLP_TRAIN) ? a.cstruct[a.atom_struct[atom]] : a.out_scale;
+        }
+        cvec[r] = c;
+      }
+    }
+
+    // ---- forward through the hidden layers: a pair of warps per m-tile (8 atoms), n-tiles split between them ----
+    if (mt < TM / 8) {
       double acc[NT][2];
       for (int l = 0; l < L - 1; l++) {
         const int n_in = p.n[l], n_out = p.n[l + 1];
-        const int ntiles = (n_out + 7) >> 3;
-        tile_gemm<false, NT>(acc, sm + p.hs_off[l], p.kpitch[l], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_in + 1, 4), ntiles, lane);
+        const int ntl = (n_out + 7) >> 3;
+        const int nt0 = half ? (ntl + 1) >> 1 : 0;
+        const int ntc = half ? ntl - nt0 : (ntl + 1) >> 1;
+        if (l == 0) tile_gemm<false, true, NT>(acc, X, kp0, sm + p.ws_off[0], kp0, mt, round_up(n_in + 1, 4), nt0, ntc, lane, mu, is);
+        else tile_gemm<false, false, NT>(acc, sm + p.hs_off[l], p.kpitch[l], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_in + 1, 4), nt0, ntc, lane, mu, is);
         double* Hn = sm + p.hs_off[l + 1] + (size_t)(8 * mt + g) * p.kpitch[l + 1];
         double* Dn = sm + p.ds_off[l + 1] + (size_t)(8 * mt + g) * p.dpitch[l + 1];
         const int* tfl = tfs + net.node_off[l];
 #pragma unroll
         for (int nt = 0; nt < NT; nt++) {
-          if (nt < ntiles) {
+          if (nt < ntc) {
 #pragma unroll
             for (int h = 0; h < 2; h++) {
-              int n = 8 * nt + 2 * q + h;
+              const int n = 8 * (nt0 + nt) + 2 * q + h;
               if (n < n_out) {
                 double d;
                 double t = pp_transfer(tfl[n], acc[nt][h], d, a.tanh_table);
                 Hn[n] = t;
-                Dn[n] = d;
+                if (BACKWARD) Dn[n] = d;
               }
             }
           }
         }
-        __syncwarp();
+        pair_barrier(mt);
       }
-      // ---- output node (always linear, NN.cpp:76): y = w_out . [H, 1];  4 lanes per atom ----------------------
-      {
+      // ---- output node (always linear, NN.cpp:76): y = w_out . [H, 1];  4 lanes per atom, first warp of the pair ----
+      if (half == 0) {
         const int n_in = p.n[L - 1];
-        const double* Hl = sm + p.hs_off[L - 1] + (size_t)(8 * mt + g) * p.kpitch[L - 1];
         const double* wo = sm + p.ws_off[L - 1];
         double y = 0.0;
-        for (int k = q; k <= n_in; k += 4) y = fma(Hl[k], wo[k], y);
+        if (L == 1) {
+          const double* xr = X + (size_t)(8 * mt + g) * kp0;
+          for (int k = q; k <= n_in; k += 4) y = fma((xr[k] - mu[k]) * is[k], wo[k], y);
+        } else {
+          const double* Hl = sm + p.hs_off[L - 1] + (size_t)(8 * mt + g) * p.kpitch[L - 1];
+          for (int k = q; k <= n_in; k += 4) y = fma(Hl[k], wo[k], y);
+        }
         y += __shfl_xor_sync(0xffffffffu, y, 1);
         y += __shfl_xor_sync(0xffffffffu, y, 2);
         const int r = 8 * mt + g;
-        if (MODE != PP_MLP_TRAIN && a.E_atom != nullptr && q == 0 && r < nvalid) {
-          size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
-          double d;
-          a.E_atom[atom] = a.out_scale * pp_transfer(tfs[net.node_off[L - 1]], y, d, a.tanh_table);
+        if (q == 0) {
+          const double e = a.out_scale * y;
+          if (MODE == PP_MLP_FUSED) erow[r] = (r < nvalid) ? e : 0.0;
+          else if (MODE != PP_MLP_TRAIN && a.E_atom != nullptr && r < nvalid) {
+            const size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
+            a.E_atom[atom] = e;
+          }
         }
       }
-      if (MODE == PP_MLP_FORWARD) continue;
+    }
+    if (MODE == PP_MLP_FUSED) {
+      // ---- per-structure energy, error and loss terms (Potential.cpp:641-668); one warp per structure ----------
+      __syncthreads();
+      const int s_first = a.tile_struct0[tile], s_last = a.tile_struct0[tile + 1];
+      for (int s = s_first + warp; s < s_last; s += MLP_WARPS) {
+        const int r_lo = (int)(a.struct_atom0[s] - row0), r_hi = (int)(a.struct_atom0[s + 1] - row0);
+        double e = 0.0;
+        for (int r = r_lo + lane; r < r_hi; r += 32) e += erow[r];
+        e = pp_warp_sum(e) + a.out_mean;
+        const double err = e - a.target[s];
+        const int tag = a.tag[s];
+        double c = 0.0;
+        if (tag == 0) { c = 2.0 * err * a.out_scale; sse_w += err * err; }
+        else if (tag == 1) { vsse_w += err * err; nval_w += 1.0; }
+        if (lane == 0) a.E_struct[s] = e;
+        for (int r = r_lo + lane; r < r_hi; r += 32) cvec[r] = c;
+      }
+      for (int r = nvalid + tid; r < TM; r += MLP_THREADS) cvec[r] = 0.0;
+      __syncthreads();
+    } else if (BACKWARD) {
+      __syncthreads();   // cvec
+    }
 
-      // ---- backward: delta of the last hidden layer, then back through the hidden layers -----------------------
-      // (output node linear: dE/dy = c; delta_{L-1}[n] = c * w_out[n] * T'(z_{L-1}[n]))
+    if (BACKWARD && mt < TM / 8) {
+      double acc[NT][2];
+      // ---- delta of the last hidden layer: c * w_out[n] * T'(z[n])  (output node linear) ------------------------
       if (L >= 2) {
-        const int n_h = p.n[L - 1];
-        double* Dl = sm + p.ds_off[L - 1] + (size_t)(8 * mt) * p.dpitch[L - 1];
-        const double* wo = sm + p.ws_off[L - 1];
-        for (int i = lane; i < 8 * n_h; i += 32) {
-          int r = i / n_h, n = i - r * n_h;
-          Dl[r * p.dpitch[L - 1] + n] *= cvec[8 * mt + r] * wo[n];
+        {
+          const int n_h = p.n[L - 1];
+          const int ntl = (n_h + 7) >> 3;
+          const int nt0 = half ? (ntl + 1) >> 1 : 0;
+          const int ntc = half ? ntl - nt0 : (ntl + 1) >> 1;
+          double* Dr = sm + p.ds_off[L - 1] + (size_t)(8 * mt + g) * p.dpitch[L - 1];
+          const double* wo = sm + p.ws_off[L - 1];
+          const double c = cvec[8 * mt + g];
+          const int n_end = min(n_h, 8 * (nt0 + ntc));
+          for (int n = 8 * nt0 + q; n < n_end; n += 4) Dr[n] *= c * wo[n];
         }
-        __syncwarp();
+        pair_barrier(mt);
         for (int l = L - 2; l >= 1; l--) {
           // delta_l = (delta_{l+1} * W_l[:, :n_l]) .* T'(z_l)
           const int n_l = p.n[l], n_up = p.n[l + 1];
-          const int ntiles = (n_l + 7) >> 3;
-          tile_gemm<true, NT>(acc, sm + p.ds_off[l + 1], p.dpitch[l + 1], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_up, 4), ntiles, lane);
+          const int ntl = (n_l + 7) >> 3;
+          const int nt0 = half ? (ntl + 1) >> 1 : 0;
+          const int ntc = half ? ntl - nt0 : (ntl + 1) >> 1;
+          tile_gemm<true, false, NT>(acc, sm + p.ds_off[l + 1], p.dpitch[l + 1], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_up, 4), nt0, ntc, lane, mu, is);
           double* Dr = sm + p.ds_off[l] + (size_t)(8 * mt + g) * p.dpitch[l];
 #pragma unroll
           for (int nt = 0; nt < NT; nt++) {
-            if (nt < ntiles) {
+            if (nt < ntc) {
 #pragma unroll
               for (int h = 0; h < 2; h++) {
-                int n = 8 * nt + 2 * q + h;
+                const int n = 8 * (nt0 + nt) + 2 * q + h;
                 if (n < n_l) Dr[n] *= acc[nt][h];
               }
             }
           }
-          __syncwarp();
+          pair_barrier(mt);
         }
       }
       if (MODE == PP_MLP_INPUT_GRAD) {
-        // dE/dG_k = (delta_1 * W_0[:, k]) / scale_k   (NN.cpp:546-566); no hidden layer: c * w_out[k] / scale_k
+        // dE/dG_k = (delta_1 * W_0[:, k]) / scale_k   (NN.cpp:546-566); without hidden layers: c * w_out[k] / scale_k
         const int r = 8 * mt + g;
         size_t atom = 0;
         if (r < nvalid) atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
         if (L >= 2) {
-          const int ntiles = (NG + 7) >> 3;
-          for (int nt0 = 0; nt0 < ntiles; nt0 += NT) {
-            const int ntc = min(NT, ntiles - nt0);
-            tile_gemm<true, NT>(acc, sm + p.ds_off[1], p.dpitch[1], sm + p.ws_off[0] + 8 * nt0, p.kpitch[0], mt, round_up(p.n[1], 4), ntc, lane);
+          const int ntl = (NG + 7) >> 3;
+          const int h0 = half ? (ntl + 1) >> 1 : 0;
+          const int hc = half ? ntl - h0 : (ntl + 1) >> 1;
+          for (int c0 = 0; c0 < hc; c0 += NT) {
+            const int ntc = min(NT, hc - c0);
+            tile_gemm<true, false, NT>(acc, sm + p.ds_off[1], p.dpitch[1], sm + p.ws_off[0], kp0, mt, round_up(p.n[1], 4), h0 + c0, ntc, lane, mu, is);
             if (r < nvalid) {
 #pragma unroll
               for (int nt = 0; nt < NT; nt++) {
                 if (nt < ntc) {
 #pragma unroll
                   for (int h = 0; h < 2; h++) {
-                    int k = 8 * (nt0 + nt) + 2 * q + h;
-                    if (k < NG) a.dEdG[atom * NG + k] = acc[nt][h] / sm[p.scale_off + k];
+                    const int k = 8 * (h0 + c0 + nt) + 2 * q + h;
+                    if (k < NG) a.dEdG[atom * NG + k] = acc[nt][h] * is[k];
                   }
                 }
               }
             }
           }
-        } else if (r < nvalid) {
+        } else if (r < nvalid && half == 0) {
           const double* wo = sm + p.ws_off[0];
-          for (int k = q; k < NG; k += 4) a.dEdG[atom * NG + k] = cvec[r] * wo[k] / sm[p.scale_off + k];
+          for (int k = q; k < NG; k += 4) a.dEdG[atom * NG + k] = cvec[r] * wo[k] * is[k];
         }
       }
     }
-    __syncthreads();
 
     // ---- parameter gradients: dW_l += delta_{l+1}^T * [H_l, 1]  (K = atoms of the tile) ------------------------
-    if constexpr (MODE == PP_MLP_TRAIN) {
-      // output node: thread t <= n_{L-1}
+    if constexpr (GRADW) {
+      __syncthreads();
       {
         const int n_in = p.n[L - 1];
         if (tid <= n_in) {
-          const double* Hl = sm + p.hs_off[L - 1] + tid;
-          const int kp = p.kpitch[L - 1];
           double s = 0.0;
-          for (int r = 0; r < TM; r++) s = fma(cvec[r], Hl[(size_t)r * kp], s);
+          if (L == 1) {
+            const double m = mu[tid], sc = is[tid];
+            for (int r = 0; r < TM; r++) s = fma(cvec[r], (X[(size_t)r * kp0 + tid] - m) * sc, s);
+          } else {
+            const double* Hl = sm + p.hs_off[L - 1] + tid;
+            const int kp = p.kpitch[L - 1];
+            for (int r = 0; r < TM; r++) s = fma(cvec[r], Hl[(size_t)r * kp], s);
+          }
           dwout += s;
         }
       }
 #pragma unroll
       for (int t = 0; t < OWN; t++) {
         const int tile_id = warp + t * MLP_WARPS;
-        if (tile_id < n_dw_tiles) {
-          int l = 0;
-          while (tile_id >= p.tile_prefix[l + 1]) l++;
-          const int local = tile_id - p.tile_prefix[l];
-          const int ncols = round_up(p.n[l] + 1, 8) >> 3;
-          const int mi = local / ncols, ni = local - mi * ncols;
-          const double* Dl = sm + p.ds_off[l + 1] + 8 * mi + g;      // A(m = neuron, k = atom) = delta[atom][neuron]
-          const double* Hl = sm + p.hs_off[l] + 8 * ni + g;          // B(k = atom, n = input) = H[atom][input]
-          const int dp = p.dpitch[l + 1], kp = p.kpitch[l];
+        if (tile_id < p.n_dw_tiles) {
+          const DwTile d = dwt[tile_id];
+          const double* Dl = sm + d.a_off + g;                      // A(m = neuron, k = atom) = delta[atom][neuron]
           double c0 = dW[t][0], c1 = dW[t][1];
-          for (int k0 = 0; k0 < TM; k0 += 4) {
-            const double av = Dl[(size_t)(k0 + q) * dp];
-            const double bv = Hl[(size_t)(k0 + q) * kp];
-            dmma884(c0, c1, av, bv);
+          if (d.layer == 0) {
+            const double* Hl = X + d.b_off + g;                     // B(k = atom, n = input) = normalised descriptor
+            const double m = mu[d.b_off + g], sc = is[d.b_off + g];
+            for (int k0 = 0; k0 < TM; k0 += 4) {
+              const double av = Dl[(size_t)(k0 + q) * d.dp];
+              const double bv = (Hl[(size_t)(k0 + q) * d.kp] - m) * sc;
+              dmma884(c0, c1, av, bv);
+            }
+          } else {
+            const double* Hl = sm + d.b_off + g;
+#pragma unroll 4
+            for (int k0 = 0; k0 < TM; k0 += 4) {
+              const double av = Dl[(size_t)(k0 + q) * d.dp];
+              const double bv = Hl[(size_t)(k0 + q) * d.kp];
+              dmma884(c0, c1, av, bv);
+            }
           }
           dW[t][0] = c0; dW[t][1] = c1;
         }
       }
-      __syncthreads();
     }
   }
+  cp_async_wait_all();
 
-  // ---- per-CTA partial gradient -> scratch -----------------------------------------------------------------
-  if constexpr (MODE == PP_MLP_TRAIN) {
-    double* out = a.partial + (size_t)blockIdx.x * a.P_total + a.p_off;
+  // ---- per-CTA partial gradient (+ loss terms) -> scratch ------------------------------------------------------
+  if constexpr (GRADW) {
+    double* out = a.partial + (size_t)blockIdx.x * (a.P_total + 3) + a.p_off;
     {
       const int n_in = p.n[L - 1];
       if (tid <= n_in) out[net.w_off[L - 1] + tid] = dwout;
@@ -397,21 +549,28 @@ mlp_kernel(MlpArgs a, MlpPlan p)
 #pragma unroll
     for (int t = 0; t < OWN; t++) {
       const int tile_id = warp + t * MLP_WARPS;
-      if (tile_id < n_dw_tiles) {
-        int l = 0;
-        while (tile_id >= p.tile_prefix[l + 1]) l++;
-        const int local = tile_id - p.tile_prefix[l];
-        const int ncols = round_up(p.n[l] + 1, 8) >> 3;
-        const int mi = local / ncols, ni = local - mi * ncols;
-        const int neuron = 8 * mi + g;
-        const int n_in = p.n[l];
-        if (neuron < p.n[l + 1]) {
+      if (tile_id < p.n_dw_tiles) {
+        const DwTile d = dwt[tile_id];
+        const int neuron = 8 * d.mi + g;
+        const int n_in = p.n[d.layer];
+        if (neuron < p.n[d.layer + 1]) {
 #pragma unroll
           for (int h = 0; h < 2; h++) {
-            int k = 8 * ni + 2 * q + h;
-            if (k <= n_in) out[net.w_off[l] + (size_t)neuron * (n_in + 1) + k] = dW[t][h];
+            const int k = 8 * d.ni + 2 * q + h;
+            if (k <= n_in) out[net.w_off[d.layer] + (size_t)neuron * (n_in + 1) + k] = dW[t][h];
           }
         }
+      }
+    }
+    if (MODE == PP_MLP_FUSED) {
+      double* red = sm + p.red_off;
+      __syncthreads();
+      if (lane == 0) { red[3 * warp] = sse_w; red[3 * warp + 1] = vsse_w; red[3 * warp + 2] = nval_w; }
+      __syncthreads();
+      if (tid < 3) {
+        double s = 0.0;
+        for (int w = 0; w < MLP_WARPS; w++) s += red[3 * w + tid];
+        a.partial[(size_t)blockIdx.x * (a.P_total + 3) + a.P_total + tid] = s;
       }
     }
   }
@@ -432,50 +591,80 @@ static int sm_count()
 
 int ppk_mlp_max_ctas(void) { return sm_count(); }
 
+// Largest tile (multiple of 8 atoms, <= 64) whose shared-memory plan fits; 0 if none.
+static int choose_tm(const NetDev& net, MlpPlan& plan, std::vector<DwTile>* tiles)
+{
+  for (int TM = 64; TM >= 8; TM -= 8) {
+    if (tiles) tiles->clear();
+    make_plan(net, TM, plan, tiles);
+    if (plan.smem_bytes <= 227 * 1024) return TM;
+  }
+  return 0;
+}
+
+int ppk_mlp_tile_atoms(const NetDev& net)
+{
+  MlpPlan plan;
+  return choose_tm(net, plan, nullptr);
+}
+
+int ppk_mlp_num_dw_tiles(const NetDev& net, void* host_tiles_out)
+{
+  MlpPlan plan;
+  std::vector<DwTile> tiles;
+  if (!choose_tm(net, plan, &tiles)) return -1;
+  if (host_tiles_out && !tiles.empty()) memcpy(host_tiles_out, tiles.data(), tiles.size() * sizeof(DwTile));
+  return (int)tiles.size();
+}
+
+int ppk_mlp_dw_tile_bytes(void) { return (int)sizeof(DwTile); }
+
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches)
 {
-  if (a.M == 0) {
-    return 0;
-  }
+  if (a.M == 0 && mode != PP_MLP_FUSED && mode != PP_MLP_TRAIN) return 0;
   const NetDev& net = a.net;
   PP_REQUIRE(net.n_layers >= 1 && net.n_layers <= PP_MAX_LAYERS, "network has %d weight layers (max %d)", net.n_layers, PP_MAX_LAYERS);
   int max_hidden = 0;
   for (int l = 1; l < net.n_layers; l++) {
-    PP_REQUIRE(net.sizes[l] <= 8 * MLP_MAX_NT, "hidden layer %d has %d nodes (max %d)", l, net.sizes[l], 8 * MLP_MAX_NT);
+    PP_REQUIRE(net.sizes[l] <= MLP_MAX_WIDTH, "hidden layer %d has %d nodes (max %d)", l, net.sizes[l], MLP_MAX_WIDTH);
     if (net.sizes[l] > max_hidden) max_hidden = net.sizes[l];
   }
   MlpPlan plan;
-  int TM = 64;
-  for (;;) {
-    make_plan(net, TM, plan);
-    if (plan.smem_bytes <= 227 * 1024) break;
-    TM -= 8;
-    PP_REQUIRE(TM >= 8, "network too large for shared memory (%zu bytes at 8 atoms per tile)", plan.smem_bytes);
-  }
-  const int n_dw_tiles = plan.tile_prefix[net.n_layers - 1 > 0 ? net.n_layers - 1 : 0];
-  PP_REQUIRE(n_dw_tiles <= MLP_MAX_OWN * MLP_WARPS, "network has %d weight-gradient tiles (max %d)", n_dw_tiles, MLP_MAX_OWN * MLP_WARPS);
-  const int n_tiles = (a.M + TM - 1) / TM;
+  const int TM = choose_tm(net, plan, nullptr);
+  PP_REQUIRE(TM > 0, "network too large for shared memory (%zu bytes at 8 atoms per tile)", plan.smem_bytes);
+  PP_REQUIRE(plan.n_dw_tiles <= 16 * MLP_WARPS, "network has %d weight-gradient tiles (max %d)", plan.n_dw_tiles, 16 * MLP_WARPS);
+  PP_REQUIRE(a.dw_tiles != nullptr || plan.n_dw_tiles == 0, "internal: weight-gradient tile table missing");
+  const int n_tiles = (mode == PP_MLP_FUSED) ? a.n_tiles : (a.M + TM - 1) / TM;
   int grid = sm_count();
-  if (mode != PP_MLP_TRAIN && grid > n_tiles) grid = n_tiles;   // TRAIN: every CTA writes its (possibly zero) partial
-  const bool wide = max_hidden > 64;
-  const bool many = (n_dw_tiles + MLP_WARPS - 1) / MLP_WARPS > 12;
+  const bool gradw = (mode == PP_MLP_TRAIN || mode == PP_MLP_FUSED);
+  if (!gradw && grid > n_tiles) grid = n_tiles;   // gradient modes: every CTA writes its (possibly zero) partial
+  if (grid == 0) return 0;
+  const bool wide = max_hidden > 64;                                         // more than 4 n-tiles per warp of a pair
+  const bool many = (plan.n_dw_tiles + MLP_WARPS - 1) / MLP_WARPS > 6;
 #define PP_LAUNCH(MODE_, NT_, OWN_)                                                                             \
   {                                                                                                             \
     auto k = mlp_kernel<MODE_, NT_, OWN_>;                                                                      \
     PP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes));        \
     k<<<grid, MLP_THREADS, plan.smem_bytes, st>>>(a, plan);                                                     \
   }
+#define PP_LAUNCH_GRAD(MODE_)                                    \
+  {                                                              \
+    if (wide && many) PP_LAUNCH(MODE_, 8, 16)                    \
+    else if (wide) PP_LAUNCH(MODE_, 8, 6)                        \
+    else if (many) PP_LAUNCH(MODE_, 4, 16)                       \
+    else PP_LAUNCH(MODE_, 4, 6)                                  \
+  }
   if (mode == PP_MLP_FORWARD) {
-    if (wide) PP_LAUNCH(PP_MLP_FORWARD, 16, 1) else PP_LAUNCH(PP_MLP_FORWARD, 8, 1)
+    if (wide) PP_LAUNCH(PP_MLP_FORWARD, 8, 1) else PP_LAUNCH(PP_MLP_FORWARD, 4, 1)
   } else if (mode == PP_MLP_INPUT_GRAD) {
-    if (wide) PP_LAUNCH(PP_MLP_INPUT_GRAD, 16, 1) else PP_LAUNCH(PP_MLP_INPUT_GRAD, 8, 1)
+    if (wide) PP_LAUNCH(PP_MLP_INPUT_GRAD, 8, 1) else PP_LAUNCH(PP_MLP_INPUT_GRAD, 4, 1)
+  } else if (mode == PP_MLP_TRAIN) {
+    PP_LAUNCH_GRAD(PP_MLP_TRAIN)
   } else {
-    if (wide && many) PP_LAUNCH(PP_MLP_TRAIN, 16, 32)
-    else if (wide) PP_LAUNCH(PP_MLP_TRAIN, 16, 12)
-    else if (many) PP_LAUNCH(PP_MLP_TRAIN, 8, 32)
-    else PP_LAUNCH(PP_MLP_TRAIN, 8, 12)
+    PP_LAUNCH_GRAD(PP_MLP_FUSED)
   }
 #undef PP_LAUNCH
+#undef PP_LAUNCH_GRAD
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   return 0;
@@ -522,19 +711,19 @@ int ppk_struct_errors(const StructArgs& a, cudaStream_t st, long long* launches)
   return 0;
 }
 
-__global__ void reduce_partials_kernel(const double* __restrict__ partial, int n_cta, int P, double* __restrict__ grad)
+__global__ void reduce_partials_kernel(const double* __restrict__ partial, int n_cta, int stride, int ncols, double* __restrict__ out)
 {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= P) return;
+  if (p >= ncols) return;
   double s = 0.0;
-  for (int c = 0; c < n_cta; c++) s += partial[(size_t)c * P + p];
-  grad[p] = s;
+  for (int c = 0; c < n_cta; c++) s += partial[(size_t)c * stride + p];
+  out[p] = s;
 }
 
-int ppk_reduce_partials(const double* partial, int n_cta, int P, double* grad, cudaStream_t st, long long* launches)
+int ppk_reduce_partials(const double* partial, int n_cta, int stride, int ncols, double* out, cudaStream_t st, long long* launches)
 {
-  if (P == 0) return 0;
-  reduce_partials_kernel<<<(P + 127) / 128, 128, 0, st>>>(partial, n_cta, P, grad);
+  if (ncols == 0) return 0;
+  reduce_partials_kernel<<<(ncols + 127) / 128, 128, 0, st>>>(partial, n_cta, stride, ncols, out);
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   return 0;
@@ -581,7 +770,7 @@ int ppk_column_stats(const double* G, int NG, const int* rows, int M, const int*
                                              reinterpret_cast<unsigned long long*>(count));
   (*launches)++;
   PP_CUDA(cudaGetLastError());
-  return ppk_reduce_partials(partial, n_cta, NG, sums, st, launches);
+  return ppk_reduce_partials(partial, n_cta, NG, NG, sums, st, launches);
 }
 
 // ---------------------------------------------------------------------------------------------------------
