@@ -18,6 +18,7 @@
 // augmented weight matrix [n_out][n_in+1].
 #include "pp_common.cuh"
 #include "pp_kernels.h"
+#include <algorithm>
 #include <cmath>
 
 #define MLP_WARPS 16
@@ -32,6 +33,7 @@ struct MlpPlan {
   int dpitch[PP_MAX_LAYERS + 1];      // pitch of Ds_l (T' then delta), l = 1..L-1
   int ws_off[PP_MAX_LAYERS], hs_off[PP_MAX_LAYERS], ds_off[PP_MAX_LAYERS + 1];
   int x_off[2];                       // double-buffered raw descriptor tiles
+  int ws_rows[PP_MAX_LAYERS];         // rows of Ws_l held in shared memory (zero padded)
   int cvec_off, erow_off, mu_off, is_off, red_off;
   int tf_off_bytes, desc_off_bytes;
   int n_dw_tiles;
@@ -48,23 +50,33 @@ struct DwTile {
 
 __host__ __device__ static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
+static int plan_nt(const NetDev& net)
+{
+  int mx = 1;
+  for (int l = 1; l < net.n_layers; l++) mx = std::max(mx, net.sizes[l]);
+  int nt = ((mx + 7) / 8 + 1) / 2;              // n-tiles per warp of a pair
+  return nt <= 2 ? 2 : nt <= 3 ? 3 : nt <= 4 ? 4 : 8;
+}
+
 static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>* tiles)
 {
+  const int NTW = 16 * plan_nt(net);             // columns a warp pair covers (zero padded)
   p.TM = TM;
   p.L = net.n_layers;
   for (int l = 0; l <= p.L; l++) p.n[l] = net.sizes[l];
   size_t off = 0;
   for (int l = 0; l < p.L; l++) {
-    p.kpitch[l] = round_up(p.n[l] + 1, 8) + 4;
+    p.kpitch[l] = (l == 0 ? round_up(p.n[l] + 1, 8) : std::max(round_up(p.n[l] + 1, 8), NTW)) + 4;
     p.ws_off[l] = (int)off;
-    int rows = (l == p.L - 1) ? 1 : round_up(p.n[l + 1], 8);
+    int rows = (l == p.L - 1) ? 1 : std::max(round_up(p.n[l + 1], 8), NTW);
+    p.ws_rows[l] = rows;
     off += (size_t)rows * p.kpitch[l];
   }
   for (int b = 0; b < 2; b++) { p.x_off[b] = (int)off; off += (size_t)TM * p.kpitch[0]; }
   p.hs_off[0] = p.x_off[0];
   for (int l = 1; l < p.L; l++) { p.hs_off[l] = (int)off; off += (size_t)TM * p.kpitch[l]; }
   for (int l = 1; l < p.L; l++) {
-    p.dpitch[l] = round_up(p.n[l], 8) + 4;
+    p.dpitch[l] = std::max(round_up(p.n[l], 8), NTW) + 4;
     p.ds_off[l] = (int)off;
     off += (size_t)TM * p.dpitch[l];
   }
@@ -179,12 +191,13 @@ __device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, 
   return 0.0;
 }
 
-// One DMMA GEMM for the 8 rows of m-tile `mt` and the n-tiles [nt0, nt0+ntc):  C[8][8 ntc] = A[8][K] * B, with
+// One DMMA GEMM for the 8 rows of m-tile `mt` and the n-tiles [nt0, nt0+NT):  C[8][8 NT] = A[8][K] * B, with
 //   A(row,k) = As[(8*mt+row)*apitch + k]            (NORM: (A - mu[k]) * is[k], the descriptor normalisation)
 //   B(k,n)   = BT ? Bs[k*bpitch + n] : Bs[n*bpitch + k]
-// K is padded to a multiple of 4 and N to a multiple of 8 by zero-filled shared memory.  The next k-step's
-// fragments are loaded before the current step's DMMAs are issued.
-template <bool BT, bool NORM, int NT>
+// K is padded to a multiple of 4 and N to 8*NT per warp by zero-filled shared memory, so the loops carry no
+// bounds tests (GUARD = true restores a run-time tile count ntc <= NT for the one product whose B operand is not
+// padded that far).  The next k-step's fragments are loaded before the current step's DMMAs are issued.
+template <bool BT, bool NORM, bool GUARD, int NT>
 __device__ __forceinline__ void tile_gemm(double (&acc)[NT][2], const double* __restrict__ As, int apitch,
                                           const double* __restrict__ Bs, int bpitch, int mt, int K4, int nt0, int ntc, int lane,
                                           const double* __restrict__ mu, const double* __restrict__ is)
@@ -192,32 +205,34 @@ __device__ __forceinline__ void tile_gemm(double (&acc)[NT][2], const double* __
   const int g = lane >> 2, q = lane & 3;
 #pragma unroll
   for (int nt = 0; nt < NT; nt++) { acc[nt][0] = 0.0; acc[nt][1] = 0.0; }
-  const double* arow = As + (size_t)(8 * mt + g) * apitch + q;
-  const double* bbase = BT ? Bs + (size_t)q * bpitch + 8 * nt0 + g : Bs + (size_t)(8 * nt0 + g) * bpitch + q;
+  const double* ap = As + (size_t)(8 * mt + g) * apitch + q;
+  const double* bp = BT ? Bs + (size_t)q * bpitch + 8 * nt0 + g : Bs + (size_t)(8 * nt0 + g) * bpitch + q;
   const int bstep_k = BT ? 4 * bpitch : 4;
   const int bstep_n = BT ? 8 : 8 * bpitch;
-  double a_cur = arow[0];
-  if (NORM) a_cur = (a_cur - mu[q]) * is[q];
+  const double* mup = mu + q;
+  const double* isp = is + q;
+  double a_cur = ap[0];
+  if (NORM) a_cur = (a_cur - mup[0]) * isp[0];
   double b_cur[NT];
 #pragma unroll
-  for (int nt = 0; nt < NT; nt++) b_cur[nt] = (nt < ntc) ? bbase[nt * bstep_n] : 0.0;
-  for (int k0 = 0; k0 < K4; k0 += 4) {
-    double a_nxt = 0.0, b_nxt[NT];
-    const bool more = (k0 + 4 < K4);
-    if (more) {
-      a_nxt = arow[k0 + 4];
-      if (NORM) a_nxt = (a_nxt - mu[k0 + 4 + q]) * is[k0 + 4 + q];
-    }
-    const double* bk = bbase + (size_t)(k0 / 4 + 1) * bstep_k;
+  for (int nt = 0; nt < NT; nt++) b_cur[nt] = (!GUARD || nt < ntc) ? bp[nt * bstep_n] : 0.0;
+  for (int k0 = 4; k0 < K4; k0 += 4) {
+    ap += 4; bp += bstep_k;
+    double a_nxt = ap[0];
+    if (NORM) { mup += 4; isp += 4; a_nxt = (a_nxt - mup[0]) * isp[0]; }
+    double b_nxt[NT];
 #pragma unroll
-    for (int nt = 0; nt < NT; nt++) b_nxt[nt] = (more && nt < ntc) ? bk[nt * bstep_n] : 0.0;
+    for (int nt = 0; nt < NT; nt++) b_nxt[nt] = (!GUARD || nt < ntc) ? bp[nt * bstep_n] : 0.0;
 #pragma unroll
     for (int nt = 0; nt < NT; nt++)
-      if (nt < ntc) dmma884(acc[nt][0], acc[nt][1], a_cur, b_cur[nt]);
+      if (!GUARD || nt < ntc) dmma884(acc[nt][0], acc[nt][1], a_cur, b_cur[nt]);
     a_cur = a_nxt;
 #pragma unroll
     for (int nt = 0; nt < NT; nt++) b_cur[nt] = b_nxt[nt];
   }
+#pragma unroll
+  for (int nt = 0; nt < NT; nt++)
+    if (!GUARD || nt < ntc) dmma884(acc[nt][0], acc[nt][1], a_cur, b_cur[nt]);
 }
 
 // MODE: PP_MLP_FORWARD (energies only), PP_MLP_TRAIN (two-phase backward: c per structure given),
@@ -241,7 +256,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
   // ---- one-time staging: weights (zero padded), constant columns, transfer ids, input scaling ----------------
   for (int l = 0; l < L; l++) {
     const int n_in = p.n[l], n_out = p.n[l + 1], kp = p.kpitch[l];
-    const int rows = (l == L - 1) ? 1 : round_up(n_out, 8);
+    const int rows = p.ws_rows[l];
     double* Ws = sm + p.ws_off[l];
     const double* src = net.params + net.w_off[l];
     for (int r = warp; r < rows; r += MLP_WARPS)
@@ -348,26 +363,22 @@ mlp_kernel(MlpArgs a, MlpPlan p)
       double acc[NT][2];
       for (int l = 0; l < L - 1; l++) {
         const int n_in = p.n[l], n_out = p.n[l + 1];
-        const int ntl = (n_out + 7) >> 3;
-        const int nt0 = half ? (ntl + 1) >> 1 : 0;
-        const int ntc = half ? ntl - nt0 : (ntl + 1) >> 1;
-        if (l == 0) tile_gemm<false, true, NT>(acc, X, kp0, sm + p.ws_off[0], kp0, mt, round_up(n_in + 1, 4), nt0, ntc, lane, mu, is);
-        else tile_gemm<false, false, NT>(acc, sm + p.hs_off[l], p.kpitch[l], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_in + 1, 4), nt0, ntc, lane, mu, is);
+        const int nt0 = half * NT;
+        if (l == 0) tile_gemm<false, true, false, NT>(acc, X, kp0, sm + p.ws_off[0], kp0, mt, round_up(n_in + 1, 4), nt0, NT, lane, mu, is);
+        else tile_gemm<false, false, false, NT>(acc, sm + p.hs_off[l], p.kpitch[l], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_in + 1, 4), nt0, NT, lane, mu, is);
         double* Hn = sm + p.hs_off[l + 1] + (size_t)(8 * mt + g) * p.kpitch[l + 1];
         double* Dn = sm + p.ds_off[l + 1] + (size_t)(8 * mt + g) * p.dpitch[l + 1];
         const int* tfl = tfs + net.node_off[l];
 #pragma unroll
         for (int nt = 0; nt < NT; nt++) {
-          if (nt < ntc) {
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-              const int n = 8 * (nt0 + nt) + 2 * q + h;
-              if (n < n_out) {
-                double d;
-                double t = pp_transfer(tfl[n], acc[nt][h], d, a.tanh_table);
-                Hn[n] = t;
-                if (BACKWARD) Dn[n] = d;
-              }
+          for (int h = 0; h < 2; h++) {
+            const int n = 8 * (nt0 + nt) + 2 * q + h;
+            if (n < n_out) {
+              double d;
+              double t = pp_transfer(tfl[n], acc[nt][h], d, a.tanh_table);
+              Hn[n] = t;
+              if (BACKWARD) Dn[n] = d;
             }
           }
         }
@@ -427,9 +438,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
       if (L >= 2) {
         {
           const int n_h = p.n[L - 1];
-          const int ntl = (n_h + 7) >> 3;
-          const int nt0 = half ? (ntl + 1) >> 1 : 0;
-          const int ntc = half ? ntl - nt0 : (ntl + 1) >> 1;
+          const int nt0 = half * NT, ntc = NT;
           double* Dr = sm + p.ds_off[L - 1] + (size_t)(8 * mt + g) * p.dpitch[L - 1];
           const double* wo = sm + p.ws_off[L - 1];
           const double c = cvec[8 * mt + g];
@@ -440,19 +449,15 @@ mlp_kernel(MlpArgs a, MlpPlan p)
         for (int l = L - 2; l >= 1; l--) {
           // delta_l = (delta_{l+1} * W_l[:, :n_l]) .* T'(z_l)
           const int n_l = p.n[l], n_up = p.n[l + 1];
-          const int ntl = (n_l + 7) >> 3;
-          const int nt0 = half ? (ntl + 1) >> 1 : 0;
-          const int ntc = half ? ntl - nt0 : (ntl + 1) >> 1;
-          tile_gemm<true, false, NT>(acc, sm + p.ds_off[l + 1], p.dpitch[l + 1], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_up, 4), nt0, ntc, lane, mu, is);
+          const int nt0 = half * NT;
+          tile_gemm<true, false, false, NT>(acc, sm + p.ds_off[l + 1], p.dpitch[l + 1], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_up, 4), nt0, NT, lane, mu, is);
           double* Dr = sm + p.ds_off[l] + (size_t)(8 * mt + g) * p.dpitch[l];
 #pragma unroll
           for (int nt = 0; nt < NT; nt++) {
-            if (nt < ntc) {
 #pragma unroll
-              for (int h = 0; h < 2; h++) {
-                const int n = 8 * (nt0 + nt) + 2 * q + h;
-                if (n < n_l) Dr[n] *= acc[nt][h];
-              }
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * (nt0 + nt) + 2 * q + h;
+              if (n < n_l) Dr[n] *= acc[nt][h];
             }
           }
           pair_barrier(mt);
@@ -469,7 +474,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
           const int hc = half ? ntl - h0 : (ntl + 1) >> 1;
           for (int c0 = 0; c0 < hc; c0 += NT) {
             const int ntc = min(NT, hc - c0);
-            tile_gemm<true, false, NT>(acc, sm + p.ds_off[1], p.dpitch[1], sm + p.ws_off[0], kp0, mt, round_up(p.n[1], 4), h0 + c0, ntc, lane, mu, is);
+            tile_gemm<true, false, true, NT>(acc, sm + p.ds_off[1], p.dpitch[1], sm + p.ws_off[0], kp0, mt, round_up(p.n[1], 4), h0 + c0, ntc, lane, mu, is);
             if (r < nvalid) {
 #pragma unroll
               for (int nt = 0; nt < NT; nt++) {
@@ -518,17 +523,26 @@ mlp_kernel(MlpArgs a, MlpPlan p)
           if (d.layer == 0) {
             const double* Hl = X + d.b_off + g;                     // B(k = atom, n = input) = normalised descriptor
             const double m = mu[d.b_off + g], sc = is[d.b_off + g];
+            const double* pa = Dl + (size_t)q * d.dp;
+            const double* pb = Hl + (size_t)q * d.kp;
+            const int sa = 4 * d.dp, sb = 4 * d.kp;
+#pragma unroll 4
             for (int k0 = 0; k0 < TM; k0 += 4) {
-              const double av = Dl[(size_t)(k0 + q) * d.dp];
-              const double bv = (Hl[(size_t)(k0 + q) * d.kp] - m) * sc;
+              const double av = *pa;
+              const double bv = (*pb - m) * sc;
+              pa += sa; pb += sb;
               dmma884(c0, c1, av, bv);
             }
           } else {
             const double* Hl = sm + d.b_off + g;
+            const double* pa = Dl + (size_t)q * d.dp;
+            const double* pb = Hl + (size_t)q * d.kp;
+            const int sa = 4 * d.dp, sb = 4 * d.kp;
 #pragma unroll 4
             for (int k0 = 0; k0 < TM; k0 += 4) {
-              const double av = Dl[(size_t)(k0 + q) * d.dp];
-              const double bv = Hl[(size_t)(k0 + q) * d.kp];
+              const double av = *pa;
+              const double bv = *pb;
+              pa += sa; pb += sb;
               dmma884(c0, c1, av, bv);
             }
           }
@@ -639,7 +653,7 @@ int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launc
   const bool gradw = (mode == PP_MLP_TRAIN || mode == PP_MLP_FUSED);
   if (!gradw && grid > n_tiles) grid = n_tiles;   // gradient modes: every CTA writes its (possibly zero) partial
   if (grid == 0) return 0;
-  const bool wide = max_hidden > 64;                                         // more than 4 n-tiles per warp of a pair
+  const int NTsel = plan_nt(net);
   const bool many = (plan.n_dw_tiles + MLP_WARPS - 1) / MLP_WARPS > 6;
 #define PP_LAUNCH(MODE_, NT_, OWN_)                                                                             \
   {                                                                                                             \
@@ -647,24 +661,19 @@ int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launc
     PP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes));        \
     k<<<grid, MLP_THREADS, plan.smem_bytes, st>>>(a, plan);                                                     \
   }
-#define PP_LAUNCH_GRAD(MODE_)                                    \
+#define PP_LAUNCH_NT(MODE_, OWN_)                                \
   {                                                              \
-    if (wide && many) PP_LAUNCH(MODE_, 8, 16)                    \
-    else if (wide) PP_LAUNCH(MODE_, 8, 6)                        \
-    else if (many) PP_LAUNCH(MODE_, 4, 16)                       \
-    else PP_LAUNCH(MODE_, 4, 6)                                  \
+    if (NTsel == 2) PP_LAUNCH(MODE_, 2, OWN_)                    \
+    else if (NTsel == 3) PP_LAUNCH(MODE_, 3, OWN_)               \
+    else if (NTsel == 4) PP_LAUNCH(MODE_, 4, OWN_)               \
+    else PP_LAUNCH(MODE_, 8, OWN_)                               \
   }
-  if (mode == PP_MLP_FORWARD) {
-    if (wide) PP_LAUNCH(PP_MLP_FORWARD, 8, 1) else PP_LAUNCH(PP_MLP_FORWARD, 4, 1)
-  } else if (mode == PP_MLP_INPUT_GRAD) {
-    if (wide) PP_LAUNCH(PP_MLP_INPUT_GRAD, 8, 1) else PP_LAUNCH(PP_MLP_INPUT_GRAD, 4, 1)
-  } else if (mode == PP_MLP_TRAIN) {
-    PP_LAUNCH_GRAD(PP_MLP_TRAIN)
-  } else {
-    PP_LAUNCH_GRAD(PP_MLP_FUSED)
-  }
+  if (mode == PP_MLP_FORWARD) PP_LAUNCH_NT(PP_MLP_FORWARD, 1)
+  else if (mode == PP_MLP_INPUT_GRAD) PP_LAUNCH_NT(PP_MLP_INPUT_GRAD, 1)
+  else if (mode == PP_MLP_TRAIN) { if (many) PP_LAUNCH_NT(PP_MLP_TRAIN, 16) else PP_LAUNCH_NT(PP_MLP_TRAIN, 6) }
+  else { if (many) PP_LAUNCH_NT(PP_MLP_FUSED, 16) else PP_LAUNCH_NT(PP_MLP_FUSED, 6) }
 #undef PP_LAUNCH
-#undef PP_LAUNCH_GRAD
+#undef PP_LAUNCH_NT
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   return 0;
