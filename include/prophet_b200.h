@@ -137,6 +137,23 @@ int pp_comm_init(pp_context* ctx, int nranks, int rank, const void* unique_id_12
 int pp_comm_rank(pp_context* ctx);
 int pp_comm_size(pp_context* ctx);
 
+/* ---- descriptor statistics without allocation ------------------------------------------------------------------ */
+/* No counterpart in the reference (it has no device memory to manage).
+ * For callers that must not allocate device memory -- a host program whose own pool already owns the GPU's memory,
+ * or a time-critical loop that cannot tolerate the device-wide synchronisation cudaMalloc/cudaFree may cause.
+ * Computes, for a row-major device matrix [n_rows][n_cols] (e.g. descriptors, one atom per row):
+ *     squared == 0 :  sums_out[k] = sum_r M[r][k]
+ *     squared != 0 :  sums_out[k] = sum_r (M[r][k] - shift[k])^2      (shift_dev may be NULL = 0)
+ * i.e. the two reductions of Potential::Precondition (Potential.cpp:404-455), with the intermediate per-block sums
+ * in a fixed 256 KiB array inside the library instead of allocated scratch.  Limits and rules:
+ *   - n_cols <= 512, otherwise the call fails with an error (use pp_precondition, which allocates);
+ *   - the array is held by every GPU that loads the library until the process exits;
+ *   - one array per GPU, shared by all calls: calls that could overlap on the same GPU must be serialised by the caller;
+ *   - the first call on a GPU resolves the array's address (a set-up step): make it before any stream capture.
+ * All pointers are DEVICE pointers; `stream` is a cudaStream_t (NULL = default stream); the call does not synchronise. */
+int pp_column_sums_static(int device, const double* matrix_dev, long long n_rows, int n_cols,
+                          const double* shift_dev, int squared, double* sums_out_dev, void* stream);
+
 /* ---- instrumentation --------------------------------------------------------------------------------------- */
 /* number of kernels this library launched since the context was created */
 long long pp_kernel_launches(pp_context* ctx);
