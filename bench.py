@@ -224,10 +224,129 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = reference_epoch_rate(cores=1, structures_per_core=args.cpu_sample, iters=6)
-        print(json.dumps(out))
     ctx.close()
+    if not args.no_md:
+        # pair_nn (second metric of BASELINE.json); at N > 1 every rank runs an independent replica of the box
+        md = run_md_bench(torch, capi, synth, local_rank, args.md_cells, args.md_steps, 2)
+        if dist is not None:
+            t = torch.tensor([md["ms_per_step"], md["e2e"]["ms_per_step"]], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            md["ms_per_step"], md["e2e"]["ms_per_step"] = [float(v) for v in t.cpu()]
+            md["value"] = world * md["atoms_local"] / (md["ms_per_step"] * 1e-3)
+            md["e2e"]["value"] = world * md["atoms_local"] / (md["e2e"]["ms_per_step"] * 1e-3)
+            md["replicas"] = world
+        if rank == 0:
+            if world == 1 and not args.no_cpu_baseline:
+                md["cpu_baseline"] = reference_md_rate()
+            out["pair_nn"] = md
+    if rank == 0:
+        print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# second headline metric: pair_nn atom-steps/s (C5: diamond-Si supercell, C2 rows, 50-40-40-1 net)
+def md_system(synth, cells, seed=5, skin=1.0):
+    cfg = synth.config_c5(cells)
+    cell, cart, Z, _, _ = synth.make_structure(cfg, seed)
+    x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + skin)
+    return cfg, np.ascontiguousarray(x), nlocal
+
+
+def run_md_bench(torch, capi, synth, device, cells, steps, warmup):
+    """pp_md_build_neighbors once (LAMMPS rebuilds every 10 steps, pair_nn.cpp:276), then `steps` calls of the
+    PairNN::compute equivalent: device-resident (value) and through host buffers (e2e)."""
+    cfg, x, nlocal = md_system(synth, cells)
+    ntotal = len(x)
+    ctx = capi.Context(device)
+    ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+    net = synth.random_network(cfg, 14, 1)
+    mean = 0.1 * synth.normal(9, cfg.NG, 3); scale = 0.5 + np.abs(synth.normal(9, cfg.NG, 4))
+    ctx.set_network(0, net["sizes"], net["params"], mean, scale)
+    ctx.md_set_types([0, 0])
+    types = np.ones(ntotal, dtype=np.int32)
+    t0 = time.perf_counter()
+    ctx.md_build_neighbors(x, types, nlocal, cfg.rcut + 1.0)
+    build_s = time.perf_counter() - t0
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    dev = torch.device("cuda", device)
+    xd = torch.from_numpy(x).to(dev)
+    fd = torch.zeros_like(xd)
+    ed = torch.zeros(1, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    for _ in range(warmup):
+        ctx.md_step_device(xd.data_ptr(), fd.data_ptr(), ed.data_ptr())
+    torch.cuda.synchronize()
+    ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
+    l0 = ctx.kernel_launches
+    ev0.record(stream)
+    for _ in range(steps):
+        ctx.md_step_device(xd.data_ptr(), fd.data_ptr(), ed.data_ptr())
+    ev1.record(stream)
+    ev1.synchronize()
+    dev_ms = ev0.elapsed_time(ev1) / steps
+    launches = ctx.kernel_launches - l0
+    # e2e: pinned host positions in, forces / energies out, every step
+    x_pin = torch.from_numpy(x).pin_memory()
+    f_pin = torch.zeros(ntotal, 3, dtype=torch.float64).pin_memory()
+    ea_pin = torch.zeros(max(nlocal, 1), dtype=torch.float64).pin_memory()
+    for _ in range(max(1, warmup - 1)):
+        ctx.md_step_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
+    phases = []
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ctx.md_step_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
+        phases.append((ctx.phase_ms(4), ctx.phase_ms(5), ctx.phase_ms(6)))
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / steps
+    ph = np.median(np.array(phases), axis=0)
+    # algorithmic flops per atom-step (SURVEY.md section 8d, C2 rows, measured mean neighbour count n)
+    off, _nb = None, None
+    nneigh = None
+    out = {"metric": "pair_nn atom-steps/sec", "value": nlocal / (dev_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": dev_ms,
+           "atoms_local": int(nlocal), "atoms_ghost": int(ntotal - nlocal), "steps": steps, "warmup": warmup,
+           "workload": "C5: diamond Si %dx%dx%d cells, Rcut 6 + skin 1, 50 descriptors, net 50-40-40-1" % (cells, cells, cells),
+           "e2e": {"value": nlocal / (e2e_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": e2e_ms,
+                   "h2d_bytes_per_step": 2 * 24 * ntotal, "d2h_bytes_per_step": 24 * ntotal + 8 * nlocal + 8},
+           "phases_ms": {"descriptors": float(ph[0]), "network": float(ph[1]), "forces": float(ph[2])},
+           "neighbor_build_s": build_s, "gpu_launches": int(launches)}
+    peaks = _fp64_peaks()
+    flops_desc, flops_force = 0.41e6, 1.21e6      # per atom at n = 45 (SURVEY 8d); the dominant kernel is the force kernel
+    out["roofline"] = {"bound": "fp64-fma", "kernel": "md_force_kernel", "achieved": flops_force * nlocal / (ph[2] * 1e-3) / 1e12,
+                       "peak": peaks["fp64_fma_tflops"], "unit": "TFLOP/s",
+                       "frac": flops_force * nlocal / (ph[2] * 1e-3) / 1e12 / peaks["fp64_fma_tflops"],
+                       "algorithmic_flops_per_atom": flops_force, "peak_source": peaks["source"]}
+    ctx.close()
+    return out
+
+
+def reference_md_rate(cells=2):
+    """atom-steps/s of the reference's PairNN::compute call chain on one host core (oracle/_ref/ref_driver md)."""
+    from prophet_b200 import ckpt, synth
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+    if not os.path.exists(exe):
+        return {"value": None, "unit": "atom-steps/s", "cores": 1, "kind": "reference", "sample": "oracle/_ref/ref_driver missing"}
+    cfg, x, nlocal = md_system(synth, cells)
+    numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+    net = synth.random_network(cfg, 14, 1)
+    d = tempfile.mkdtemp(prefix="ppmd_")
+    try:
+        ckpt.write_checkpoint(os.path.join(d, "pot_Si"), "Si", ["Si"], {"G1": [], "G2": cfg.G2, "G3": [], "G4": cfg.G4},
+                              np.zeros(cfg.NG), np.ones(cfg.NG), 0.0, 1.0, net["sizes"], net["params"], header_precision=17)
+        with open(os.path.join(d, "case.txt"), "w") as f:
+            f.write("Rcut %r\nntypes 1\ncoeff 1 pot_Si\natoms %d %d\n" % (float(cfg.rcut), nlocal, len(x) - nlocal))
+            for r in x:
+                f.write("1 %r %r %r\n" % (float(r[0]), float(r[1]), float(r[2])))
+            for i in range(nlocal):
+                f.write("neigh %d %d %s\n" % (i, numneigh[i], " ".join(str(j) for j in flat[offsets[i]:offsets[i + 1]])))
+        r = subprocess.run([exe, "md", "case.txt", "out.bin"], cwd=d, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        m = re.search(r"MD_COMPUTE_SECONDS ([0-9.eE+-]+)", r.stdout)
+        secs = float(m.group(1)) if m else None
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    return {"value": (nlocal / secs) if secs else None, "unit": "atom-steps/s", "cores": 1, "kind": "reference",
+            "sample": "1 step, %d local + %d ghost Si atoms, unmodified reference classes driven as PairNN::compute does "
+                      "(oracle/_ref/ref_driver md)" % (nlocal, len(x) - nlocal), "seconds": secs}
 
 
 class _host_optimizer:
@@ -373,6 +492,9 @@ def main():
     ap.add_argument("--structures", type=int, default=N_STRUCT_PER_GPU, help="structures per GPU (C2 = 10000)")
     ap.add_argument("--cpu-sample", type=int, default=24, help="structures per host core for the CPU arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-md", action="store_true", help="skip the pair_nn (MD) section")
+    ap.add_argument("--md-cells", type=int, default=50, help="diamond-Si supercell edge in unit cells (C5 = 50 -> 1M atoms)")
+    ap.add_argument("--md-steps", type=int, default=5)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

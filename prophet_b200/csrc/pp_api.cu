@@ -110,6 +110,11 @@ struct pp_context {
   DevBuf<int> d_md_rows[PP_MAX_ELEM];
   int md_rows_n[PP_MAX_ELEM] = {0, 0, 0, 0};
   std::vector<int> h_md_elem;
+  // cell-list work space and resident-step buffers
+  DevBuf<int> d_cell_of, d_cell_count, d_sorted, d_counts;
+  DevBuf<long long> d_cell_start, d_scan_sums, d_scan_total;
+  DevBuf<double> d_sum_partial, d_etotal;
+  bool md_list_resident = false;
 
   PPComm comm;
 };
@@ -163,6 +168,8 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_stat_partial.release(); c->d_stat_sums.release(); c->d_count.release();
   c->d_x.release(); c->d_f.release(); c->d_Gmd.release(); c->d_dEdG.release(); c->d_eatom.release();
   c->d_md_elem.release(); c->d_neigh.release(); c->d_neigh_off.release();
+  c->d_cell_of.release(); c->d_cell_count.release(); c->d_sorted.release(); c->d_counts.release();
+  c->d_cell_start.release(); c->d_scan_sums.release(); c->d_scan_total.release(); c->d_sum_partial.release(); c->d_etotal.release();
   for (int e = 0; e < PP_MAX_ELEM; e++) {
     c->d_rows[e].release(); c->d_md_rows[e].release();
     c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release();
@@ -891,7 +898,7 @@ static int md_upload_atoms(pp_context* c, const double* x, const int* type, int 
   return 0;
 }
 
-static int md_run(pp_context* c)
+static int md_run(pp_context* c, const double* x_dev, double* f_dev)
 {
   cudaStream_t st = c->stream;
   const int nlocal = c->md_nlocal;
@@ -899,13 +906,13 @@ static int md_run(pp_context* c)
   memset(&a, 0, sizeof(a));
   a.spec = c->d_spec;
   a.nlocal = nlocal;
-  a.x = c->d_x.p;
+  a.x = x_dev;
   a.elem = c->d_md_elem.p;
   a.neigh_offsets = c->d_neigh_off.p;
   a.neigh = c->d_neigh.p;
   a.G = c->d_Gmd.p;
   a.dEdG = c->d_dEdG.p;
-  a.f = c->d_f.p;
+  a.f = f_dev;
   a.overflow = c->d_overflow.p;
   if (tick(c, 0)) return 1;
   if (ppk_md_desc(c->spec, a, &c->md_cap, st, &c->launches)) return 1;
@@ -949,7 +956,8 @@ extern "C" int pp_md_compute(pp_context* c, const double* x, const int* type, in
   if (nn) PP_CUDA(cudaMemcpyAsync(c->d_neigh.p, neigh_flat, nn * sizeof(int), cudaMemcpyHostToDevice, st));
   c->md_nneigh = nn;
   PP_CUDA(cudaMemsetAsync(c->d_f.p, 0, 3 * (size_t)ntotal * sizeof(double), st));
-  if (md_run(c)) return 1;
+  c->md_list_resident = false;
+  if (md_run(c, c->d_x.p, c->d_f.p)) return 1;
   std::vector<double> f(3 * (size_t)ntotal), ea(std::max(nlocal, 1));
   PP_CUDA(cudaMemcpyAsync(f.data(), c->d_f.p, f.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
   PP_CUDA(cudaMemcpyAsync(ea.data(), c->d_eatom.p, nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -964,25 +972,108 @@ extern "C" int pp_md_compute(pp_context* c, const double* x, const int* type, in
   return 0;
 }
 
-extern "C" int pp_md_build_neighbors(pp_context*, const double*, const int*, int, int, double)
+// GPU cell list -> device-resident full neighbour list (LAMMPS' test rsq < cutneigh^2 over locals + ghosts)
+extern "C" int pp_md_build_neighbors(pp_context* c, const double* x, const int* type, int nlocal, int nghost, double cutneigh)
 {
-  pp_set_error("pp_md_build_neighbors: not implemented yet");
-  return 1;
+  if (nets_ready(c)) return 1;
+  PP_REQUIRE(!c->type_to_elem.empty(), "pp_md_build_neighbors: call pp_md_set_types first");
+  PP_REQUIRE(nlocal >= 0 && nghost >= 0 && x && type && cutneigh > 0, "pp_md_build_neighbors: bad arguments");
+  PP_REQUIRE(cutneigh >= c->spec.Rcut, "pp_md_build_neighbors: cutneigh %g is smaller than Rcut %g", cutneigh, c->spec.Rcut);
+  PP_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int ntotal = nlocal + nghost;
+  if (md_upload_atoms(c, x, type, nlocal, nghost)) return 1;
+  // bounding box -> cells of edge >= cutneigh
+  CellGrid g;
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (int i = 0; i < ntotal; i++)
+    for (int k = 0; k < 3; k++) {
+      double v = x[3 * (size_t)i + k];
+      if (v < lo[k]) lo[k] = v;
+      if (v > hi[k]) hi[k] = v;
+    }
+  long long ncells = 1;
+  for (int k = 0; k < 3; k++) {
+    if (ntotal == 0) { lo[k] = 0; hi[k] = 1; }
+    double L = hi[k] - lo[k];
+    int n = (int)floor(L / cutneigh);
+    if (n < 1) n = 1;
+    if (n > 1024) n = 1024;
+    g.n[k] = n;
+    g.lo[k] = lo[k];
+    g.inv[k] = L > 0 ? n / L : 0.0;
+    ncells *= n;
+  }
+  if (c->d_cell_of.ensure(std::max(ntotal, 1), 0, st) || c->d_sorted.ensure(std::max(ntotal, 1), 0, st) ||
+      c->d_cell_count.ensure(ncells, 0, st) || c->d_cell_start.ensure(ncells + 1, 0, st) || c->d_counts.ensure(std::max(nlocal, 1), 0, st) ||
+      c->d_scan_sums.ensure(std::max<long long>(ncells, nlocal) / 1024 + 8, 0, st) || c->d_scan_total.ensure(1, 0, st) ||
+      c->d_neigh_off.ensure(nlocal + 1, 0, st))
+    return 1;
+  CellWork w;
+  w.cell_of = c->d_cell_of.p; w.cell_count = c->d_cell_count.p; w.cell_start = c->d_cell_start.p; w.sorted = c->d_sorted.p;
+  w.counts = c->d_counts.p; w.block_sums = c->d_scan_sums.p; w.total = c->d_scan_total.p;
+  if (ppk_build_cell_neighbors(c->d_x.p, nlocal, ntotal, g, cutneigh, w, st, &c->launches)) return 1;
+  if (ppk_scan_counts(c->d_counts.p, nlocal, c->d_neigh_off.p, w, st, &c->launches)) return 1;
+  long long total = 0;
+  PP_CUDA(cudaMemcpyAsync(&total, c->d_scan_total.p, sizeof(long long), cudaMemcpyDeviceToHost, st));
+  PP_CUDA(cudaStreamSynchronize(st));
+  if (c->d_neigh.ensure(std::max<long long>(total, 1), 0, st)) return 1;
+  if (ppk_fill_cell_neighbors(c->d_x.p, nlocal, g, cutneigh, w, c->d_neigh_off.p, c->d_neigh.p, st, &c->launches)) return 1;
+  PP_CUDA(cudaStreamSynchronize(st));
+  c->md_nneigh = total;
+  c->md_list_resident = true;
+  return 0;
 }
-extern "C" int pp_md_get_neighbors(pp_context*, long long*, int*, long long*)
+
+extern "C" int pp_md_get_neighbors(pp_context* c, long long* neigh_offsets, int* neigh_flat, long long* n_total)
 {
-  pp_set_error("pp_md_get_neighbors: not implemented yet");
-  return 1;
+  PP_REQUIRE(c && c->md_list_resident, "pp_md_get_neighbors: no resident list (call pp_md_build_neighbors)");
+  if (n_total) *n_total = c->md_nneigh;
+  if (neigh_offsets) PP_CUDA(cudaMemcpyAsync(neigh_offsets, c->d_neigh_off.p, (c->md_nlocal + 1) * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  if (neigh_flat && c->md_nneigh) PP_CUDA(cudaMemcpyAsync(neigh_flat, c->d_neigh.p, c->md_nneigh * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
 }
-extern "C" int pp_md_step(pp_context*, const double*, double*, double*, double*)
+
+static int md_energy_total(pp_context* c, double* out_dev)
 {
-  pp_set_error("pp_md_step: not implemented yet");
-  return 1;
+  if (c->d_sum_partial.ensure(128, 0, c->stream)) return 1;
+  return ppk_sum(c->d_eatom.p, c->md_nlocal, c->out_mean, c->d_sum_partial.p, out_dev, c->stream, &c->launches);
 }
-extern "C" int pp_md_step_device(pp_context*, const double*, double*, double*)
+
+// One MD step on the resident list with device-resident positions / forces (forces are accumulated into f_dev).
+extern "C" int pp_md_step_device(pp_context* c, const double* x_dev, double* f_dev, double* etotal_dev)
 {
-  pp_set_error("pp_md_step_device: not implemented yet");
-  return 1;
+  PP_REQUIRE(c && c->md_list_resident, "pp_md_step_device: no resident list (call pp_md_build_neighbors)");
+  PP_REQUIRE(x_dev && f_dev, "pp_md_step_device: NULL device pointer");
+  PP_CUDA(cudaSetDevice(c->device));
+  if (md_run(c, x_dev, f_dev)) return 1;
+  if (etotal_dev && md_energy_total(c, etotal_dev)) return 1;
+  return 0;
+}
+
+// One MD step on the resident list: x uploaded, forces downloaded and ADDED into f_inout, energies downloaded.
+extern "C" int pp_md_step(pp_context* c, const double* x, double* f_inout, double* eatom_out, double* etotal_out)
+{
+  PP_REQUIRE(c && c->md_list_resident, "pp_md_step: no resident list (call pp_md_build_neighbors)");
+  PP_REQUIRE(x, "pp_md_step: NULL positions");
+  PP_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int ntotal = c->md_ntotal, nlocal = c->md_nlocal;
+  if (c->d_etotal.ensure(1, 0, st)) return 1;
+  PP_CUDA(cudaMemcpyAsync(c->d_x.p, x, 3 * (size_t)ntotal * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (f_inout) PP_CUDA(cudaMemcpyAsync(c->d_f.p, f_inout, 3 * (size_t)ntotal * sizeof(double), cudaMemcpyHostToDevice, st));
+  else PP_CUDA(cudaMemsetAsync(c->d_f.p, 0, 3 * (size_t)ntotal * sizeof(double), st));
+  if (md_run(c, c->d_x.p, c->d_f.p)) return 1;
+  if (md_energy_total(c, c->d_etotal.p)) return 1;
+  if (f_inout) PP_CUDA(cudaMemcpyAsync(f_inout, c->d_f.p, 3 * (size_t)ntotal * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (eatom_out) PP_CUDA(cudaMemcpyAsync(eatom_out, c->d_eatom.p, nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));
+  double et = 0.0;
+  PP_CUDA(cudaMemcpyAsync(&et, c->d_etotal.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+  PP_CUDA(cudaStreamSynchronize(st));
+  tock(c, 0, 1, 4); tock(c, 1, 2, 5); tock(c, 2, 3, 6);
+  if (etotal_out) *etotal_out = et;
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -109,3 +109,24 @@ int ppk_column_stats(const double* G, int NG, const int* rows, int M, const int*
                      cudaStream_t st, long long* launches);
 
 void ppk_make_tanh_table(std::vector<double>& table);
+
+// ---- MD harness: GPU cell list and full neighbour list (pp_cell.cu) ------------------------------------------
+struct CellGrid {
+  double lo[3], inv[3];   // cell index = (x - lo) * inv, clamped
+  int n[3];
+};
+struct CellWork {
+  int* cell_of;           // [ntotal]
+  int* cell_count;        // [ncells]
+  long long* cell_start;  // [ncells+1]
+  int* sorted;            // [ntotal] atoms grouped by cell, ascending index inside a cell
+  int* counts;            // [nlocal] neighbours per local atom
+  long long* block_sums;  // scan scratch
+  long long* total;       // [1]
+};
+int ppk_build_cell_neighbors(const double* x_dev, int nlocal, int ntotal, const CellGrid& g, double cutneigh, CellWork& w,
+                             cudaStream_t st, long long* launches);
+int ppk_scan_counts(const int* counts, long long n, long long* offsets, CellWork& w, cudaStream_t st, long long* launches);
+int ppk_fill_cell_neighbors(const double* x_dev, int nlocal, const CellGrid& g, double cutneigh, CellWork& w, const long long* offsets,
+                            int* neigh_out, cudaStream_t st, long long* launches);
+int ppk_sum(const double* v, long long n, double add, double* partial, double* out, cudaStream_t st, long long* launches);

@@ -1,0 +1,91 @@
+"""GPU tests of the MD harness path: GPU cell-list neighbour build (checked bit-exact, as sets, against a CPU
+brute-force list using the same comparison) and the resident-list step entry points."""
+import numpy as np
+import pytest
+
+from golden_util import MDCase, rel_err
+from prophet_b200 import capi, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _si_system(reps, seed, skin=1.0):
+    cfg = synth.config_c2(1)
+    cfg.lattice = synth.lattice_si(reps)
+    cell, cart, Z, _, _ = synth.make_structure(cfg, seed)
+    x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + skin)
+    return cfg, x, nlocal
+
+
+def _ctx(cfg, seed=3):
+    net = synth.random_network(cfg, 14, seed)
+    mean = 0.1 * synth.normal(9, cfg.NG, 3); scale = 0.5 + np.abs(synth.normal(9, cfg.NG, 4))
+    ctx = capi.Context(0)
+    ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+    ctx.set_network(0, net["sizes"], net["params"], mean, scale)
+    ctx.set_output_scaling(-0.5, 1.25)
+    ctx.md_set_types([0, 0])
+    return ctx
+
+
+def test_cell_list_neighbors_bit_exact_sets():
+    cfg, x, nlocal = _si_system((3, 3, 3), 11)
+    numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+    ctx = _ctx(cfg)
+    try:
+        ctx.md_build_neighbors(x, np.ones(len(x), dtype=np.int32), nlocal, cfg.rcut + 1.0)
+        off, nb = ctx.md_get_neighbors()
+        assert np.array_equal(np.diff(off), numneigh)
+        for i in range(nlocal):
+            assert np.array_equal(np.sort(nb[off[i]:off[i + 1]]), flat[offsets[i]:offsets[i + 1]]), i
+        # deterministic: a second build yields the identical list, order included
+        ctx.md_build_neighbors(x, np.ones(len(x), dtype=np.int32), nlocal, cfg.rcut + 1.0)
+        off2, nb2 = ctx.md_get_neighbors()
+        assert np.array_equal(off, off2) and np.array_equal(nb, nb2)
+    finally:
+        ctx.close()
+
+
+def test_resident_step_matches_host_list_and_golden():
+    c = MDCase("si_md")
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(1, c.G1, c.G2, c.G3, c.G4, c.rcut)
+        ctx.set_network(0, c.sizes, c.d["params.14"], c.d["in_mean.14"], c.d["in_scale.14"])
+        ctx.set_output_scaling(c.out_mean, c.out_scale)
+        ctx.md_set_types([0, 0])
+        ctx.md_build_neighbors(c.x, c.types, c.nlocal, c.rcut + 1.0)
+        r = ctx.md_step(c.x)
+        assert rel_err(r["eatom"], c.d["eatom"]) < 1e-10
+        assert abs(r["etotal"] - c.d["etotal"][0]) < 1e-10 * abs(c.d["etotal"][0])
+        assert rel_err(r["f"], c.d["f"]) < 1e-10
+        # forces are added into the caller's array
+        f0 = np.full_like(c.x, 2.0)
+        r2 = ctx.md_step(c.x, f=f0)
+        assert rel_err(r2["f"] - 2.0, c.d["f"]) < 1e-9
+    finally:
+        ctx.close()
+
+
+def test_step_device_pointers():
+    import torch
+    cfg, x, nlocal = _si_system((3, 3, 3), 12)
+    ctx = _ctx(cfg)
+    try:
+        types = np.ones(len(x), dtype=np.int32)
+        ctx.md_build_neighbors(x, types, nlocal, cfg.rcut + 1.0)
+        ref = ctx.md_step(x)
+        dev = torch.device("cuda", 0)
+        xd = torch.from_numpy(x).to(dev)
+        fd = torch.zeros_like(xd)
+        ed = torch.zeros(1, dtype=torch.float64, device=dev)
+        torch.cuda.synchronize()
+        ctx.md_step_device(xd.data_ptr(), fd.data_ptr(), ed.data_ptr())
+        torch.cuda.synchronize()
+        import ctypes
+        # the library runs on its own stream: synchronise it through a blocking host call
+        ctx.md_get_neighbors()
+        assert rel_err(fd.cpu().numpy(), ref["f"]) < 1e-10
+        assert abs(float(ed.cpu()[0]) - ref["etotal"]) < 1e-10 * abs(ref["etotal"])
+    finally:
+        ctx.close()
