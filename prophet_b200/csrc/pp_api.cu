@@ -278,6 +278,36 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
       S.ang_prog[k] = prog;
     }
   }
+  // power-basis fast path: every xi an integer power of two below 2^5 and at most two distinct lambdas
+  {
+    S.basis_nb = 0;
+    S.basis_lam[0] = S.basis_lam[1] = 0.0;
+    bool ok = nG4 > 0;
+    int nlam = 0, maxb = 0;
+    for (int k = 0; k < S.NA && ok; k++) {
+      int e = S.ang_xi_int[k];
+      if (!(e >= 1 && (e & (e - 1)) == 0 && e <= 16)) { ok = false; break; }
+      int b = 0;
+      while ((1 << b) < e) b++;
+      maxb = std::max(maxb, b);
+      int g = -1;
+      for (int q = 0; q < nlam; q++) if (S.basis_lam[q] == S.ang_lam[k]) g = q;
+      if (g < 0) {
+        if (nlam == 2) { ok = false; break; }
+        S.basis_lam[nlam++] = S.ang_lam[k];
+      }
+    }
+    if (ok) {
+      S.basis_nb = maxb + 1 <= 3 ? 3 : 5;
+      for (int r = 0; r < nG4; r++) {
+        int k = S.g4_ang[r];
+        int e = S.ang_xi_int[k], b = 0;
+        while ((1 << b) < e) b++;
+        S.g4_bb[r] = b;
+        S.g4_bg[r] = (S.basis_lam[0] == S.ang_lam[k]) ? 0 : 1;
+      }
+    }
+  }
   // squared-distance thresholds equivalent to the reference's tests on d = sqrt(d2) (Structure.cpp:1337)
   {
     auto thr = [](double r) {

@@ -6,7 +6,7 @@
 
 // ---------------------------------------------------------------------------------------------------------
 // K1+K2+K3 fused, periodic structures (training set-up): one warp per atom.
-template <int NR_T, int NA_T>
+template <int NR_T, int NX, bool BASIS>
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 desc_periodic_kernel(PeriodicArgs a)
 {
@@ -34,7 +34,7 @@ desc_periodic_kernel(PeriodicArgs a)
     return;
   }
   pp_finalize_entries<false>(w, a.cap, lane, S, n);
-  pp_descriptor_row<NR_T, NA_T>(w, a.cap, lane, S, false);
+  pp_descriptor_row<NR_T, NX, BASIS>(w, a.cap, lane, S, false);
   double* out = a.G + (size_t)atom * S->NG;
   for (int g = lane; g < S->NG; g += 32) out[g] = w.buf[g];
 }
@@ -75,7 +75,7 @@ neighbors_periodic_kernel(PeriodicArgs a, int s, int pass, int* counts, const in
 
 // ---------------------------------------------------------------------------------------------------------
 // MD (LAMMPS list) descriptors: Structure::Calc_G non-periodic branch (Structure.cpp:1073-1145).
-template <int NR_T, int NA_T>
+template <int NR_T, int NX, bool BASIS>
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 md_desc_kernel(MdArgs a)
 {
@@ -95,13 +95,13 @@ md_desc_kernel(MdArgs a)
     return;
   }
   pp_finalize_entries<false>(w, a.cap, lane, S, n);
-  pp_descriptor_row<NR_T, NA_T>(w, a.cap, lane, S, S->nG3 > 0);
+  pp_descriptor_row<NR_T, NX, BASIS>(w, a.cap, lane, S, S->nG3 > 0);
   double* out = a.G + (size_t)i * S->NG;
   for (int g = lane; g < S->NG; g += 32) out[g] = w.buf[g];
 }
 
 // MD forces: Structure::Get_Forces non-periodic branch (Structure.cpp:429-713) with dE/dG given.
-template <int NR_T, int NA_T>
+template <int NR_T, int NX, bool BASIS>
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 md_force_kernel(MdArgs a)
 {
@@ -124,7 +124,7 @@ md_force_kernel(MdArgs a)
   const double* wrow = a.dEdG + (size_t)i * S->NG;
   for (int g = lane; g < S->NG; g += 32) w.buf[g] = wrow[g];
   __syncwarp();
-  pp_force_entries<NR_T, NA_T>(w, a.cap, lane, S, S->nG3 > 0);
+  pp_force_entries<NR_T, NX, BASIS>(w, a.cap, lane, S, S->nG3 > 0);
   // f[j] -= grad_j ; f[i] += sum_j grad_j   (Structure.cpp:700-706)
   double sx = 0.0, sy = 0.0, sz = 0.0;
   for (int p = lane; p < n; p += 32) {
@@ -144,17 +144,25 @@ md_force_kernel(MdArgs a)
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// template dispatch on the register-tile of the G4 grid
+// template dispatch on the register tile of the G4 grid.
+//   basis path (power-of-two xi, <= 2 lambdas): NR_T in {1,3,5,8} x NB in {3,5}
+//   general path (any xi / lambda):             NR_T in {3,8}     x NA_T = 4, chunked over the grid
 template <typename F>
-static int dispatch_tile(int NR, int NA, F&& f)
+static int dispatch_tile(const DescSpec& hs, F&& f)
 {
-  int nr = NR <= 1 ? 1 : NR <= 3 ? 3 : NR <= 5 ? 5 : 8;
-  int na = NA <= 4 ? 4 : 8;
-#define PP_CASE(R_, A_) if (nr == R_ && na == A_) return f(std::integral_constant<int, R_>(), std::integral_constant<int, A_>());
-  PP_CASE(1, 4) PP_CASE(1, 8) PP_CASE(3, 4) PP_CASE(3, 8) PP_CASE(5, 4) PP_CASE(5, 8) PP_CASE(8, 4) PP_CASE(8, 8)
+  const int NR = hs.NR;
+#define PP_CASE(R_, X_, B_) return f(std::integral_constant<int, R_>(), std::integral_constant<int, X_>(), std::integral_constant<bool, B_>());
+  if (hs.basis_nb > 0) {
+    const int nr = NR <= 1 ? 1 : NR <= 3 ? 3 : NR <= 5 ? 5 : 8;
+    if (hs.basis_nb <= 3) {
+      if (nr == 1) PP_CASE(1, 3, true) if (nr == 3) PP_CASE(3, 3, true) if (nr == 5) PP_CASE(5, 3, true) PP_CASE(8, 3, true)
+    } else {
+      if (nr == 1) PP_CASE(1, 5, true) if (nr == 3) PP_CASE(3, 5, true) if (nr == 5) PP_CASE(5, 5, true) PP_CASE(8, 5, true)
+    }
+  }
+  if (NR <= 3) PP_CASE(3, 4, false)
+  PP_CASE(8, 4, false)
 #undef PP_CASE
-  pp_set_error("internal: no descriptor kernel for tile %dx%d", nr, na);
-  return 1;
 }
 
 static int max_cap_for(int NR, int NG, bool force)
@@ -185,8 +193,8 @@ int ppk_desc_periodic(const DescSpec& hs, PeriodicArgs a, int* cap_io, cudaStrea
     PP_CUDA(cudaMemsetAsync(a.overflow, 0, sizeof(int), st));
     size_t bytes = pp_warp_smem_bytes(cap, hs.NR, hs.NG, false) * DESC_WARPS;
     unsigned grid = (unsigned)((a.n_atoms + DESC_WARPS - 1) / DESC_WARPS);
-    int rc = dispatch_tile(hs.NR, hs.NA, [&](auto R_, auto A_) {
-      auto k = desc_periodic_kernel<decltype(R_)::value, decltype(A_)::value>;
+    int rc = dispatch_tile(hs, [&](auto R_, auto X_, auto B_) {
+      auto k = desc_periodic_kernel<decltype(R_)::value, decltype(X_)::value, decltype(B_)::value>;
       if (set_smem(k, bytes)) return 1;
       k<<<grid, DESC_WARPS * 32, bytes, st>>>(a);
       return 0;
@@ -233,8 +241,8 @@ int ppk_md_desc(const DescSpec& hs, MdArgs a, int* cap_io, cudaStream_t st, long
     PP_CUDA(cudaMemsetAsync(a.overflow, 0, sizeof(int), st));
     size_t bytes = pp_warp_smem_bytes(cap, hs.NR, hs.NG, false) * DESC_WARPS;
     unsigned grid = (unsigned)((a.nlocal + DESC_WARPS - 1) / DESC_WARPS);
-    int rc = dispatch_tile(hs.NR, hs.NA, [&](auto R_, auto A_) {
-      auto k = md_desc_kernel<decltype(R_)::value, decltype(A_)::value>;
+    int rc = dispatch_tile(hs, [&](auto R_, auto X_, auto B_) {
+      auto k = md_desc_kernel<decltype(R_)::value, decltype(X_)::value, decltype(B_)::value>;
       if (set_smem(k, bytes)) return 1;
       k<<<grid, DESC_WARPS * 32, bytes, st>>>(a);
       return 0;
@@ -264,8 +272,8 @@ int ppk_md_force(const DescSpec& hs, MdArgs a, int cap, cudaStream_t st, long lo
   a.cap = cap;
   size_t bytes = pp_warp_smem_bytes(cap, hs.NR, hs.NG, true) * DESC_WARPS;
   unsigned grid = (unsigned)((a.nlocal + DESC_WARPS - 1) / DESC_WARPS);
-  int rc = dispatch_tile(hs.NR, hs.NA, [&](auto R_, auto A_) {
-    auto k = md_force_kernel<decltype(R_)::value, decltype(A_)::value>;
+  int rc = dispatch_tile(hs, [&](auto R_, auto X_, auto B_) {
+    auto k = md_force_kernel<decltype(R_)::value, decltype(X_)::value, decltype(B_)::value>;
     if (set_smem(k, bytes)) return 1;
     k<<<grid, DESC_WARPS * 32, bytes, st>>>(a);
     return 0;

@@ -400,7 +400,217 @@ __device__ inline void pp_g4_block_desc(WarpNbr& w, int cap, int lane, const Des
   __syncwarp();
 }
 
-template <int NR_T, int NA_T>
+
+// ---------------------------------------------------------------------------------------------------------
+// Power-basis fast path for the G4 grid.
+//
+// When every angular key has an integer power-of-two xi = 2^b (b < NB) and at most two distinct lambdas occur
+// (the usual Behler sets: xi in {1,2,4,8,16}, lambda = +-1), the angular factors are members of the small basis
+//     pw_g[b] = max(1 + lam_g c, 0)^(2^b),   g in {0,1}, b in [0, NB)
+// obtained by NB-1 successive squarings per lambda.  Accumulating on the basis, acc[r][g][b] += pw_g[b] * A_r A_r',
+// keeps the pair loop free of branches, selects and run-time exponents: 3 FMA (cos) + 2 FMA + 2(NB-1) squarings +
+// NR multiplies + 2 NR NB FMAs.  Rows pick their (r, g, b) slot once per atom at the end.  Basis slots no row
+// uses are wasted FMAs (level b = 3 for xi in {1,2,4,16}), which is far cheaper than evaluating powers per key.
+
+// Sum `v[i]` over the warp for all i at once by recursive halving: after the call lane l holds in v[0 .. NPAD/32)
+// the warp totals of the slots (NPAD/32)*l + p.  NPAD/2 + NPAD/4 + ... shuffles instead of 5 per value.
+template <int NPAD>
+__device__ __forceinline__ void pp_reduce_scatter(double (&v)[NPAD], int lane)
+{
+  static_assert(NPAD == 32 || NPAD == 64 || NPAD == 128, "NPAD must be 32, 64 or 128");
+#pragma unroll
+  for (int step = 0; step < 5; step++) {
+    const int h = NPAD >> (step + 1);
+    const int m = 16 >> step;
+    const bool up = (lane & m) != 0;
+#pragma unroll
+    for (int i = 0; i < h; i++) {
+      const double send = up ? v[i] : v[i + h];
+      const double keep = up ? v[i + h] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+    }
+  }
+}
+
+template <int NR_T, int NB>
+__device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
+                                              int e1, int e2, int r0, bool skip_rjk)
+{
+  constexpr int NACC = NR_T * 2 * NB;
+  constexpr int NPAD = NACC <= 32 ? 32 : (NACC <= 64 ? 64 : 128);
+  const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
+  const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
+  const bool same = (e1 == e2);
+  const double rcut2 = S->Rcut * S->Rcut;
+  const double lam0 = S->basis_lam[0], lam1 = S->basis_lam[1];
+  double acc[NPAD];
+#pragma unroll
+  for (int i = 0; i < NPAD; i++) acc[i] = 0.0;
+  const int NR = S->NR;
+  const double* Arow[NR_T];
+#pragma unroll
+  for (int r = 0; r < NR_T; r++) Arow[r] = w.A + (size_t)min(r0 + r, NR - 1) * cap;
+
+  for (int a = lane; a < m1; a += 32) {
+    const int ja = s1 + a;
+    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+    double Aa[NR_T];
+#pragma unroll
+    for (int r = 0; r < NR_T; r++) Aa[r] = (r0 + r < NR) ? Arow[r][ja] : 0.0;
+    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    int b = same ? a + 1 : 0;
+    if (same && b >= m1) b -= m1;
+    const int sb = same ? s1 : s2, mb = same ? m1 : m2;
+    for (int t = 0; t < nt; t++) {
+      const int jb = sb + b;
+      b++;
+      if (b >= mb) b -= mb;
+      const double c = ax * w.ux[jb] + ay * w.uy[jb] + az * w.uz[jb];
+      if (skip_rjk) {
+        const double Rb = w.R[jb];
+        const double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c;
+        if (rjk2 > rcut2) continue;
+      }
+      double pw[2][NB];
+      pw[0][0] = fmax(fma(lam0, c, 1.0), 0.0);
+      pw[1][0] = fmax(fma(lam1, c, 1.0), 0.0);
+#pragma unroll
+      for (int k = 1; k < NB; k++) { pw[0][k] = pw[0][k - 1] * pw[0][k - 1]; pw[1][k] = pw[1][k - 1] * pw[1][k - 1]; }
+#pragma unroll
+      for (int r = 0; r < NR_T; r++) {
+        const double tr = Aa[r] * Arow[r][jb];
+#pragma unroll
+        for (int g = 0; g < 2; g++)
+#pragma unroll
+          for (int k = 0; k < NB; k++) acc[(r * 2 + g) * NB + k] = fma(pw[g][k], tr, acc[(r * 2 + g) * NB + k]);
+      }
+    }
+  }
+  pp_reduce_scatter<NPAD>(acc, lane);
+  constexpr int PER = NPAD / 32;
+#pragma unroll
+  for (int p = 0; p < PER; p++) w.cell[PER * lane + p] = 2.0 * acc[p];     // factor 2 = both (j,k) orders of the reference
+  __syncwarp();
+  const int base = S->trip_base[e1][e2] + S->nG3;
+  for (int row = lane; row < S->nG4; row += 32) {
+    const int rr = S->g4_rad[row] - r0;
+    if (rr >= 0 && rr < NR_T) w.buf[base + row] = S->ang_pref[S->g4_ang[row]] * w.cell[(rr * 2 + S->g4_bg[row]) * NB + S->g4_bb[row]];
+  }
+  __syncwarp();
+}
+
+// Force chain rule on the power basis.  W[r][g][b] = 2 * 2^(1-xi) * dE/dG(row) at the row's slot (0 elsewhere).
+//   d/dc pw_g[b] = 2^b lam_g x^(2^b - 1) = 2^b lam_g * prod_{k<b} pw_g[k]        (no division)
+template <int NR_T, int NB>
+__device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
+                                               int e1, int e2, int r0, bool skip_rjk)
+{
+  constexpr int NW = NR_T * 2 * NB;
+  const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
+  const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
+  if (m1 == 0 || m2 == 0) return;
+  const bool same = (e1 == e2);
+  const double rcut2 = S->Rcut * S->Rcut;
+  const double lam0 = S->basis_lam[0], lam1 = S->basis_lam[1];
+  for (int i = lane; i < NW; i += 32) w.cell[i] = 0.0;
+  __syncwarp();
+  const int base = S->trip_base[e1][e2] + S->nG3;
+  for (int row = lane; row < S->nG4; row += 32) {
+    const int rr = S->g4_rad[row] - r0;
+    if (rr >= 0 && rr < NR_T)
+      atomicAdd(&w.cell[(rr * 2 + S->g4_bg[row]) * NB + S->g4_bb[row]], 2.0 * S->ang_pref[S->g4_ang[row]] * w.buf[base + row]);
+  }
+  __syncwarp();
+  double W[NR_T][2][NB];
+#pragma unroll
+  for (int r = 0; r < NR_T; r++)
+#pragma unroll
+    for (int g = 0; g < 2; g++)
+#pragma unroll
+      for (int k = 0; k < NB; k++) W[r][g][k] = w.cell[(r * 2 + g) * NB + k];
+  const int NR = S->NR;
+  const double *Arow[NR_T], *dArow[NR_T];
+#pragma unroll
+  for (int r = 0; r < NR_T; r++) {
+    Arow[r] = w.A + (size_t)min(r0 + r, NR - 1) * cap;
+    dArow[r] = w.dA + (size_t)min(r0 + r, NR - 1) * cap;
+  }
+  const int width = same ? 32 : (m2 < 32 ? m2 : 32);
+  const int npass = (m1 + width - 1) / width;
+  const int nt_max = same ? (m1 >> 1) : m2;
+  for (int pass = 0; pass < npass; pass++) {
+    const int a = pass * width + lane;
+    const bool act = (lane < width) && (a < m1);
+    const int ja = s1 + (act ? a : 0);
+    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+    const double invRa = 1.0 / Ra;
+    double Aa[NR_T], dAa[NR_T];
+#pragma unroll
+    for (int r = 0; r < NR_T; r++) {
+      const bool ok = (r0 + r < NR);
+      Aa[r] = ok ? Arow[r][ja] : 0.0;
+      dAa[r] = ok ? dArow[r][ja] : 0.0;
+    }
+    double gx = 0.0, gy = 0.0, gz = 0.0;
+    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    const int sb = same ? s1 : s2, mb = same ? m1 : m2;
+    int b = same ? a + 1 : lane;
+    if (b >= mb) b -= mb;
+    for (int t = 0; t < nt_max; t++) {
+      if (act && t < nt) {
+        const int jb = sb + b;
+        const double bx = w.ux[jb], by = w.uy[jb], bz = w.uz[jb], Rb = w.R[jb];
+        const double c = ax * bx + ay * by + az * bz;
+        bool skip = false;
+        if (skip_rjk) { const double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c; skip = rjk2 > rcut2; }
+        if (!skip) {
+          double pw[2][NB], dpw[2][NB];
+          pw[0][0] = fmax(fma(lam0, c, 1.0), 0.0);
+          pw[1][0] = fmax(fma(lam1, c, 1.0), 0.0);
+          dpw[0][0] = pw[0][0] > 0.0 ? lam0 : 0.0;
+          dpw[1][0] = pw[1][0] > 0.0 ? lam1 : 0.0;
+          double pp0 = dpw[0][0], pp1 = dpw[1][0];      // lam_g * prod_{k<b} pw_g[k]
+#pragma unroll
+          for (int k = 1; k < NB; k++) {
+            pp0 *= pw[0][k - 1]; pp1 *= pw[1][k - 1];
+            pw[0][k] = pw[0][k - 1] * pw[0][k - 1];
+            pw[1][k] = pw[1][k - 1] * pw[1][k - 1];
+            dpw[0][k] = (double)(1 << k) * pp0;
+            dpw[1][k] = (double)(1 << k) * pp1;
+          }
+          double dRa = 0.0, dRb = 0.0, dc = 0.0;
+#pragma unroll
+          for (int r = 0; r < NR_T; r++) {
+            double Sr = 0.0, Tr = 0.0;
+#pragma unroll
+            for (int g = 0; g < 2; g++)
+#pragma unroll
+              for (int k = 0; k < NB; k++) { Sr = fma(W[r][g][k], pw[g][k], Sr); Tr = fma(W[r][g][k], dpw[g][k], Tr); }
+            const double Ab = Arow[r][jb], dAb = dArow[r][jb];
+            dRa = fma(Sr * dAa[r], Ab, dRa);
+            dRb = fma(Sr * Aa[r], dAb, dRb);
+            dc = fma(Tr * Aa[r], Ab, dc);
+          }
+          const double ca = dc * invRa, cb = dc / Rb;
+          gx += dRa * ax + ca * (bx - c * ax);
+          gy += dRa * ay + ca * (by - c * ay);
+          gz += dRa * az + ca * (bz - c * az);
+          w.fx[jb] += dRb * bx + cb * (ax - c * bx);
+          w.fy[jb] += dRb * by + cb * (ay - c * by);
+          w.fz[jb] += dRb * bz + cb * (az - c * bz);
+        }
+      }
+      b++;
+      if (b >= mb) b -= mb;
+      __syncwarp();
+    }
+    if (act) { w.fx[ja] += gx; w.fy[ja] += gy; w.fz[ja] += gz; }
+    __syncwarp();
+  }
+}
+
+// NX is the angular register tile NA_T on the general path and the number of power levels NB on the basis path.
+template <int NR_T, int NX, bool BASIS>
 __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
 {
   for (int g = lane; g < S->NG; g += 32) w.buf[g] = 0.0;
@@ -409,8 +619,11 @@ __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const De
   if (S->nG4) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++)
-        for (int r0 = 0; r0 < S->NR; r0 += NR_T)
-          for (int a0 = 0; a0 < S->NA; a0 += NA_T) pp_g4_block_desc<NR_T, NA_T>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
+        for (int r0 = 0; r0 < S->NR; r0 += NR_T) {
+          if constexpr (BASIS) pp_g4_block_desc_basis<NR_T, NX>(w, cap, lane, S, e1, e2, r0, skip_rjk);
+          else
+            for (int a0 = 0; a0 < S->NA; a0 += NX) pp_g4_block_desc<NR_T, NX>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
+        }
   }
 }
 
@@ -542,14 +755,17 @@ __device__ inline void pp_g4_block_force(WarpNbr& w, int cap, int lane, const De
   }
 }
 
-template <int NR_T, int NA_T>
+template <int NR_T, int NX, bool BASIS>
 __device__ inline void pp_force_entries(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
 {
   if (S->npair) pp_pair_rows_force(w, cap, lane, S);
   if (S->nG4) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++)
-        for (int r0 = 0; r0 < S->NR; r0 += NR_T)
-          for (int a0 = 0; a0 < S->NA; a0 += NA_T) pp_g4_block_force<NR_T, NA_T>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
+        for (int r0 = 0; r0 < S->NR; r0 += NR_T) {
+          if constexpr (BASIS) pp_g4_block_force_basis<NR_T, NX>(w, cap, lane, S, e1, e2, r0, skip_rjk);
+          else
+            for (int a0 = 0; a0 < S->NA; a0 += NX) pp_g4_block_force<NR_T, NX>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
+        }
   }
 }
