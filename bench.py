@@ -28,6 +28,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly one JSON line: NCCL's own banner / debug output goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 METRIC = "training structures/sec/epoch"
 UNIT = "structures/s"
@@ -172,14 +174,14 @@ def run_ours(args):
         ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
         fwd_ms.append(ctx.phase_ms(1)); bwd_ms.append(ctx.phase_ms(2)); coll_ms.append(ctx.phase_ms(3))
     # ---- e2e: host buffers through pp_epoch, host->device params and device->host results every step ---------
-    opt = _host_optimizer(P)
+    opt = _host_optimizer(net["params"], int(0.95 * n_struct * world))
     for _ in range(args.warmup):
         ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         sse, vsse, nval = ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
-        opt.step(x_pin, g_pin)
+        opt.step(x_pin, g_pin, sse)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
@@ -350,19 +352,15 @@ def reference_md_rate(cells=2):
 
 
 class _host_optimizer:
-    """Host-side optimizer step for the e2e loop.  Uses the C++ host library's Rprop when it is built."""
+    """Host-side optimizer step of the e2e loop: the C++ host layer's Optimizer::update_network + Rprop
+    (prophet_b200/host/pph_optimizer.cpp), reading the gradient from and writing the new parameters to pinned memory."""
 
-    def __init__(self, P):
-        self.impl = None
-        try:
-            from prophet_b200 import hostapi
-            self.impl = hostapi.Rprop(P)
-        except Exception:
-            self.impl = None
+    def __init__(self, x0, ntrain):
+        from prophet_b200 import hostapi
+        self.impl = hostapi.Optimizer(x0, "rprop", max(ntrain, 1))
 
-    def step(self, x_pin, g_pin):
-        if self.impl is not None:
-            self.impl.step_ptr(x_pin.data_ptr(), g_pin.data_ptr())
+    def step(self, x_pin, g_pin, sse=0.0):
+        self.impl.step_ptr(x_pin.data_ptr(), g_pin.data_ptr(), sse)
 
 
 def _torch_nccl_path():

@@ -136,6 +136,9 @@ int pp_comm_unique_id(void* unique_id_128);
 int pp_comm_init(pp_context* ctx, int nranks, int rank, const void* unique_id_128);
 int pp_comm_rank(pp_context* ctx);
 int pp_comm_size(pp_context* ctx);
+/* in-place sum over ranks of n host doubles, result on every rank: Parallel::Reduce(..., MPI_SUM) followed by
+ * Parallel::Bcast (Parallel.h:93-150), the pattern of every small collective in Potential / Setup; identity for one rank */
+int pp_comm_allreduce_host(pp_context* ctx, double* buf, int n);
 
 /* ---- descriptor statistics without allocation ------------------------------------------------------------------ */
 /* No counterpart in the reference (it has no device memory to manage).

@@ -33,7 +33,7 @@ SYMBOLS = [
     "pp_epoch_device", "pp_epoch_result_dev", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
     "pp_md_compute", "pp_md_build_neighbors", "pp_md_get_neighbors", "pp_md_step", "pp_md_step_device",
     "pp_comm_unique_id", "pp_comm_init", "pp_comm_rank", "pp_comm_size", "pp_kernel_launches", "pp_last_phase_ms",
-    "pp_stream", "pp_column_sums_static",
+    "pp_stream", "pp_column_sums_static", "pp_comm_allreduce_host",
 ]
 
 

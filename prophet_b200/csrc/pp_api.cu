@@ -1114,5 +1114,11 @@ extern "C" int pp_comm_init(pp_context* c, int nranks, int rank, const void* id)
   PP_CUDA(cudaSetDevice(c->device));
   return c->comm.init(nranks, rank, id);
 }
+extern "C" int pp_comm_allreduce_host(pp_context* c, double* buf, int n)
+{
+  PP_REQUIRE(c && (buf || n == 0) && n >= 0, "pp_comm_allreduce_host: bad arguments");
+  PP_CUDA(cudaSetDevice(c->device));
+  return c->comm.allreduce_host(buf, n, c->stream);
+}
 extern "C" int pp_comm_rank(pp_context* c) { return c ? c->comm.rank : 0; }
 extern "C" int pp_comm_size(pp_context* c) { return c ? c->comm.nranks : 1; }

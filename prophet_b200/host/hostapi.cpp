@@ -1,0 +1,170 @@
+// extern "C" test hooks into the host layer (used by tests/test_host_layer.py through ctypes).
+#include <cstring>
+#include <fstream>
+#include <sstream>
+
+#include "pph.h"
+
+#include "pair_nn.h"
+
+using namespace pph;
+
+extern "C" {
+
+// ---- Rprop driven step by step with caller-supplied gradients -------------------------------------------------
+struct pph_opt { Parallel mpi; FunctionalParams F; Optimizer* opt; };
+
+void* pph_optimizer_create(int P, const double* x0, const char* algorithm, int Nsystems)
+{
+  pph_opt* h = new pph_opt();
+  h->F.training_algorithm = algorithm;
+  h->F.Niterations = 1 << 30;
+  h->opt = new Optimizer(&h->mpi, h->F, Nsystems);
+  h->opt->do_print = false;
+  h->opt->init(std::vector<REAL>(x0, x0 + P));
+  return h;
+}
+void pph_optimizer_step(void* hv, int P, double sse, const double* grad, double* x_out)
+{
+  pph_opt* h = (pph_opt*)hv;
+  h->opt->update_network(sse, std::vector<REAL>(grad, grad + P));
+  const std::vector<REAL>& x = h->opt->parameters();
+  memcpy(x_out, x.data(), sizeof(double) * P);
+}
+// in-place variant for pinned buffers: x is both the current parameters' destination and not read
+void pph_optimizer_step_ptr(void* hv, int P, double sse, const double* grad, double* x_inout)
+{
+  pph_optimizer_step(hv, P, sse, grad, x_inout);
+}
+void pph_optimizer_destroy(void* hv)
+{
+  pph_opt* h = (pph_opt*)hv;
+  delete h->opt;
+  delete h;
+}
+
+// ---- checkpoint: read a file, write it back ---------------------------------------------------------------------
+int pph_checkpoint_roundtrip(const char* in_path, const char* out_path)
+{
+  std::ifstream in(in_path);
+  if (!in.is_open()) return 1;
+  HostNet net;
+  net.params.read(in);
+  net.sizes.clear();
+  net.sizes.push_back(net.params.NG());
+  for (size_t l = 0; l < net.params.hidden.size(); l++) net.sizes.push_back(net.params.hidden[l]);
+  net.sizes.push_back(1);
+  net.load(in);
+  std::ofstream out(out_path);
+  net.print(out);
+  return 0;
+}
+
+// ---- Setup: parse an input_file (cwd must hold what it references) and report what was understood ---------------
+int pph_setup_parse(const char* input_file, int rank, int nprocs, char* report, int report_len)
+{
+  std::ostringstream r;
+  {
+    std::ostringstream a, b;
+    a << rank;
+    b << nprocs;
+    setenv("PP_RANK", a.str().c_str(), 1);
+    setenv("PP_WORLD_SIZE", b.str().c_str(), 1);
+  }
+  Parallel mpi;
+  Setup s(input_file, &mpi, true);
+  const FunctionalParams& F = s.F;
+  r << "Rcut " << F.Rcut << "\n";
+  r << "hidden";
+  for (size_t i = 0; i < F.hidden.size(); i++) r << " " << F.hidden[i];
+  r << "\n";
+  r << "transfer " << F.transfer_function << "\nalgorithm " << F.training_algorithm << "\n";
+  r << "Niterations " << F.Niterations << "\nNprint " << F.Nprint << "\nNcheckpoint " << F.Ncheckpoint << "\n";
+  r << "checkpoint_in " << F.input_file << "\ncheckpoint_out " << F.output_file << "\n";
+  r << "rows " << F.G1.size() << " " << F.G2.size() << " " << F.G3.size() << " " << F.G4.size() << "\n";
+  r << "Nradial " << F.Nradial << " Nangular " << F.Nangular << "\n";
+  r << "systems_total " << s.Ntotal_systems << " local " << s.Nsystems() << "\n";
+  for (int i = 0; i < s.Nsystems(); i++) {
+    const SystemSpec& sp = s.system(i);
+    r << "system";
+    for (std::map<std::string, std::string>::const_iterator it = sp.files.begin(); it != sp.files.end(); ++it)
+      r << " " << it->first << "=" << it->second;
+    r << "\n";
+  }
+  std::string out = r.str();
+  strncpy(report, out.c_str(), report_len - 1);
+  report[report_len - 1] = 0;
+  unsetenv("PP_RANK");
+  unsetenv("PP_WORLD_SIZE");
+  return 0;
+}
+
+// ---- readers ------------------------------------------------------------------------------------------------------
+int pph_read_vasprun(const char* dir, double* cell9, int* natoms, double* pos, int* Z, double* target, int cap)
+{
+  StructureData sd = read_vasprun(dir);
+  if (sd.natoms() > cap) return 1;
+  memcpy(cell9, sd.cell, sizeof(double) * 9);
+  *natoms = sd.natoms();
+  memcpy(pos, sd.pos.data(), sizeof(double) * sd.pos.size());
+  memcpy(Z, sd.Z.data(), sizeof(int) * sd.Z.size());
+  *target = sd.target;
+  return 0;
+}
+
+int pph_auto_rows(double Rcut, int Nradial, int Nangular, double* G2_out, int* nG2, double* G4_out, int* nG4, int cap)
+{
+  FunctionalParams F;
+  F.Rcut = Rcut;
+  F.Nradial = Nradial;
+  F.Nangular = Nangular;
+  F.auto_rows();
+  if ((int)F.G2.size() > cap || (int)F.G4.size() > cap) return 1;
+  *nG2 = (int)F.G2.size();
+  *nG4 = (int)F.G4.size();
+  for (size_t i = 0; i < F.G2.size(); i++) memcpy(G2_out + 4 * i, F.G2[i].data(), sizeof(double) * 4);
+  for (size_t i = 0; i < F.G4.size(); i++) memcpy(G4_out + 5 * i, F.G4[i].data(), sizeof(double) * 5);
+  return 0;
+}
+
+// ---- pair_style nn through the LAMMPS stand-in: settings + coeff + compute on caller arrays ----------------------
+int pph_pair_nn_run(double Rcut, int ntypes, const int* coeff_types, const char** coeff_files, int nlocal, int nghost,
+                    double* x, int* type, const int* numneigh, const int* neigh_flat, double* f, double* eatom, double* eng_vdwl)
+{
+  using namespace LAMMPS_NS;
+  const int ntotal = nlocal + nghost;
+  std::vector<double*> xp(ntotal), fp(ntotal);
+  for (int i = 0; i < ntotal; i++) { xp[i] = x + 3 * (size_t)i; fp[i] = f + 3 * (size_t)i; }
+  Atom atom = {xp.data(), fp.data(), type, nlocal, nghost, ntypes};
+  Comm comm = {0};
+  Error err;
+  LAMMPS lmp = {&atom, &comm, &err};
+  std::vector<int> ilist(nlocal);
+  std::vector<int*> first(nlocal);
+  std::vector<int> nn(numneigh, numneigh + nlocal);
+  std::vector<int> flat(neigh_flat, neigh_flat + 0);
+  size_t total = 0;
+  for (int i = 0; i < nlocal; i++) total += numneigh[i];
+  flat.assign(neigh_flat, neigh_flat + total);
+  size_t off = 0;
+  for (int i = 0; i < nlocal; i++) { ilist[i] = i; first[i] = flat.data() + off; off += numneigh[i]; }
+  NeighList list = {nlocal, ilist.data(), nn.data(), first.data()};
+  PairNN pair(&lmp);
+  char buf[64];
+  snprintf(buf, sizeof(buf), "%.17g", Rcut);
+  char* sarg[1] = {buf};
+  pair.settings(1, sarg);
+  for (int i = 0; i < ntypes; i++) {
+    char tbuf[16];
+    snprintf(tbuf, sizeof(tbuf), "%d", coeff_types[i]);
+    char* carg[2] = {tbuf, (char*)coeff_files[i]};
+    pair.coeff(2, carg);
+  }
+  pair.init_list(1, &list);
+  pair.eatom = eatom;
+  pair.compute(3, 0);
+  *eng_vdwl = pair.eng_vdwl;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,111 @@
+// See pair_nn.h.  Reference: pair_nn.cpp:112-188 (compute), 223-259 (coeff), 499-539 (settings),
+// Potential::insert_atom_type (Potential.cpp:1214-1253).
+#include "pair_nn.h"
+
+#include <cstring>
+#include <fstream>
+
+using namespace LAMMPS_NS;
+
+PairNN::PairNN(LAMMPS* lmp) : Pair(lmp), Rcut(0.0), out_mean(0.0), ctx(NULL), ready(false) {}
+
+PairNN::~PairNN()
+{
+  if (ctx) pp_destroy(ctx);
+}
+
+void PairNN::settings(int narg, char** arg)
+{
+  if (narg != 1) error->all(FLERR, "pair_style nn takes exactly one argument: the cutoff radius");
+  Rcut = atof(arg[0]);
+  if (!ctx) {
+    int device = getenv("LOCAL_RANK") ? atoi(getenv("LOCAL_RANK")) : 0;
+    if (pp_create(device, 64, &ctx)) error->all(FLERR, pp_last_error());
+  }
+}
+
+void PairNN::coeff(int narg, char** arg)
+{
+  if (narg != 2 && narg != 3) error->all(FLERR, "Format of pair_coeff command is\npair_coeff atom_type parameter_file\n");
+  const int this_type = atoi(arg[0]);
+  for (size_t i = 0; i < coeff_types.size(); i++)
+    if (coeff_types[i] == this_type) return;          // Potential::insert_atom_type: a type is inserted once
+  std::ifstream file(arg[1]);
+  if (!file.is_open()) error->all(FLERR, (std::string("Could not open parameter file \"") + arg[1] + "\"").c_str());
+  pph::HostNet net;
+  net.params.read(file);                              // header: rows, element list, means, hidden layers
+  net.Z = pph::atomic_number(net.params.current_atom_type);
+  net.sizes.clear();
+  net.sizes.push_back(net.params.NG());
+  for (size_t l = 0; l < net.params.hidden.size(); l++) net.sizes.push_back(net.params.hidden[l]);
+  net.sizes.push_back(1);
+  net.load(file);
+  out_mean = net.params.output_mean;
+  if (comm->me == 0) printf("Initializing atom type %d with file %s\n", this_type, arg[1]);
+  coeff_types.push_back(this_type);
+  coeff_nets.push_back(net);
+  ready = false;
+  if (coeff_nets.size() == net.params.atomic_symbols.size()) finish_setup();
+}
+
+void PairNN::finish_setup()
+{
+  // Once every element named in the checkpoint header has a pair_coeff line, map LAMMPS types to the header's
+  // element order (ascending Z), as Potential::insert_atom_type does (Potential.cpp:1236-1250).
+  const pph::FunctionalParams& P = coeff_nets[0].params;
+  const int n_elem = (int)P.atomic_symbols.size();
+  std::vector<double> g1, g2, g3, g4;
+  for (size_t r = 0; r < P.G1.size(); r++) g1.insert(g1.end(), P.G1[r].begin(), P.G1[r].end());
+  for (size_t r = 0; r < P.G2.size(); r++) g2.insert(g2.end(), P.G2[r].begin(), P.G2[r].end());
+  for (size_t r = 0; r < P.G3.size(); r++) g3.insert(g3.end(), P.G3[r].begin(), P.G3[r].end());
+  for (size_t r = 0; r < P.G4.size(); r++) g4.insert(g4.end(), P.G4[r].begin(), P.G4[r].end());
+  const double rc = Rcut > 0 ? Rcut : P.Rcut;
+  if (pp_set_descriptors(ctx, n_elem, (int)P.G1.size(), g1.data(), (int)P.G2.size(), g2.data(), (int)P.G3.size(), g3.data(),
+                         (int)P.G4.size(), g4.data(), rc))
+    error->all(FLERR, pp_last_error());
+  int max_type = 0;
+  for (size_t i = 0; i < coeff_types.size(); i++) max_type = std::max(max_type, coeff_types[i]);
+  std::vector<int> type_to_elem(max_type + 1, 0);
+  for (size_t i = 0; i < coeff_nets.size(); i++) {
+    pph::HostNet& n = coeff_nets[i];
+    int e = -1;
+    for (int k = 0; k < n_elem; k++)
+      if (P.atomic_symbols[k] == n.params.current_atom_type) e = k;
+    if (e < 0) error->all(FLERR, "pair_coeff file's element is not in the potential's element list");
+    type_to_elem[coeff_types[i]] = e;
+    std::vector<int> tf;
+    for (size_t k = 0; k < n.node_transfer.size(); k++) tf.push_back(pph::transfer_id(n.node_transfer[k]));
+    if (pp_set_network(ctx, e, (int)n.sizes.size() - 1, n.sizes.data(), tf.data(), n.weights.data(), n.params.input_mean.data(),
+                       n.params.input_variance.data()))
+      error->all(FLERR, pp_last_error());
+  }
+  if (pp_set_output_scaling(ctx, coeff_nets[0].params.output_mean, coeff_nets[0].params.output_variance)) error->all(FLERR, pp_last_error());
+  if (pp_md_set_types(ctx, max_type, type_to_elem.data())) error->all(FLERR, pp_last_error());
+  ready = true;
+}
+
+void PairNN::compute(int eflag, int vflag)
+{
+  if (eflag || vflag) ev_setup(eflag, vflag);
+  else evflag = vflag_fdotr = 0;
+  if (!ready) error->all(FLERR, "pair_style nn: not every element of the potential has a pair_coeff line");
+  const int nlocal = atom->nlocal;
+  // LAMMPS' paged full neighbour list -> one CSR list.  Like the reference this assumes ilist[ii] == ii
+  // (pair_nn.cpp:151-157) and unmasked neighbour indices.
+  offsets.resize(nlocal + 1);
+  offsets[0] = 0;
+  for (int ii = 0; ii < list->inum; ii++) offsets[ii + 1] = offsets[ii] + list->numneigh[ii];
+  flat.resize((size_t)offsets[list->inum] + 1);
+  for (int ii = 0; ii < list->inum; ii++)
+    memcpy(flat.data() + offsets[ii], list->firstneigh[ii], sizeof(int) * (size_t)list->numneigh[ii]);
+  double etotal = 0.0;
+  if (pp_md_compute(ctx, atom->x[0], atom->type, nlocal, atom->nghost, offsets.data(), flat.data(), atom->f[0],
+                    eflag_atom ? eatom : NULL, &etotal, NULL, NULL))
+    error->all(FLERR, pp_last_error());
+  if (eflag_global) {
+    // per-atom energies summed on every rank, the shift added once on rank 0 (pair_nn.cpp:156-179)
+    eng_vdwl += etotal - out_mean;
+    if (comm->me == 0) eng_vdwl += out_mean;
+  }
+  if (vflag_fdotr) virial_fdotr_compute();
+}

@@ -1,0 +1,49 @@
+// pair_style nn on the B200 device path: the reference's LAMMPS plug-in (pair_nn.h:38-89, pair_nn.cpp) with the same
+// user-facing commands
+//     pair_style nn <Rcut>
+//     pair_coeff <type> <checkpoint_file>
+// but with PairNN::compute forwarding LAMMPS' own arrays to pp_md_compute instead of copying them into nested
+// vectors and looping over atoms on the CPU.
+#ifdef PAIR_CLASS
+PairStyle(nn, PairNN)
+#else
+#ifndef LMP_PAIR_NN_B200_H
+#define LMP_PAIR_NN_B200_H
+
+#ifdef PPH_LAMMPS_STUB
+#include "lammps_stub.h"
+#else
+#include "pair.h"
+#endif
+#include <string>
+#include <vector>
+
+#include "pph.h"
+
+namespace LAMMPS_NS {
+
+class PairNN : public Pair {
+ public:
+  explicit PairNN(LAMMPS* lmp);
+  virtual ~PairNN();
+  virtual void compute(int eflag, int vflag);
+  virtual void settings(int narg, char** arg);      // exactly one argument: Rcut (pair_nn.cpp:502-507)
+  virtual void coeff(int narg, char** arg);         // type file [cut]       (pair_nn.cpp:226-234)
+  void init_list(int id, NeighList* ptr) { if (id == 1) list = ptr; }
+  double init_one(int, int) { return Rcut; }
+  double energy_shift() const { return out_mean; }
+
+ private:
+  void finish_setup();
+  double Rcut, out_mean;
+  pp_context* ctx;
+  bool ready;
+  std::vector<int> coeff_types;
+  std::vector<pph::HostNet> coeff_nets;
+  std::vector<long long> offsets;
+  std::vector<int> flat;
+};
+
+}  // namespace LAMMPS_NS
+#endif
+#endif

@@ -1,0 +1,103 @@
+"""ctypes access to the host-side C++ layer (libprophet_b200_host.so): test hooks for Setup, the checkpoint
+reader/writer, the Optimizer and the pair_style nn shim.  Harness code; the classes themselves are C++."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libprophet_b200_host.so")
+CLI_PATH = os.path.join(_HERE, "PROPhet_b200")
+_LIB = None
+_d = ctypes.POINTER(ctypes.c_double)
+_i = ctypes.POINTER(ctypes.c_int)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("%s not built (make -C prophet_b200/host)" % LIB_PATH)
+        # the device library first, by full path, so the host library's dependency resolves to the in-tree build
+        ctypes.CDLL(os.path.join(_HERE, "libprophet_b200.so"), mode=ctypes.RTLD_GLOBAL)
+        L = ctypes.CDLL(LIB_PATH)
+        L.pph_optimizer_create.restype = ctypes.c_void_p
+        L.pph_optimizer_create.argtypes = [ctypes.c_int, _d, ctypes.c_char_p, ctypes.c_int]
+        L.pph_optimizer_step.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, _d, _d]
+        L.pph_optimizer_step_ptr.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
+        L.pph_optimizer_destroy.argtypes = [ctypes.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+class Optimizer:
+    """pph::Optimizer (Optimizer::update_network + rprop / steepest descent) driven with caller-supplied gradients."""
+
+    def __init__(self, x0, algorithm="rprop", nsystems=1):
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        self.P = len(x0)
+        self._h = lib().pph_optimizer_create(self.P, x0.ctypes.data_as(_d), algorithm.encode(), nsystems)
+
+    def step(self, sse, grad):
+        grad = np.ascontiguousarray(grad, dtype=np.float64)
+        x = np.zeros(self.P)
+        lib().pph_optimizer_step(self._h, self.P, float(sse), grad.ctypes.data_as(_d), x.ctypes.data_as(_d))
+        return x
+
+    def step_ptr(self, x_ptr, grad_ptr, sse=0.0):
+        lib().pph_optimizer_step_ptr(self._h, self.P, float(sse), grad_ptr, x_ptr)
+
+    def __del__(self):
+        try:
+            lib().pph_optimizer_destroy(self._h)
+        except Exception:
+            pass
+
+
+class Rprop(Optimizer):
+    def __init__(self, P_or_x0):
+        x0 = np.zeros(P_or_x0) if np.isscalar(P_or_x0) else P_or_x0
+        super().__init__(x0, "rprop", 1)
+
+
+def checkpoint_roundtrip(in_path, out_path):
+    rc = lib().pph_checkpoint_roundtrip(in_path.encode(), out_path.encode())
+    if rc:
+        raise RuntimeError("could not read " + in_path)
+
+
+def setup_parse(input_file, rank=0, nprocs=1):
+    buf = ctypes.create_string_buffer(1 << 20)
+    lib().pph_setup_parse(input_file.encode(), rank, nprocs, buf, len(buf))
+    return buf.value.decode()
+
+
+def read_vasprun(directory, cap=4096):
+    cell = np.zeros(9); pos = np.zeros(3 * cap); Z = np.zeros(cap, dtype=np.int32)
+    n = ctypes.c_int(); tgt = ctypes.c_double()
+    rc = lib().pph_read_vasprun(directory.encode(), cell.ctypes.data_as(_d), ctypes.byref(n), pos.ctypes.data_as(_d),
+                                Z.ctypes.data_as(_i), ctypes.byref(tgt), cap)
+    assert rc == 0
+    return cell.reshape(3, 3), pos[:3 * n.value].reshape(-1, 3), Z[:n.value].copy(), tgt.value
+
+
+def auto_rows(rcut, nradial, nangular, cap=256):
+    g2 = np.zeros(4 * cap); g4 = np.zeros(5 * cap); n2 = ctypes.c_int(); n4 = ctypes.c_int()
+    rc = lib().pph_auto_rows(ctypes.c_double(rcut), nradial, nangular, g2.ctypes.data_as(_d), ctypes.byref(n2),
+                             g4.ctypes.data_as(_d), ctypes.byref(n4), cap)
+    assert rc == 0
+    return g2[:4 * n2.value].reshape(-1, 4), g4[:5 * n4.value].reshape(-1, 5)
+
+
+def pair_nn_run(rcut, coeff_types, coeff_files, x, types, nlocal, numneigh, neigh_flat):
+    """pair_style nn <rcut>; pair_coeff <type> <file> ...; one compute() through the LAMMPS stand-in."""
+    x = np.ascontiguousarray(x, dtype=np.float64); types = np.ascontiguousarray(types, dtype=np.int32)
+    numneigh = np.ascontiguousarray(numneigh, dtype=np.int32); neigh_flat = np.ascontiguousarray(neigh_flat, dtype=np.int32)
+    ct = np.ascontiguousarray(coeff_types, dtype=np.int32)
+    files = (ctypes.c_char_p * len(coeff_files))(*[f.encode() for f in coeff_files])
+    f = np.zeros_like(x); eatom = np.zeros(nlocal); eng = ctypes.c_double()
+    rc = lib().pph_pair_nn_run(ctypes.c_double(rcut), len(ct), ct.ctypes.data_as(_i), files, nlocal, len(x) - nlocal,
+                               x.ctypes.data_as(_d), types.ctypes.data_as(_i), numneigh.ctypes.data_as(_i),
+                               neigh_flat.ctypes.data_as(_i), f.ctypes.data_as(_d), eatom.ctypes.data_as(_d), ctypes.byref(eng))
+    assert rc == 0
+    return dict(f=f, eatom=eatom, eng_vdwl=eng.value)

@@ -294,6 +294,31 @@ CASES = {
     "variants_md": case_variants_md, "tutorial_c1": case_tutorial_c1, "batio3_doc": case_batio3_doc,
 }
 
+
+
+def case_checkpoint_files():
+    """Checkpoint files written by the reference's own Potential::save (3 Rprop iterations on two small TiO2
+    structures, nets 52-5-4-1, tanh_spline default transfer): byte-level fixtures for the host layer's reader/writer."""
+    cfg = synth.config_c3(2)
+    cfg.hidden = [5, 4]
+    cfg.transfer = "tanh_spline"
+    cwd = tempfile.mkdtemp(prefix="golden_ckpt_")
+    try:
+        st = [synth.make_structure(cfg, s) for s in range(2)]
+        synth.write_prophet_xml(os.path.join(cwd, "PROPhet.xml"), st)
+        synth.write_input_file(os.path.join(cwd, "input_file"), cfg, niterations=3, extra=("seed = 11",))
+        r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "PROPhet"), "-in", "input_file", "-train"], cwd=cwd,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert r.returncode == 0, r.stdout[-2000:]
+        for sym in ("O", "Ti"):
+            shutil.copy(os.path.join(cwd, "potential_" + sym), os.path.join(OUT, "ref_checkpoint_" + sym + ".txt"))
+        print("wrote ref_checkpoint_O.txt, ref_checkpoint_Ti.txt")
+    finally:
+        shutil.rmtree(cwd, ignore_errors=True)
+
+
+CASES["checkpoint_files"] = case_checkpoint_files
+
 if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh first (needs %s)" % REF)

@@ -1,0 +1,114 @@
+"""GPU tests of the drop-in surfaces: the PROPhet_b200 command line against the reference's own CLI on the same
+input_file / PROPhet.xml / checkpoint files, and pair_style nn through the LAMMPS stand-in against the MD goldens."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from golden_util import MDCase, rel_err
+from prophet_b200 import ckpt, hostapi, synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+REF_CLI = os.path.join(ROOT, "oracle", "_ref", "PROPhet")
+IT_LINE = re.compile(r"^(\d+)\s+([-+0-9.eE]+)\s+([-+0-9.eE]+)(?:\s+([-+0-9.eE]+))?\s*$")
+
+
+def _iteration_table(stdout):
+    rows = []
+    for line in stdout.splitlines():
+        m = IT_LINE.match(line)
+        if m:
+            rows.append([float(x) for x in m.groups() if x is not None])
+    return rows
+
+
+def _write_case(cwd, cfg, n_struct, tags, hidden, seed, niter, extra=()):
+    cfg.hidden = hidden
+    st = [synth.make_structure(cfg, 40 + s) for s in range(n_struct)]
+    st = [(c, x, z, t, tag) for (c, x, z, t, _), tag in zip(st, tags)]
+    synth.write_prophet_xml(os.path.join(cwd, "PROPhet.xml"), st)
+    syms = [synth.Z_TO_SYMBOL[z] for z in cfg.elements]
+    for z in cfg.elements:
+        net = synth.random_network(cfg, z, seed)
+        ckpt.write_checkpoint(os.path.join(cwd, "start_" + synth.Z_TO_SYMBOL[z]), synth.Z_TO_SYMBOL[z], syms,
+                              {"G1": cfg.G1, "G2": cfg.G2, "G3": cfg.G3, "G4": cfg.G4},
+                              0.3 * np.abs(synth.normal(z, cfg.NG, 3)), 0.5 + np.abs(synth.normal(z, cfg.NG, 4)), 0.0, 1.0,
+                              net["sizes"], net["params"], header_precision=17)
+    synth.write_input_file(os.path.join(cwd, "input_file"), cfg, niterations=niter, checkpoint_in="start",
+                           checkpoint_out="trained", extra=extra)
+
+
+def _run(exe, args, cwd):
+    r = subprocess.run([exe] + args, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:]
+    return r.stdout
+
+
+@pytest.mark.skipif(not os.path.exists(REF_CLI), reason="oracle/_ref/PROPhet not built")
+@pytest.mark.parametrize("cfg_name,hidden", [("C2", [8, 6]), ("C3", [7, 5])])
+def test_cli_train_matches_reference_cli(cfg_name, hidden, tmp_path):
+    """Same input_file, PROPhet.xml and checkpoint_in for both programs: the printed training table and the saved
+    potentials must agree (single- and two-element systems, with a validation structure -> early-stop table)."""
+    assert os.path.exists(hostapi.CLI_PATH), "PROPhet_b200 not built"
+    cfg = synth.CONFIGS[cfg_name](5)
+    ours = tmp_path / "ours"; ref = tmp_path / "ref"
+    for d in (ours, ref):
+        d.mkdir()
+        _write_case(str(d), cfg, 5, [0, 0, 1, 0, 2], hidden, seed=9, niter=6)
+    out_ref = _run(REF_CLI, ["-in", "input_file", "-train"], str(ref))
+    out_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-train"], str(ours))
+    t_ref, t_ours = _iteration_table(out_ref), _iteration_table(out_ours)
+    assert len(t_ref) == 6 and len(t_ours) == 6, (out_ref[-1500:], out_ours[-1500:])
+    assert np.allclose(np.array(t_ours), np.array(t_ref), rtol=2e-6, atol=0), (t_ours, t_ref)
+    for z in cfg.elements:
+        sym = synth.Z_TO_SYMBOL[z]
+        a = ckpt.read_checkpoint(str(ours / ("trained_" + sym)))
+        b = ckpt.read_checkpoint(str(ref / ("trained_" + sym)))
+        assert a["sizes"] == b["sizes"] and a["rows"] == b["rows"] and a["node_transfer"] == b["node_transfer"]
+        assert rel_err(a["params"], b["params"]) < 1e-9
+        assert np.allclose(a["means"], b["means"], rtol=1e-11) and np.allclose(a["scales"], b["scales"], rtol=1e-11)
+    # -validate and -run on the trained potentials: the prediction tables agree
+    for d in (ours, ref):
+        txt = open(str(d / "input_file")).read().replace("checkpoint_in = start", "checkpoint_in = trained")
+        open(str(d / "input_file"), "w").write(txt)
+    v_ref = _run(REF_CLI, ["-in", "input_file", "-validate"], str(ref))
+    v_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-validate"], str(ours))
+
+    def table(txt):
+        rows = []
+        for line in txt.splitlines():
+            tok = line.split()
+            if len(tok) == 5 and tok[0].isdigit() and tok[4] in ("train", "val", "test", "other"):
+                rows.append((int(tok[0]), float(tok[1]), float(tok[2]), int(tok[3]), tok[4]))
+        return rows
+
+    tr, to = table(v_ref), table(v_ours)
+    assert len(tr) == 5 and len(to) == 5
+    for a, b in zip(to, tr):
+        assert a[0] == b[0] and a[3] == b[3] and a[4] == b[4]
+        assert abs(a[1] - b[1]) <= 1e-8 * abs(b[1]) and a[2] == b[2]
+    rms = lambda txt: float(re.search(r"RMS Error =\s+([-+0-9.eE]+)", txt).group(1))
+    assert abs(rms(v_ours) - rms(v_ref)) <= 1e-5 * abs(rms(v_ref))
+
+
+@pytest.mark.parametrize("name", ["si_md", "tio2_md"])
+def test_pair_style_nn_through_lammps_stand_in(name, tmp_path):
+    """pair_style nn <Rcut> / pair_coeff <type> <file> / compute(), with checkpoint files in the reference's format."""
+    c = MDCase(name)
+    syms = [synth.Z_TO_SYMBOL[z] for z in c.elements]
+    files = []
+    for z in c.elements:
+        p = str(tmp_path / ("pot_" + synth.Z_TO_SYMBOL[z]))
+        ckpt.write_checkpoint(p, synth.Z_TO_SYMBOL[z], syms, {"G1": c.G1.tolist(), "G2": c.G2.tolist(), "G3": c.G3.tolist(), "G4": c.G4.tolist()},
+                              c.d["in_mean.%d" % z], c.d["in_scale.%d" % z], c.out_mean, c.out_scale, c.sizes, c.d["params.%d" % z],
+                              header_precision=17)
+        files.append(p)
+    # give the pair_coeff lines in reverse order: the type -> element map must come from the files, not the order
+    types = list(range(1, len(c.elements) + 1))
+    r = hostapi.pair_nn_run(c.rcut, types[::-1], files[::-1], c.x, c.types, c.nlocal, c.numneigh, c.neigh)
+    assert rel_err(r["eatom"], c.d["eatom"]) < 1e-10
+    assert abs(r["eng_vdwl"] - c.d["etotal"][0]) < 1e-10 * abs(c.d["etotal"][0])
+    assert rel_err(r["f"], c.d["f"]) < 1e-10
