@@ -196,7 +196,6 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
   PP_REQUIRE(nG1 + nG2 <= PP_MAX_PAIR_ROWS, "pp_set_descriptors: %d pair rows (max %d)", nG1 + nG2, PP_MAX_PAIR_ROWS);
   PP_REQUIRE(nG4 <= PP_MAX_G4_ROWS, "pp_set_descriptors: %d G4 rows (max %d)", nG4, PP_MAX_G4_ROWS);
   PP_REQUIRE(nG3 <= PP_MAX_G3_ROWS, "pp_set_descriptors: %d G3 rows (max %d)", nG3, PP_MAX_G3_ROWS);
-  PP_REQUIRE(nG3 == 0, "pp_set_descriptors: G3 rows are not implemented on the GPU path yet");
   PP_REQUIRE(Rcut > 0, "pp_set_descriptors: Rcut must be positive");
   PP_REQUIRE(c->n_struct == 0, "pp_set_descriptors: structures already added; call pp_clear_structures first");
   DescSpec& S = c->spec;

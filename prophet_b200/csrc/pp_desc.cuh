@@ -609,6 +609,143 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// G3 rows (Structure.h:361-367): 2^(1-xi) (1+lam c)^xi exp(-eta (R^2+Ru^2+Rjk^2)) fc(R) fc(Ru) fc(Rjk).
+// The Rjk dependence rules out the factorisation used for G4, so each pair evaluates each row directly (exp, pow,
+// three cutoffs).  Kept out of line: potentials without G3 rows (every BASELINE config) pay nothing for it.
+__device__ __forceinline__ double pp_rjk(double ax, double ay, double az, double Ra, double bx, double by, double bz, double Rb,
+                                          double& dx, double& dy, double& dz)
+{
+  dx = Ra * ax - Rb * bx; dy = Ra * ay - Rb * by; dz = Ra * az - Rb * bz;     // r_j - r_j2
+  return sqrt(dx * dx + dy * dy + dz * dz);
+}
+
+__device__ __noinline__ void pp_g3_block_desc(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, int e1, int e2,
+                                              bool nonperiodic)
+{
+  const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
+  const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
+  const bool same = (e1 == e2);
+  const int nG3 = S->nG3;
+  double acc[PP_MAX_G3_ROWS];
+#pragma unroll
+  for (int r = 0; r < PP_MAX_G3_ROWS; r++) acc[r] = 0.0;
+  for (int a = lane; a < m1; a += 32) {
+    const int ja = s1 + a;
+    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    for (int t = 0; t < nt; t++) {
+      int jb;
+      if (same) { int b = a + t + 1; if (b >= m1) b -= m1; jb = s1 + b; }
+      else jb = s2 + t;
+      const double bx = w.ux[jb], by = w.uy[jb], bz = w.uz[jb], Rb = w.R[jb];
+      const double c = ax * bx + ay * by + az * bz;
+      double dx, dy, dz;
+      const double Rjk = pp_rjk(ax, ay, az, Ra, bx, by, bz, Rb, dx, dy, dz);
+      if (nonperiodic ? (Rjk > S->Rcut) : (Rjk < 0.01)) continue;          // Structure.cpp:1129-1132 / :1048-1050
+#pragma unroll
+      for (int r = 0; r < PP_MAX_G3_ROWS; r++) {
+        if (r < nG3) {
+          const double term = 1.0 + S->g3_lam[r] * c;
+          if (term > 0.0) {
+            const double rc = S->g3_rc[r];
+            const int fs = S->g3_fc[r];
+            acc[r] += pow(term, S->g3_xi[r]) * exp(-S->g3_eta[r] * (Ra * Ra + Rb * Rb + Rjk * Rjk)) * pp_fc(Ra / rc, fs) *
+                      pp_fc(Rb / rc, fs) * pp_fc(Rjk / rc, fs);
+          }
+        }
+      }
+    }
+  }
+  const int base = S->trip_base[e1][e2];
+#pragma unroll
+  for (int r = 0; r < PP_MAX_G3_ROWS; r++) {
+    if (r < nG3) {
+      const double v = pp_warp_sum(acc[r]);
+      if (lane == 0) w.buf[base + r] = 2.0 * pow(2.0, 1.0 - S->g3_xi[r]) * v;
+    }
+  }
+  __syncwarp();
+}
+
+// angular_term of the reference (Structure.h:251-279) for one row: integer xi by squaring, else the series
+__device__ __forceinline__ double pp_angular_term(double c, double lam, double xi)
+{
+  const double th = lam * c;
+  if (th <= -1.0) return 0.0;
+  if (xi == (double)(int)xi) return pp_ipow(xi >= 0 ? 1.0 + th : 1.0 / (1.0 + th), abs((int)xi));
+  return pp_series_pow(th, xi);
+}
+
+__device__ __noinline__ void pp_g3_block_force(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, int e1, int e2)
+{
+  // Structure.cpp:510-607 (non-periodic branch), unordered pairs x 2 on the circulant schedule of the G4 kernel
+  const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
+  const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
+  if (m1 == 0 || m2 == 0) return;
+  const bool same = (e1 == e2);
+  const int nG3 = S->nG3;
+  const int base = S->trip_base[e1][e2];
+  const int width = same ? 32 : (m2 < 32 ? m2 : 32);
+  const int npass = (m1 + width - 1) / width;
+  const int nt_max = same ? (m1 >> 1) : m2;
+  for (int pass = 0; pass < npass; pass++) {
+    const int a = pass * width + lane;
+    const bool act = (lane < width) && (a < m1);
+    const int ja = s1 + (act ? a : 0);
+    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+    double gx = 0.0, gy = 0.0, gz = 0.0;
+    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    const int sb = same ? s1 : s2, mb = same ? m1 : m2;
+    int b = same ? a + 1 : lane;
+    if (b >= mb) b -= mb;
+    for (int t = 0; t < nt_max; t++) {
+      if (act && t < nt) {
+        const int jb = sb + b;
+        const double bx = w.ux[jb], by = w.uy[jb], bz = w.uz[jb], Rb = w.R[jb];
+        const double c = ax * bx + ay * by + az * bz;
+        double d3x, d3y, d3z;
+        const double Rjk = pp_rjk(ax, ay, az, Ra, bx, by, bz, Rb, d3x, d3y, d3z);
+        if (!(Rjk > S->Rcut)) {
+          const double irjk = 1.0 / Rjk;
+          d3x *= irjk; d3y *= irjk; d3z *= irjk;                    // unit vector j2 -> j
+          double fax = 0, fay = 0, faz = 0, fbx = 0, fby = 0, fbz = 0;
+          for (int r = 0; r < nG3; r++) {
+            const double rc = S->g3_rc[r];
+            if (Ra >= rc || Rb >= rc || Rjk >= rc) continue;
+            const double lam = S->g3_lam[r], xi = S->g3_xi[r], eta = S->g3_eta[r];
+            const int fs = S->g3_fc[r];
+            const double term = 1.0 + lam * c;
+            if (term <= 0.0) continue;
+            const double pref = 2.0 * pow(2.0, 1.0 - xi) * w.buf[base + r] * pp_angular_term(c, lam, xi);   // x2: both orders
+            const double ex = exp(-eta * (Ra * Ra + Rb * Rb + Rjk * Rjk));
+            const double fR = pp_fc(Ra / rc, fs), fU = pp_fc(Rb / rc, fs), fJ = pp_fc(Rjk / rc, fs);
+            const double dG_dR = ex * fU * fJ * (pp_dfc(rc, Ra, fs) - 2.0 * Ra * eta * fR);
+            const double dG_dRu = ex * fR * fJ * (pp_dfc(rc, Rb, fs) - 2.0 * Rb * eta * fU);
+            const double dG_dRjk = ex * fR * fU * (pp_dfc(rc, Rjk, fs) - 2.0 * Rjk * eta * fJ);
+            const double dG_dcos = ex * (xi * lam / term) * fR * fU * fJ / (Ra * Rb);
+            const double Fjkx = pref * dG_dRjk * d3x, Fjky = pref * dG_dRjk * d3y, Fjkz = pref * dG_dRjk * d3z;
+            fax += pref * (dG_dR * ax + Rb * dG_dcos * (bx - c * ax)) + Fjkx;
+            fay += pref * (dG_dR * ay + Rb * dG_dcos * (by - c * ay)) + Fjky;
+            faz += pref * (dG_dR * az + Rb * dG_dcos * (bz - c * az)) + Fjkz;
+            fbx += pref * (dG_dRu * bx + Ra * dG_dcos * (ax - c * bx)) - Fjkx;
+            fby += pref * (dG_dRu * by + Ra * dG_dcos * (ay - c * by)) - Fjky;
+            fbz += pref * (dG_dRu * bz + Ra * dG_dcos * (az - c * bz)) - Fjkz;
+          }
+          gx += fax; gy += fay; gz += faz;
+          w.fx[jb] += fbx; w.fy[jb] += fby; w.fz[jb] += fbz;
+        }
+      }
+      b++;
+      if (b >= mb) b -= mb;
+      __syncwarp();
+    }
+    if (act) { w.fx[ja] += gx; w.fy[ja] += gy; w.fz[ja] += gz; }
+    __syncwarp();
+  }
+}
+
 // NX is the angular register tile NA_T on the general path and the number of power levels NB on the basis path.
 template <int NR_T, int NX, bool BASIS>
 __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
@@ -616,6 +753,10 @@ __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const De
   for (int g = lane; g < S->NG; g += 32) w.buf[g] = 0.0;
   __syncwarp();
   if (S->npair) pp_pair_rows_desc(w, cap, lane, S);
+  if (S->nG3) {
+    for (int e1 = 0; e1 < S->n_elem; e1++)
+      for (int e2 = e1; e2 < S->n_elem; e2++) pp_g3_block_desc(w, cap, lane, S, e1, e2, skip_rjk);
+  }
   if (S->nG4) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++)
@@ -759,6 +900,10 @@ template <int NR_T, int NX, bool BASIS>
 __device__ inline void pp_force_entries(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
 {
   if (S->npair) pp_pair_rows_force(w, cap, lane, S);
+  if (S->nG3) {
+    for (int e1 = 0; e1 < S->n_elem; e1++)
+      for (int e2 = e1; e2 < S->n_elem; e2++) pp_g3_block_force(w, cap, lane, S, e1, e2);
+  }
   if (S->nG4) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++)

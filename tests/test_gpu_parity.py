@@ -34,8 +34,6 @@ def add_all(ctx, c):
 @pytest.fixture(scope="module", params=TRAIN_CASES)
 def train_case(request):
     c = TrainCase(request.param)
-    if _has_g3(c):
-        pytest.skip("G3 rows: separate test")
     ctx = make_ctx(c)
     add_all(ctx, c)
     yield c, ctx
@@ -106,8 +104,6 @@ def test_epoch_is_bit_reproducible(train_case):
 @pytest.mark.parametrize("name", MD_CASES)
 def test_md_energy_forces(name):
     c = MDCase(name)
-    if _has_g3(c):
-        pytest.skip("G3 rows: separate test")
     ctx = capi.Context(0)
     try:
         ctx.set_descriptors(len(c.elements), c.G1, c.G2, c.G3, c.G4, c.rcut)
