@@ -31,7 +31,9 @@ struct WarpNbr {
   double *buf;                // [max(NG, ...)] G row (desc) or dE/dG row (force)
   double *cell;               // [PP_MAX_RAD*PP_MAX_ANG] reduced grid cells
   int n;                      // entries
-  int start[PP_MAX_ELEM + 1]; // element block boundaries after the sort
+  int* start;                 // [PP_MAX_ELEM + 1] element block boundaries after the sort.  Kept in shared memory:
+                              // a run-time indexed array member would push the whole struct (and with it every
+                              // pointer above) into local memory and turn all shared loads into generic ones.
 };
 
 __host__ __device__ inline size_t pp_warp_smem_bytes(int cap, int NR, int NG, bool force)
@@ -43,7 +45,7 @@ __host__ __device__ inline size_t pp_warp_smem_bytes(int cap, int NR, int NG, bo
   if (force) d += (size_t)NR * cap + 3 * (size_t)cap;
   d += (size_t)NG;
   d += PP_MAX_RAD * PP_MAX_ANG;
-  size_t bytes = d * sizeof(double) + 4 * (size_t)cap * sizeof(int);
+  size_t bytes = d * sizeof(double) + 4 * (size_t)cap * sizeof(int) + 8 * sizeof(int);
   return (bytes + 15) & ~(size_t)15;
 }
 
@@ -59,6 +61,7 @@ __device__ inline void pp_warp_views(WarpNbr& w, unsigned char* base, int cap, i
   w.cell = p; p += PP_MAX_RAD * PP_MAX_ANG;
   int* q = reinterpret_cast<int*>(p);
   w.elem = q; q += cap; w.selem = q; q += cap; w.idx = q; q += cap; w.sidx = q; q += cap;
+  w.start = q; q += 8;
   w.n = 0;
 }
 
@@ -165,7 +168,7 @@ __device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const 
   // destination index of every staged entry
   int base = 0;
   for (int e = 0; e < n_elem; e++) {
-    w.start[e] = base;
+    if (lane == 0) w.start[e] = base;
     int cnt = 0;
     for (int p0 = 0; p0 < n; p0 += 32) {
       int p = p0 + lane;
@@ -184,7 +187,8 @@ __device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const 
     }
     base += cnt;
   }
-  for (int e = n_elem; e <= PP_MAX_ELEM; e++) w.start[e] = base;
+  if (lane == 0)
+    for (int e = n_elem; e <= PP_MAX_ELEM; e++) w.start[e] = base;
   __syncwarp();
   // radial factors of the G4 grid: A_r = exp(-eta_r R^2) fc_r(R)  (0 beyond the row's own Rc: fc returns 0)
   const int NR = S->NR;
@@ -621,7 +625,7 @@ __device__ __forceinline__ double pp_rjk(double ax, double ay, double az, double
   return sqrt(dx * dx + dy * dy + dz * dz);
 }
 
-__device__ __noinline__ void pp_g3_block_desc(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, int e1, int e2,
+__device__ __noinline__ void pp_g3_block_desc(WarpNbr w, int cap, int lane, const DescSpec* __restrict__ S, int e1, int e2,
                                               bool nonperiodic)
 {
   const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
@@ -678,7 +682,7 @@ __device__ __forceinline__ double pp_angular_term(double c, double lam, double x
   return pp_series_pow(th, xi);
 }
 
-__device__ __noinline__ void pp_g3_block_force(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, int e1, int e2)
+__device__ __noinline__ void pp_g3_block_force(WarpNbr w, int cap, int lane, const DescSpec* __restrict__ S, int e1, int e2)
 {
   // Structure.cpp:510-607 (non-periodic branch), unordered pairs x 2 on the circulant schedule of the G4 kernel
   const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
