@@ -28,8 +28,14 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly one JSON line: NCCL's own banner / debug output goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout must carry exactly ONE JSON line, but libraries (NCCL's version banner, for one) write to file descriptor 1
+# directly.  Keep a private copy of the real stdout for the result and point fd 1 at stderr for everything else.
+_RESULT_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(obj):
+    os.write(_RESULT_FD, (json.dumps(obj) + "\n").encode())
 
 METRIC = "training structures/sec/epoch"
 UNIT = "structures/s"
@@ -229,37 +235,49 @@ def run_ours(args):
     ctx.close()
     if not args.no_md:
         # pair_nn (second metric of BASELINE.json); at N > 1 every rank runs an independent replica of the box
-        md = run_md_bench(torch, capi, synth, local_rank, args.md_cells, args.md_steps, 2)
+        md = run_md_bench(torch, capi, synth, local_rank, args.md_cells, args.md_steps, 2, dist=dist, rank=rank, world=world)
         if dist is not None:
             t = torch.tensor([md["ms_per_step"], md["e2e"]["ms_per_step"]], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             md["ms_per_step"], md["e2e"]["ms_per_step"] = [float(v) for v in t.cpu()]
             md["value"] = world * md["atoms_local"] / (md["ms_per_step"] * 1e-3)
             md["e2e"]["value"] = world * md["atoms_local"] / (md["e2e"]["ms_per_step"] * 1e-3)
-            md["replicas"] = world
+            md["n_gpus"] = world
+            md["partition"] = "%d sub-boxes along x (weak scaling), ghost forces of the x faces exchanged with ring neighbours " \
+                              "(NCCL send/recv), y/z images folded locally, energy all-reduced; e2e leg: per-rank host round trip " \
+                              "without the exchange" % world
         if rank == 0:
             if world == 1 and not args.no_cpu_baseline:
                 md["cpu_baseline"] = reference_md_rate()
             out["pair_nn"] = md
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.destroy_process_group()
 
 
 # ------------------------------------------------------------------------------------------------------------
 # second headline metric: pair_nn atom-steps/s (C5: diamond-Si supercell, C2 rows, 50-40-40-1 net)
-def md_system(synth, cells, seed=5, skin=1.0):
+def md_system(synth, cells, seed=5, skin=1.0, with_owner=False):
     cfg = synth.config_c5(cells)
     cell, cart, Z, _, _ = synth.make_structure(cfg, seed)
+    if with_owner:
+        x, Zall, nlocal, owner, shift = synth.expand_ghosts(cell, cart, Z, cfg.rcut + skin, with_owner=True)
+        return cfg, np.ascontiguousarray(x), nlocal, owner, shift
     x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + skin)
     return cfg, np.ascontiguousarray(x), nlocal
 
 
-def run_md_bench(torch, capi, synth, device, cells, steps, warmup):
+def run_md_bench(torch, capi, synth, device, cells, steps, warmup, dist=None, rank=0, world=1):
     """pp_md_build_neighbors once (LAMMPS rebuilds every 10 steps, pair_nn.cpp:276), then `steps` calls of the
-    PairNN::compute equivalent: device-resident (value) and through host buffers (e2e)."""
-    cfg, x, nlocal = md_system(synth, cells)
+    PairNN::compute equivalent: device-resident (value) and through host buffers (e2e).
+
+    N > 1 (weak scaling): the global box is N sub-boxes side by side along x, one per GPU, periodic.  Each rank
+    computes forces on its locals AND ghosts exactly as the reference does (pair_nn.cpp:182 writes ghost forces and
+    relies on LAMMPS' reverse communication); the harness then plays LAMMPS' part: ghost forces of y/z images are
+    folded onto their owners locally, those of the two x faces travel to the neighbouring ranks (NCCL send/recv,
+    ring) and are added there, and the energy is all-reduced.  That exchange is inside the timed region."""
+    cfg, x, nlocal, owner, shift = md_system(synth, cells, with_owner=True)
     ntotal = len(x)
     ctx = capi.Context(device)
     ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
@@ -277,18 +295,63 @@ def run_md_bench(torch, capi, synth, device, cells, steps, warmup):
     fd = torch.zeros_like(xd)
     ed = torch.zeros(1, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
-    for _ in range(warmup):
+    exchange = None
+    if world > 1:
+        own = torch.from_numpy(owner).to(dev)
+        gidx = torch.arange(nlocal, ntotal, device=dev)
+        sx = torch.from_numpy(shift[:, 0].copy()).to(dev)
+        sel_self, sel_left, sel_right = (sx == 0), (sx < 0), (sx > 0)
+        g_self, o_self = gidx[sel_self], own[sel_self]
+        g_left, o_left = gidx[sel_left], own[sel_left]
+        g_right, o_right = gidx[sel_right], own[sel_right]
+        left, right = (rank - 1) % world, (rank + 1) % world
+        recv_r = torch.empty((len(g_left), 3), dtype=torch.float64, device=dev)    # from the right neighbour: its left ghosts = my atoms
+        recv_l = torch.empty((len(g_right), 3), dtype=torch.float64, device=dev)
+
+        def exchange():
+            with torch.cuda.stream(stream):
+                fd.index_add_(0, o_self, fd[g_self])                      # local fold (y/z periodic images)
+                send_l, send_r = fd[g_left].contiguous(), fd[g_right].contiguous()
+                ops = [dist.P2POp(dist.isend, send_l, left), dist.P2POp(dist.isend, send_r, right),
+                       dist.P2POp(dist.irecv, recv_r, right), dist.P2POp(dist.irecv, recv_l, left)]
+                for w_ in dist.batch_isend_irecv(ops):
+                    w_.wait()
+                fd.index_add_(0, o_left, recv_r)
+                fd.index_add_(0, o_right, recv_l)
+                dist.all_reduce(ed)
+
+    def one_step():
+        with torch.cuda.stream(stream):
+            fd.zero_()                                                    # LAMMPS clears forces before Pair::compute
         ctx.md_step_device(xd.data_ptr(), fd.data_ptr(), ed.data_ptr())
+        if exchange is not None:
+            exchange()
+
+    for _ in range(warmup):
+        one_step()
     torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
     ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
     l0 = ctx.kernel_launches
     ev0.record(stream)
     for _ in range(steps):
-        ctx.md_step_device(xd.data_ptr(), fd.data_ptr(), ed.data_ptr())
+        one_step()
     ev1.record(stream)
     ev1.synchronize()
+    torch.cuda.synchronize()
     dev_ms = ev0.elapsed_time(ev1) / steps
     launches = ctx.kernel_launches - l0
+    # property check (outside the timed region): once every ghost force is back on its owner the forces on the local
+    # atoms are those of the periodic system, whose total force vanishes
+    one_step()
+    with torch.cuda.stream(stream):
+        f_loc = fd[:nlocal].clone()
+        if world == 1:
+            f_loc.index_add_(0, torch.from_numpy(owner).to(dev), fd[nlocal:])
+        fsum = float(f_loc.sum(dim=0).abs().max() / f_loc.abs().max())
+    torch.cuda.synchronize()
     # e2e: pinned host positions in, forces / energies out, every step
     x_pin = torch.from_numpy(x).pin_memory()
     f_pin = torch.zeros(ntotal, 3, dtype=torch.float64).pin_memory()
@@ -311,7 +374,7 @@ def run_md_bench(torch, capi, synth, device, cells, steps, warmup):
            "e2e": {"value": nlocal / (e2e_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": e2e_ms,
                    "h2d_bytes_per_step": 2 * 24 * ntotal, "d2h_bytes_per_step": 24 * ntotal + 8 * nlocal + 8},
            "phases_ms": {"descriptors": float(ph[0]), "network": float(ph[1]), "forces": float(ph[2])},
-           "neighbor_build_s": build_s, "gpu_launches": int(launches)}
+           "neighbor_build_s": build_s, "gpu_launches": int(launches), "total_force_over_max_force": fsum}
     peaks = _fp64_peaks()
     flops_desc, flops_force = 0.41e6, 1.21e6      # per atom at n = 45; the dominant kernel is the force kernel
     out["roofline"] = {"bound": "fp64-fma", "kernel": "md_force_kernel", "achieved": flops_force * nlocal / (ph[2] * 1e-3) / 1e12,
@@ -478,7 +541,7 @@ def run_reference(args):
            "cpu_baseline": r,
            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out))
+    emit(out)
 
 
 def main():

@@ -678,7 +678,7 @@ extern "C" int pp_precondition(pp_context* c, int input_precondition)
   if (nets_ready(c)) return 1;
   PP_CUDA(cudaSetDevice(c->device));
   const int NG = c->spec.NG;
-  const int n_cta = 64;
+  const int n_cta = 2 * ppk_mlp_max_ctas();
   cudaStream_t st = c->stream;
   if (c->d_stat_partial.ensure((size_t)n_cta * NG, 0, st) || c->d_stat_sums.ensure(2 * (size_t)NG, 0, st) || c->d_count.ensure(1, 0, st)) return 1;
   for (int e = 0; e < c->spec.n_elem; e++) {

@@ -746,25 +746,44 @@ column_stats_kernel(const double* __restrict__ G, int NG, const int* __restrict_
                     const int* __restrict__ tag, const double* __restrict__ mean, int pass, double* __restrict__ partial,
                     unsigned long long* __restrict__ count)
 {
+  // a block owns a contiguous range of rows; warp w takes rows r0+w, r0+w+8, ...; lanes take columns (coalesced);
+  // the 8 warps' sums are combined in shared memory in a fixed order
+  __shared__ double acc[8][33];
+  __shared__ unsigned long long cnt_s[8];
   const int per = (M + gridDim.x - 1) / gridDim.x;
   const int r0 = blockIdx.x * per, r1 = min(M, r0 + per);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned long long cnt = 0;
-  for (int k = threadIdx.x; k < NG; k += blockDim.x) {
+  for (int k0 = 0; k0 < NG; k0 += 32) {
+    const int k = k0 + lane;
+    const double mu = (pass && k < NG) ? mean[k] : 0.0;
     double s = 0.0;
-    const double mu = pass ? mean[k] : 0.0;
-    unsigned long long c = 0;
-    for (int r = r0; r < r1; r++) {
-      size_t atom = rows ? (size_t)rows[r] : (size_t)r;
+    for (int r = r0 + warp; r < r1; r += 8) {
+      const size_t atom = rows ? (size_t)rows[r] : (size_t)r;
       if (tag[atom_struct[atom]] != 0) continue;
-      double v = G[atom * NG + k];
-      if (pass) { double d = v - mu; s += d * d; }
-      else s += v;
-      c++;
+      if (k0 == 0 && lane == 0) cnt++;
+      if (k < NG) {
+        const double v = G[atom * NG + k];
+        if (pass) { const double d = v - mu; s += d * d; }
+        else s += v;
+      }
     }
-    partial[(size_t)blockIdx.x * NG + k] = s;
-    if (k == 0) cnt = c;
+    acc[warp][lane] = s;
+    __syncthreads();
+    if (warp == 0 && k < NG) {
+      double t = 0.0;
+      for (int w = 0; w < 8; w++) t += acc[w][lane];
+      partial[(size_t)blockIdx.x * NG + k] = t;
+    }
+    __syncthreads();
   }
-  if (threadIdx.x == 0 && pass == 0) atomicAdd(count, cnt);
+  if (lane == 0) cnt_s[warp] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0 && pass == 0) {
+    unsigned long long t = 0;
+    for (int w = 0; w < 8; w++) t += cnt_s[w];
+    atomicAdd(count, t);
+  }
 }
 
 int ppk_column_stats(const double* G, int NG, const int* rows, int M, const int* atom_struct, const int* tag,

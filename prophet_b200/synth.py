@@ -287,12 +287,16 @@ def random_network(cfg: Config, Z: int, seed: int) -> Dict[str, np.ndarray]:
 
 # ----------------------------------------------------------------------------------------------
 # MD harness helpers: what LAMMPS would hand to pair_style nn (pair_nn.cpp:112-153)
-def expand_ghosts(cell: np.ndarray, cart: np.ndarray, Z: np.ndarray, halo: float):
-    """Locals followed by periodic-image ghosts lying within ``halo`` of the (orthorhombic) box."""
+def expand_ghosts(cell: np.ndarray, cart: np.ndarray, Z: np.ndarray, halo: float, with_owner: bool = False):
+    """Locals followed by periodic-image ghosts lying within ``halo`` of the (orthorhombic) box.
+
+    with_owner=True also returns, per ghost, the index of the local atom it is an image of and its image shift
+    (what LAMMPS' reverse communication uses to return ghost forces to their owners)."""
     L = np.diag(cell)
     assert np.allclose(cell, np.diag(L)), "ghost expansion implemented for orthorhombic boxes"
     nrep = np.ceil(halo / L).astype(int)
-    xs, zs = [cart], [Z]
+    xs, zs, owners, shifts = [cart], [Z], [], []
+    idx = np.arange(len(cart))
     for i in range(-nrep[0], nrep[0] + 1):
         for j in range(-nrep[1], nrep[1] + 1):
             for k in range(-nrep[2], nrep[2] + 1):
@@ -302,6 +306,12 @@ def expand_ghosts(cell: np.ndarray, cart: np.ndarray, Z: np.ndarray, halo: float
                 keep = np.all((sh > -halo) & (sh < L + halo), axis=1)
                 xs.append(sh[keep])
                 zs.append(Z[keep])
+                owners.append(idx[keep])
+                shifts.append(np.tile(np.array([i, j, k], dtype=np.int32), (int(keep.sum()), 1)))
+    if with_owner:
+        owner = np.concatenate(owners) if owners else np.zeros(0, dtype=np.int64)
+        shift = np.concatenate(shifts) if shifts else np.zeros((0, 3), dtype=np.int32)
+        return np.concatenate(xs), np.concatenate(zs), len(cart), owner, shift
     return np.concatenate(xs), np.concatenate(zs), len(cart)
 
 
