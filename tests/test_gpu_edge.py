@@ -1,0 +1,156 @@
+"""GPU edge cases through the C ABI, each against the oracle: ragged batches, appended batches, structures that
+lack an element, isolated atoms, neighbour counts beyond the first shared-memory capacity, and error returns."""
+import numpy as np
+import pytest
+
+import oracle
+from golden_util import rel_err
+from prophet_b200 import capi, synth
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _nets(cfg, seed):
+    out = []
+    for z in cfg.elements:
+        n = synth.random_network(cfg, z, seed)
+        out.append((n["sizes"], n["params"], 0.2 * synth.normal(z, cfg.NG, 3), 0.5 + np.abs(synth.normal(z, cfg.NG, 4))))
+    return out
+
+
+def _check_epoch(cfg, structs, tags, seed=4):
+    """structs: list of (cell, cart, Z); compares descriptors, epoch outputs and evaluate() with the oracle."""
+    zmap = {z: i for i, z in enumerate(cfg.elements)}
+    ne = len(cfg.elements)
+    fracs = [capi.cart_to_frac(c, x) for c, x, _ in structs]
+    elems = [np.array([zmap[int(z)] for z in Z], dtype=np.int32) for _, _, Z in structs]
+    targets = np.array([-3.0 * len(e) + 0.1 * k for k, e in enumerate(elems)])
+    nets = _nets(cfg, seed)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        for e, (sizes, params, mean, scale) in enumerate(nets):
+            ctx.set_network(e, sizes, params, mean, scale)
+        # two appends must equal one
+        h = max(1, len(structs) // 2)
+        for lo, hi in ((0, h), (h, len(structs))):
+            if hi > lo:
+                ctx.add_structures([len(e) for e in elems[lo:hi]], np.stack([s[0] for s in structs[lo:hi]]),
+                                   np.concatenate(fracs[lo:hi]), np.concatenate(elems[lo:hi]), targets[lo:hi], tags[lo:hi])
+        Gs = []
+        for s in range(len(structs)):
+            G = ctx.get_descriptors(s)
+            Gref = oracle.descriptors_periodic(structs[s][0], fracs[s], elems[s], ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+            assert rel_err(G, Gref) < TOL or np.max(np.abs(G - Gref)) < 1e-14, (s, rel_err(G, Gref))
+            Gs.append(Gref.T)
+        off = np.zeros(len(structs) + 1, dtype=np.int32)
+        off[1:] = np.cumsum([len(e) for e in elems])
+        onets = [oracle.Net(sizes, params, mean, scale) for sizes, params, mean, scale in nets]
+        ro = oracle.epoch(off, np.concatenate(elems), np.concatenate(Gs), targets, np.array(tags, dtype=np.int32), onets)
+        r = ctx.epoch()
+        assert rel_err(r["gradient"], ro["gradient"]) < TOL
+        assert abs(r["SSE"] - ro["SSE"]) <= TOL * abs(ro["SSE"]) and abs(r["vSSE"] - ro["vSSE"]) <= TOL * max(abs(ro["vSSE"]), 1e-300)
+        assert r["nval"] == ro["nval"]
+        E = ctx.evaluate()
+        mask = np.array(tags) != 2
+        assert rel_err(E[mask], ro["E_struct"][mask]) < TOL
+        return ctx.n_structures
+    finally:
+        ctx.close()
+
+
+def test_ragged_single_element_batch_uses_packed_tiles():
+    """Structures of 8, 64, 16, 27 and 64 Si atoms: the fused epoch packs several whole structures per tile."""
+    cfg = synth.config_c2(1)
+    structs = []
+    for k, reps in enumerate([(1, 1, 1), (2, 2, 2), (1, 1, 2), (2, 2, 2), (1, 2, 2), (1, 1, 1), (1, 1, 1)]):
+        c = synth.config_c2(1)
+        c.lattice = synth.lattice_si(reps)
+        cell, cart, Z, _, _ = synth.make_structure(c, 500 + k)
+        structs.append((cell, cart, Z))
+    assert _check_epoch(cfg, structs, [0, 1, 0, 0, 2, 0, 1]) == 7
+
+
+def test_ragged_two_element_batch_with_a_structure_lacking_one_element():
+    cfg = synth.config_c3(1)
+    structs = []
+    for k, reps in enumerate([(2, 2, 3), (2, 2, 4), (2, 2, 2)]):
+        c = synth.config_c3(1)
+        c.lattice = synth.lattice_tio2(reps)
+        cell, cart, Z, _, _ = synth.make_structure(c, 600 + k)
+        structs.append((cell, cart, Z))
+    # an oxygen-only structure: the Ti net must receive no gradient from it (the reference would re-add a stale one,
+    # SURVEY appendix C #6; the mathematically correct gradient is what the oracle and the GPU path compute)
+    cell, cart, Z = structs[2]
+    keep = Z == 8
+    structs[2] = (cell, cart[keep], Z[keep])
+    _check_epoch(cfg, structs, [0, 0, 0])
+
+
+def test_isolated_atom_and_large_cutoff_overflowing_first_capacity():
+    # one atom in a big box: no neighbour image within Rcut -> all descriptors zero
+    cfg = synth.config_c2(1)
+    cell = np.eye(3) * 30.0
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        ctx.add_structures([1], cell[None], np.array([[0.5, 0.5, 0.5]]), [0], [0.0], [0])
+        assert np.all(ctx.get_descriptors(0) == 0.0)
+        nb = ctx.get_neighbors(0)
+        assert len(nb["neigh_j"]) == 0 and nb["neigh_offset"].tolist() == [0, 0]
+    finally:
+        ctx.close()
+    # Rcut 9: ~150 neighbour images per atom, beyond the initial 128-entry staging capacity (relaunch path)
+    big = synth.config_c2(1)
+    big.rcut = 9.0
+    big.G2 = [[9.0, 0.0, 0.05, 0.0], [9.0, 0.0, 0.4, 3.0]]
+    big.G4 = [[9.0, 0.0, 0.01, 1.0, 1.0], [9.0, 0.0, 0.01, 2.0, -1.0], [9.0, 0.0, 0.05, 4.0, 1.0]]
+    cell, cart, Z, _, _ = synth.make_structure(synth.config_c2(1), 700)
+    frac = capi.cart_to_frac(cell, cart)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(1, big.G1, big.G2, big.G3, big.G4, big.rcut)
+        ctx.add_structures([64], cell[None], frac, np.zeros(64, dtype=np.int32), [0.0], [0])
+        G = ctx.get_descriptors(0)
+        Gref = oracle.descriptors_periodic(cell, frac, np.zeros(64, dtype=np.int32), 1, big.G1, big.G2, big.G3, big.G4, big.rcut)
+        assert rel_err(G, Gref) < TOL
+        nb = ctx.get_neighbors(0)
+        ref = oracle.neighbors_periodic(cell, frac, big.rcut)
+        assert np.array_equal(nb["image_t"], ref["image_t"]) and np.array_equal(nb["neigh_j"], ref["neigh_j"])
+        assert np.diff(nb["image_offset"]).sum() / 64 > 128
+    finally:
+        ctx.close()
+
+
+def test_error_returns_are_messages_not_crashes():
+    cfg = synth.config_c2(1)
+    ctx = capi.Context(0)
+    try:
+        with pytest.raises(capi.PPError, match="pp_set_descriptors first"):
+            ctx.add_structures([1], np.eye(3)[None], np.zeros((1, 3)), [0], [0.0], [0])
+        ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        with pytest.raises(capi.PPError, match="element index"):
+            ctx.add_structures([1], np.eye(3)[None] * 20, np.zeros((1, 3)), [3], [0.0], [0])
+        with pytest.raises(capi.PPError, match="no network set"):
+            ctx.epoch()
+        net = synth.random_network(cfg, 14, 1)
+        with pytest.raises(capi.PPError, match="input width"):
+            ctx.set_network(0, [7, 3, 1], np.zeros(28), np.zeros(7), np.ones(7))
+        ctx.set_network(0, net["sizes"], net["params"], np.zeros(cfg.NG), np.ones(cfg.NG))
+        with pytest.raises(capi.PPError, match="no structures"):
+            ctx.epoch()
+        with pytest.raises(capi.PPError, match="fp_mode"):
+            capi.Context(0, fp_mode=32)
+        # clear and re-add
+        cell, cart, Z, _, _ = synth.make_structure(cfg, 1)
+        frac = capi.cart_to_frac(cell, cart)
+        ctx.add_structures([64], cell[None], frac, np.zeros(64, dtype=np.int32), [-300.0], [0])
+        a = ctx.epoch()
+        ctx.clear_structures()
+        assert ctx.n_structures == 0
+        ctx.add_structures([64], cell[None], frac, np.zeros(64, dtype=np.int32), [-300.0], [0])
+        b = ctx.epoch()
+        assert np.array_equal(a["gradient"], b["gradient"])
+    finally:
+        ctx.close()
