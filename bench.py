@@ -223,7 +223,7 @@ def run_ours(args):
             "roofline": {"bound": "tensor", "kernel": "mlp_kernel<TRAIN> (FP64 DMMA: forward recompute + backprop + weight gradients)",
                          "achieved": achieved, "peak": peaks["fp64_dmma_tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["fp64_dmma_tflops"],
                          "peak_source": peaks["source"], "algorithmic_flops_per_atom": train_flops_atom, "atoms_per_launch": atoms,
-                         "kernel_ms": bwd, "traffic": None,
+                         "kernel_ms": bwd, "traffic": _ncu_traffic(n_struct),
                          "hbm_view": {"algorithmic_bytes_per_atom": 8 * cfg.NG, "achieved_gbs": 8 * cfg.NG * atoms / (bwd * 1e-3) / 1e9,
                                       "peak_gbs": _measured_hbm()}},
             "phases_ms": {"forward": float(np.median(fwd_ms)), "backward_reduce": bwd, "collective": float(np.median(coll_ms))},
@@ -435,6 +435,17 @@ def _torch_nccl_path():
         if hits:
             return hits[0]
     return "libnccl.so.2"
+
+
+def _ncu_traffic(n_struct):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed ncu capture
+    (only valid for the workload it was captured on)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            d = json.load(f).get("mlp_kernel_fused_C2_%d" % n_struct)
+        return (d["dram_bytes_read"] + d["dram_bytes_write"]) if d else None
+    except Exception:
+        return None
 
 
 def _measured_hbm():
