@@ -202,7 +202,7 @@ __device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const 
       w.A[(size_t)r * cap + p] = ex * f;
       if (FORCE) w.dA[(size_t)r * cap + p] = ex * (pp_dfc(rc, R, fs) - 2.0 * R * eta * f);
     }
-    if (FORCE) { w.fx[p] = 0.0; w.fy[p] = 0.0; w.fz[p] = 0.0; }
+    if (FORCE) { w.fx[p] = 0.0; w.fy[p] = 0.0; w.fz[p] = 0.0; w.sR[p] = 1.0 / R; }   // staging is free now: keep 1/R there
   }
   __syncwarp();
 }
@@ -582,20 +582,30 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
             dpw[0][k] = (double)(1 << k) * pp0;
             dpw[1][k] = (double)(1 << k) * pp1;
           }
+          // 4 NR_T independent accumulation chains (per radial key and lambda group) instead of 2 long ones per key
+          double Ab[NR_T], dAb[NR_T], S0[NR_T], S1[NR_T], T0[NR_T], T1[NR_T];
+#pragma unroll
+          for (int r = 0; r < NR_T; r++) {
+            Ab[r] = Arow[r][jb]; dAb[r] = dArow[r][jb];
+            S0[r] = W[r][0][0] * pw[0][0]; S1[r] = W[r][1][0] * pw[1][0];
+            T0[r] = W[r][0][0] * dpw[0][0]; T1[r] = W[r][1][0] * dpw[1][0];
+          }
+#pragma unroll
+          for (int k = 1; k < NB; k++)
+#pragma unroll
+            for (int r = 0; r < NR_T; r++) {
+              S0[r] = fma(W[r][0][k], pw[0][k], S0[r]); S1[r] = fma(W[r][1][k], pw[1][k], S1[r]);
+              T0[r] = fma(W[r][0][k], dpw[0][k], T0[r]); T1[r] = fma(W[r][1][k], dpw[1][k], T1[r]);
+            }
           double dRa = 0.0, dRb = 0.0, dc = 0.0;
 #pragma unroll
           for (int r = 0; r < NR_T; r++) {
-            double Sr = 0.0, Tr = 0.0;
-#pragma unroll
-            for (int g = 0; g < 2; g++)
-#pragma unroll
-              for (int k = 0; k < NB; k++) { Sr = fma(W[r][g][k], pw[g][k], Sr); Tr = fma(W[r][g][k], dpw[g][k], Tr); }
-            const double Ab = Arow[r][jb], dAb = dArow[r][jb];
-            dRa = fma(Sr * dAa[r], Ab, dRa);
-            dRb = fma(Sr * Aa[r], dAb, dRb);
-            dc = fma(Tr * Aa[r], Ab, dc);
+            const double Sr = S0[r] + S1[r], Tr = T0[r] + T1[r];
+            dRa = fma(Sr * dAa[r], Ab[r], dRa);
+            dRb = fma(Sr * Aa[r], dAb[r], dRb);
+            dc = fma(Tr * Aa[r], Ab[r], dc);
           }
-          const double ca = dc * invRa, cb = dc / Rb;
+          const double ca = dc * invRa, cb = dc * w.sR[jb];          // sR holds 1/R after pp_finalize_entries
           gx += dRa * ax + ca * (bx - c * ax);
           gy += dRa * ay + ca * (by - c * ay);
           gz += dRa * az + ca * (bz - c * az);
