@@ -34,7 +34,8 @@ struct MlpPlan {
   int ws_off[PP_MAX_LAYERS], hs_off[PP_MAX_LAYERS], ds_off[PP_MAX_LAYERS + 1];
   int x_off[2];                       // double-buffered raw descriptor tiles
   int ws_rows[PP_MAX_LAYERS];         // rows of Ws_l held in shared memory (zero padded)
-  int cvec_off, erow_off, mu_off, is_off, red_off;
+  int cvec_off, erow_off, mu_off, is_off, red_off, sttgt_off;
+  int stint_off_bytes;                // per-tile structure table: row offsets [TM+1] and tags [TM] (ints)
   int tf_off_bytes, desc_off_bytes;
   int n_dw_tiles;
   size_t smem_bytes;
@@ -85,10 +86,14 @@ static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>
   p.mu_off = (int)off; off += p.kpitch[0];
   p.is_off = (int)off; off += p.kpitch[0];
   p.red_off = (int)off; off += 3 * MLP_WARPS;
+  p.sttgt_off = (int)off; off += TM;
   p.tf_off_bytes = (int)(off * sizeof(double));
   int nodes = 0;
   for (int l = 1; l <= p.L; l++) nodes += p.n[l];
   size_t bytes = off * sizeof(double) + (size_t)nodes * sizeof(int);
+  bytes = (bytes + 15) & ~(size_t)15;
+  p.stint_off_bytes = (int)bytes;
+  bytes += (size_t)(2 * TM + 2) * sizeof(int);
   bytes = (bytes + 15) & ~(size_t)15;
   p.desc_off_bytes = (int)bytes;
   int t = 0;
@@ -305,21 +310,32 @@ mlp_kernel(MlpArgs a, MlpPlan p)
   const int kp0 = p.kpitch[0];
   const bool vec16 = (NG & 1) == 0;
 
-  // tile geometry
-  auto tile_rows = [&](int tile, int& row0, int& nvalid) {
-    if (MODE == PP_MLP_FUSED) {
-      const long long r0 = a.struct_atom0[a.tile_struct0[tile]];
-      row0 = (int)r0;
-      nvalid = (int)(a.struct_atom0[a.tile_struct0[tile + 1]] - r0);
-    } else {
-      row0 = tile * TM;
-      nvalid = min(TM, a.M - row0);
+  // tile geometry (first / one-past-last structure, first row, row count); FUSED tiles come from two dependent global
+  // loads, so the geometry of tile t+2 is requested while tile t is being processed
+  struct Geom { int s0, s1, row0, nvalid; };
+  auto tile_geom = [&](int tile) {
+    Geom gm;
+    gm.s0 = gm.s1 = gm.row0 = gm.nvalid = 0;
+    if (tile < n_tiles) {
+      if (MODE == PP_MLP_FUSED) {
+        gm.s0 = a.tile_struct0[tile];
+        gm.s1 = a.tile_struct0[tile + 1];
+        const long long r0 = a.struct_atom0[gm.s0];
+        gm.row0 = (int)r0;
+        gm.nvalid = (int)(a.struct_atom0[gm.s1] - r0);
+      } else {
+        gm.row0 = tile * TM;
+        gm.nvalid = min(TM, a.M - gm.row0);
+      }
     }
+    return gm;
   };
+  int* st_lo = reinterpret_cast<int*>(smem_raw + p.stint_off_bytes);     // [TM+1] first row of each structure of the tile
+  int* st_tag = st_lo + TM + 1;                                            // [TM]
+  double* st_tgt = sm + p.sttgt_off;                                       // [TM]
   // asynchronous copy of one tile's raw descriptor rows into X[buf]
-  auto issue_load = [&](int tile, int buf) {
-    int row0, nvalid;
-    tile_rows(tile, row0, nvalid);
+  auto issue_load = [&](const Geom& gm, int buf) {
+    const int row0 = gm.row0, nvalid = gm.nvalid;
     double* X = sm + p.x_off[buf];
     for (int r = warp; r < TM; r += MLP_WARPS) {
       double* dst = X + (size_t)r * kp0;
@@ -336,16 +352,26 @@ mlp_kernel(MlpArgs a, MlpPlan p)
   };
 
   int buf = 0;
-  if ((int)blockIdx.x < n_tiles) issue_load(blockIdx.x, 0);
+  Geom g_cur = tile_geom(blockIdx.x), g_nxt = tile_geom(blockIdx.x + gridDim.x);
+  if ((int)blockIdx.x < n_tiles) issue_load(g_cur, 0);
   __syncthreads();
 
   const int mt = warp >> 1, half = warp & 1;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
-    int row0, nvalid;
-    tile_rows(tile, row0, nvalid);
+    const int row0 = g_cur.row0, nvalid = g_cur.nvalid;
+    const int s_first = g_cur.s0, s_last = g_cur.s1;
+    const Geom g_nn = tile_geom(tile + 2 * gridDim.x);      // consumed one iteration from now
     cp_async_wait_all();
     __syncthreads();
-    if (tile + (int)gridDim.x < n_tiles) issue_load(tile + gridDim.x, buf ^ 1);
+    if (tile + (int)gridDim.x < n_tiles) issue_load(g_nxt, buf ^ 1);
+    if (MODE == PP_MLP_FUSED) {
+      // structure table of this tile; its global-load latency hides behind the forward pass (read after the next barrier)
+      for (int i = tid; i <= s_last - s_first; i += MLP_THREADS) {
+        const int sidx = s_first + i;
+        st_lo[i] = (int)(a.struct_atom0[sidx] - row0);
+        if (sidx < s_last) { st_tgt[i] = a.target[sidx]; st_tag[i] = a.tag[sidx]; }
+      }
+    }
     const double* X = sm + p.x_off[buf];
     if (MODE == PP_MLP_TRAIN || MODE == PP_MLP_INPUT_GRAD) {
       for (int r = tid; r < TM; r += MLP_THREADS) {
@@ -412,18 +438,17 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     if (MODE == PP_MLP_FUSED) {
       // ---- per-structure energy, error and loss terms (Potential.cpp:641-668); one warp per structure ----------
       __syncthreads();
-      const int s_first = a.tile_struct0[tile], s_last = a.tile_struct0[tile + 1];
-      for (int s = s_first + warp; s < s_last; s += MLP_WARPS) {
-        const int r_lo = (int)(a.struct_atom0[s] - row0), r_hi = (int)(a.struct_atom0[s + 1] - row0);
+      for (int i = warp; i < s_last - s_first; i += MLP_WARPS) {
+        const int r_lo = st_lo[i], r_hi = st_lo[i + 1];
         double e = 0.0;
         for (int r = r_lo + lane; r < r_hi; r += 32) e += erow[r];
         e = pp_warp_sum(e) + a.out_mean;
-        const double err = e - a.target[s];
-        const int tag = a.tag[s];
+        const double err = e - st_tgt[i];
+        const int tag = st_tag[i];
         double c = 0.0;
         if (tag == 0) { c = 2.0 * err * a.out_scale; sse_w += err * err; }
         else if (tag == 1) { vsse_w += err * err; nval_w += 1.0; }
-        if (lane == 0) a.E_struct[s] = e;
+        if (lane == 0) a.E_struct[s_first + i] = e;
         for (int r = r_lo + lane; r < r_hi; r += 32) cvec[r] = c;
       }
       for (int r = nvalid + tid; r < TM; r += MLP_THREADS) cvec[r] = 0.0;
@@ -499,14 +524,16 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     if constexpr (GRADW) {
       __syncthreads();
       {
+        // output-node gradient on the threads of the LAST warps (they own the fewest weight-gradient tiles)
         const int n_in = p.n[L - 1];
-        if (tid <= n_in) {
+        const int j = MLP_THREADS - 1 - tid;
+        if (j <= n_in) {
           double s = 0.0;
           if (L == 1) {
-            const double m = mu[tid], sc = is[tid];
-            for (int r = 0; r < TM; r++) s = fma(cvec[r], (X[(size_t)r * kp0 + tid] - m) * sc, s);
+            const double m = mu[j], sc = is[j];
+            for (int r = 0; r < TM; r++) s = fma(cvec[r], (X[(size_t)r * kp0 + j] - m) * sc, s);
           } else {
-            const double* Hl = sm + p.hs_off[L - 1] + tid;
+            const double* Hl = sm + p.hs_off[L - 1] + j;
             const int kp = p.kpitch[L - 1];
             for (int r = 0; r < TM; r++) s = fma(cvec[r], Hl[(size_t)r * kp], s);
           }
@@ -550,6 +577,8 @@ mlp_kernel(MlpArgs a, MlpPlan p)
         }
       }
     }
+    g_cur = g_nxt;
+    g_nxt = g_nn;
   }
   cp_async_wait_all();
 
@@ -558,7 +587,8 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     double* out = a.partial + (size_t)blockIdx.x * (a.P_total + 3) + a.p_off;
     {
       const int n_in = p.n[L - 1];
-      if (tid <= n_in) out[net.w_off[L - 1] + tid] = dwout;
+      const int j = MLP_THREADS - 1 - tid;
+      if (j <= n_in) out[net.w_off[L - 1] + j] = dwout;
     }
 #pragma unroll
     for (int t = 0; t < OWN; t++) {
