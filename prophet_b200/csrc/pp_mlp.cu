@@ -436,23 +436,37 @@ mlp_kernel(MlpArgs a, MlpPlan p)
       }
     }
     if (MODE == PP_MLP_FUSED) {
-      // ---- per-structure energy, error and loss terms (Potential.cpp:641-668); one warp per structure ----------
+      // ---- per-structure energy, error and loss terms (Potential.cpp:641-668) --------------------------------
+      // After this one barrier every warp works out the error factor c of ITS OWN 8 rows by summing the energies
+      // of the structures that overlap them (redundantly with the other warps those structures touch: a few dozen
+      // shared-memory loads), so no second barrier is needed before the backward pass.  The structure's outputs
+      // are written by the warp whose rows contain the structure's first atom.
       __syncthreads();
-      for (int i = warp; i < s_last - s_first; i += MLP_WARPS) {
-        const int r_lo = st_lo[i], r_hi = st_lo[i + 1];
-        double e = 0.0;
-        for (int r = r_lo + lane; r < r_hi; r += 32) e += erow[r];
-        e = pp_warp_sum(e) + a.out_mean;
-        const double err = e - st_tgt[i];
-        const int tag = st_tag[i];
-        double c = 0.0;
-        if (tag == 0) { c = 2.0 * err * a.out_scale; sse_w += err * err; }
-        else if (tag == 1) { vsse_w += err * err; nval_w += 1.0; }
-        if (lane == 0) a.E_struct[s_first + i] = e;
-        for (int r = r_lo + lane; r < r_hi; r += 32) cvec[r] = c;
+      if (mt < TM / 8) {
+        const int rb = 8 * mt, re = 8 * mt + 8;
+        const int ns = s_last - s_first;
+        if (lane < 8) cvec[rb + lane] = 0.0;
+        __syncwarp();
+        for (int i = 0; i < ns; i++) {
+          const int r_lo = st_lo[i], r_hi = st_lo[i + 1];
+          if (r_hi <= rb) continue;
+          if (r_lo >= re) break;
+          double e = 0.0;
+          for (int r = r_lo + lane; r < r_hi; r += 32) e += erow[r];
+          e = pp_warp_sum(e) + a.out_mean;
+          const double err = e - st_tgt[i];
+          const int tag = st_tag[i];
+          const double c = (tag == 0) ? 2.0 * err * a.out_scale : 0.0;
+          if (half == 0 && r_lo >= rb && r_lo < re) {
+            if (tag == 0) sse_w += err * err;
+            else if (tag == 1) { vsse_w += err * err; nval_w += 1.0; }
+            if (lane == 0) a.E_struct[s_first + i] = e;
+          }
+          const int r = rb + lane;
+          if (lane < 8 && r >= r_lo && r < r_hi) cvec[r] = c;
+        }
+        __syncwarp();
       }
-      for (int r = nvalid + tid; r < TM; r += MLP_THREADS) cvec[r] = 0.0;
-      __syncthreads();
     } else if (BACKWARD) {
       __syncthreads();   // cvec
     }
