@@ -15,6 +15,8 @@
 //       Potential::train (Potential.cpp:607-672) so every per-iteration quantity can be dumped.
 //   ref_driver md <md_case.txt> <out.bin>
 //       Follows PairNN::settings/coeff/compute (pair_nn.cpp:499-526, 223-259, 112-188) without LAMMPS.
+//   ref_driver ks <samples.txt> <out.bin>
+//       samples.txt: n1 v... n2 v...; calls Analysis::KS (Analysis.cpp:149-202) and dumps D and p.
 
 #include <algorithm>
 #include <cmath>
@@ -50,6 +52,7 @@
 #include "NN.h"
 #include "Optimizer.h"
 #include "Structure.h"
+#include "Analysis.h"
 
 using namespace std;
 
@@ -326,10 +329,28 @@ static int run_md(const string& case_file)
   return 0;
 }
 
+static int run_ks(const string& file)
+{
+  ifstream in(file.c_str());
+  if (!in.is_open()) { fprintf(stderr, "cannot open %s\n", file.c_str()); return 2; }
+  int n1 = 0, n2 = 0;
+  in >> n1;
+  vector<REAL> a(n1);
+  for (int i = 0; i < n1; i++) in >> a[i];
+  in >> n2;
+  vector<REAL> b(n2);
+  for (int i = 0; i < n2; i++) in >> b[i];
+  Analysis A;
+  REAL D = A.KS(a, b);
+  put_scalar("D", D);
+  put_scalar("p", A.p);
+  return 0;
+}
+
 int main(int argc, char** argv)
 {
   if (argc < 4) {
-    fprintf(stderr, "usage: ref_driver train <input_file> <out.bin> <n_iter> | md <case.txt> <out.bin>\n");
+    fprintf(stderr, "usage: ref_driver train <input_file> <out.bin> <n_iter> | md <case.txt> <out.bin> | ks <samples.txt> <out.bin>\n");
     return 2;
   }
   string mode = argv[1];
@@ -338,6 +359,7 @@ int main(int argc, char** argv)
   int rc = 2;
   if (mode == "train") rc = run_train(argv[2], argc > 4 ? atoi(argv[4]) : 0);
   else if (mode == "md") rc = run_md(argv[2]);
+  else if (mode == "ks") rc = run_ks(argv[2]);
   fclose(g_out);
   return rc;
 }

@@ -14,10 +14,22 @@ extern "C" {
 // ---- Rprop driven step by step with caller-supplied gradients -------------------------------------------------
 struct pph_opt { Parallel mpi; FunctionalParams F; Optimizer* opt; };
 
+// line_min_epsilon / debug / sd_momentum as the input_file keys of those names would set them
+void* pph_optimizer_create2(int P, const double* x0, const char* algorithm, int Nsystems, double line_min_epsilon,
+                            double debug, double sd_momentum);
 void* pph_optimizer_create(int P, const double* x0, const char* algorithm, int Nsystems)
+{
+  FunctionalParams d;
+  return pph_optimizer_create2(P, x0, algorithm, Nsystems, d.line_min_epsilon, d.debug, d.sd_momentum);
+}
+void* pph_optimizer_create2(int P, const double* x0, const char* algorithm, int Nsystems, double line_min_epsilon,
+                            double debug, double sd_momentum)
 {
   pph_opt* h = new pph_opt();
   h->F.training_algorithm = algorithm;
+  h->F.line_min_epsilon = line_min_epsilon;
+  h->F.debug = debug;
+  h->F.sd_momentum = sd_momentum;
   h->F.Niterations = 1 << 30;
   h->opt = new Optimizer(&h->mpi, h->F, Nsystems);
   h->opt->do_print = false;
@@ -110,6 +122,15 @@ int pph_read_vasprun(const char* dir, double* cell9, int* natoms, double* pos, i
   memcpy(Z, sd.Z.data(), sizeof(int) * sd.Z.size());
   *target = sd.target;
   return 0;
+}
+
+// Analysis::KS as Potential::validate uses it; returns D, *p_out the approximate p value
+double pph_ks(const double* a, int n1, const double* b, int n2, double* p_out)
+{
+  REAL p = 0;
+  REAL D = approximate_KS(std::vector<REAL>(a, a + n1), std::vector<REAL>(b, b + n2), &p);
+  *p_out = p;
+  return D;
 }
 
 int pph_auto_rows(double Rcut, int Nradial, int Nangular, double* G2_out, int* nG2, double* G4_out, int* nG4, int cap)

@@ -150,14 +150,18 @@ class Optimizer {
   // the algorithms, exposed for tests
   std::vector<REAL> rprop();
   std::vector<REAL> steepest_descent();
+  std::vector<REAL> steepest_descent_with_line_opt();   // Optimizer.cpp:457-491
+  std::vector<REAL> LBFGS();                            // Optimizer.cpp:607-696
+  REAL brent_line_min(REAL tolerance);                  // Optimizer.cpp:709-869
 
  private:
   std::vector<REAL> switch_to_sd();
   std::vector<REAL> switch_to_rprop();
+  std::vector<REAL> switch_to_BFGS();
   std::vector<REAL> next_x();
   Parallel* mpi;
   FunctionalParams F;
-  enum Algo { RPROP, SD } algo;
+  enum Algo { RPROP, SD, SD_LINE, BFGS } algo;
   bool allow_training_switch, early_stop;
   int my_Nsystems, my_max_steps, my_Ncheckpoint, my_Nbackup, my_Nparameters, iteration_counter;
   bool my_Tbackup, my_is_converged, my_is_checkpoint, my_is_backup, line_min;
@@ -167,7 +171,16 @@ class Optimizer {
   std::deque<std::vector<REAL> > x, gradient;
   std::deque<REAL> Errors;
   std::vector<REAL> search_direction, rprop_weights, rprop_step;
+  // L-BFGS / Brent line minimisation state (Optimizer.h:215-234)
+  int BFGS_Nmax;
+  REAL convergence, line_last_E, line_last_alpha, line_last_g, brent_c, brent_g_c, brent_d;
+  bool brent_flag;
+  std::vector<REAL> BFGS_last_x, BFGS_last_gradient;
+  std::vector<std::vector<REAL> > s, y;
+  std::deque<REAL> rho, line_g, line_alpha;
 };
+
+REAL approximate_KS(const std::vector<REAL>& data1, const std::vector<REAL>& data2, REAL* p_out);   // Analysis.cpp:149-202
 
 // ---- Potential ------------------------------------------------------------------------------------------------
 class Potential {
@@ -176,7 +189,7 @@ class Potential {
   ~Potential();
   REAL train();                       // Potential.cpp:607-693
   std::vector<REAL> evaluate();       // :515-551
-  void validate();                    // :971-1122 (without the Kolmogorov-Smirnov appendix)
+  void validate();                    // :971-1122
   void save();                        // :296-317
   void backup(int niter);             // :323-345
   pp_context* context() { return ctx; }

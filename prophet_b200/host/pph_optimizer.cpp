@@ -36,7 +36,9 @@ Optimizer::Optimizer(Parallel* mpi_in, const FunctionalParams& params, int Nsyst
   if (a == "default") { algo = RPROP; allow_training_switch = true; }
   else if (a == "rprop") { algo = RPROP; allow_training_switch = false; }
   else if (a == "steepest_descent") { algo = SD; allow_training_switch = false; }
-  else PPH_ERROR("Training algorithm \"" + a + "\" is not implemented in this build (default, rprop, steepest_descent are)");
+  else if (a == "steepest_descent_with_line_opt") { algo = SD_LINE; allow_training_switch = false; }
+  else if (a == "bfgs") { algo = BFGS; allow_training_switch = false; }
+  else PPH_ERROR("Training algorithm \"" + a + "\" is not implemented");
   iteration_counter = 1;
   my_is_converged = my_is_checkpoint = my_is_backup = false;
   line_min = true;
@@ -48,6 +50,10 @@ Optimizer::Optimizer(Parallel* mpi_in, const FunctionalParams& params, int Nsyst
   alpha1 = lambda0;
   rprop_weights_max = 0.5;
   rprop_weights_min = 1000.0 * std::numeric_limits<REAL>::epsilon();
+  BFGS_Nmax = 77;
+  convergence = 100 * std::numeric_limits<REAL>::epsilon();
+  line_last_E = line_last_alpha = line_last_g = brent_c = brent_g_c = brent_d = 0.0;
+  brent_flag = false;
 }
 
 void Optimizer::init(const std::vector<REAL>& x0)
@@ -154,9 +160,8 @@ std::vector<REAL> Optimizer::steepest_descent()
       dg += std::sqrt(dot(gradient[i], gradient[i])) - std::sqrt(dot(gradient[i - 1], gradient[i - 1]));
     }
     dg /= ave;
-    // the reference would hand over to L-BFGS when dg in (-debug, 0); that optimizer is not part of this build,
-    // so steepest descent simply continues in that case
-    if (dg > debug) return switch_to_rprop();
+    if (dg > -debug && dg < 0) return switch_to_BFGS();
+    else if (dg > debug) return switch_to_rprop();
   }
   for (size_t i = 0; i < x1.size(); i++)
     x1[i] = x1[i] - alpha1 * (search_direction[i] + F.sd_momentum * (x[N - 1][i] - x[N - 2][i]));
@@ -182,7 +187,205 @@ std::vector<REAL> Optimizer::switch_to_rprop()
   return rprop();
 }
 
-std::vector<REAL> Optimizer::next_x() { return algo == RPROP ? rprop() : steepest_descent(); }
+std::vector<REAL> Optimizer::switch_to_BFGS()
+{
+  if (mpi->io_node() && do_print) std::cout << "----- Switching to BFGS -----" << std::endl;     // Optimizer.h:262-268
+  search_direction.clear();
+  algo = BFGS;
+  return LBFGS();
+}
+
+std::vector<REAL> Optimizer::next_x()
+{
+  switch (algo) {
+    case RPROP: return rprop();
+    case SD: return steepest_descent();
+    case SD_LINE: return steepest_descent_with_line_opt();
+    default: return LBFGS();
+  }
+}
+
+static std::vector<REAL> normalized(const std::vector<REAL>& v)
+{
+  std::vector<REAL> out = v;
+  REAL norm = std::sqrt(dot(v, v));
+  for (size_t i = 0; i < v.size(); i++) out[i] /= norm;
+  return out;
+}
+
+std::vector<REAL> Optimizer::steepest_descent_with_line_opt()
+{
+  // Optimizer.cpp:457-491
+  if (search_direction.size() == 0 || line_min) {
+    std::vector<REAL> x1 = x.back();
+    search_direction = normalized(gradient.back());
+    BFGS_last_x = x.back();
+    BFGS_last_gradient = gradient.back();
+    REAL delta = brent_line_min(F.line_min_epsilon);
+    for (size_t i = 0; i < x1.size(); i++) x1[i] -= delta * search_direction[i];
+    return x1;
+  }
+  std::vector<REAL> x1 = BFGS_last_x;
+  REAL delta = brent_line_min(F.line_min_epsilon);
+  for (size_t i = 0; i < search_direction.size(); i++) x1[i] -= delta * search_direction[i];
+  return x1;
+}
+
+std::vector<REAL> Optimizer::LBFGS()
+{
+  // Optimizer.cpp:607-696
+  if (search_direction.size() == 0) {
+    std::vector<REAL> x1 = x.back();
+    search_direction = normalized(gradient.back());
+    BFGS_last_x = x.back();
+    BFGS_last_gradient = gradient.back();
+    REAL delta = brent_line_min(F.line_min_epsilon);
+    for (size_t i = 0; i < x1.size(); i++) x1[i] -= delta * search_direction[i];
+    return x1;
+  }
+  if (!line_min) {
+    std::vector<REAL> x1 = BFGS_last_x;
+    REAL delta = brent_line_min(F.line_min_epsilon);
+    for (size_t i = 0; i < search_direction.size(); i++) x1[i] -= delta * search_direction[i];
+    return x1;
+  }
+  std::vector<REAL> alpha(s.size() + 1, 0.0);
+  REAL beta;
+  search_direction = gradient.back();
+  if (!(iteration_counter % (8 * BFGS_Nmax))) { s.clear(); y.clear(); rho.clear(); }
+  const size_t P = search_direction.size();
+  s.push_back(std::vector<REAL>(P, 0.0));
+  y.push_back(std::vector<REAL>(P, 0.0));
+  for (size_t i = 0; i < P; i++) {
+    s.back()[i] = x.back()[i] - BFGS_last_x[i];
+    y.back()[i] = gradient.back()[i] - BFGS_last_gradient[i];
+  }
+  rho.push_back(1 / dot(y.back(), s.back()));
+  if ((int)s.size() > BFGS_Nmax) { s.erase(s.begin()); y.erase(y.begin()); rho.pop_front(); }
+  for (int i = (int)s.size() - 1; i >= 0; i--) {
+    alpha.at(i) = rho[i] * dot(s[i], search_direction);
+    for (size_t j = 0; j < P; j++) search_direction[j] -= alpha[i] * y[i][j];
+  }
+  REAL H = dot(y.back(), s.back()) / dot(y.back(), y.back());
+  for (size_t j = 0; j < P; j++) search_direction[j] *= H;
+  for (size_t i = 0; i < s.size(); i++) {
+    beta = rho[i] * dot(y[i], search_direction);
+    for (size_t j = 0; j < P; j++) search_direction[j] += s[i][j] * (alpha[i] - beta);
+  }
+  search_direction = normalized(search_direction);
+  BFGS_last_x = x.back();
+  BFGS_last_gradient = gradient.back();
+  REAL delta = brent_line_min(F.line_min_epsilon);
+  std::vector<REAL> x1 = BFGS_last_x;
+  for (size_t i = 0; i < P; i++) x1[i] -= delta * search_direction[i];
+  return x1;
+}
+
+
+REAL Optimizer::brent_line_min(REAL tolerance)
+{
+  // Optimizer.cpp:709-869.  The line search is driven one gradient evaluation per call: the bracket lives in the
+  // two-slot deques line_alpha / line_g (front = the end with the larger |g| once a sign change is bracketed),
+  // (brent_c, brent_g_c) is the previous best point and brent_d the one before it.  The value returned is the
+  // step length along -search_direction measured from BFGS_last_x.
+  const REAL eps = std::numeric_limits<REAL>::epsilon();
+  const REAL g = dot(normalized(search_direction), gradient.back());
+  // ---- a fresh line: take the trial step lambda0 ----
+  if (line_min || line_g.empty()) {
+    line_min = false;
+    line_g.assign(1, g);
+    line_alpha.assign(1, 0.0);
+    alpha1 = lambda0;
+    line_last_E = Errors.back();
+    line_last_alpha = alpha1;
+    line_last_g = g;
+    return alpha1;
+  }
+
+  // ---- finished: slope small enough, or the bracket has collapsed ----
+  const bool collapsed = std::abs(line_alpha.front() - line_alpha.back()) < 20 * eps;
+  if (std::abs(g) < tolerance || (line_g.size() == 2 && collapsed)) {
+    line_min = true;
+    if (collapsed && std::abs(g) > tolerance)
+      std::cout << "<<WARNING>> In BFGS: Line optimization could not reach the requested precision" << std::endl;
+    return alpha1;
+  }
+
+  if (line_g.size() == 1) {
+    if (sign(g * line_g.back()) <= 0) {
+      // the slope changed sign: the minimum is bracketed; keep the smaller |g| at the back
+      if (std::abs(g) <= std::abs(line_g.back())) { line_g.push_back(g); line_alpha.push_back(alpha1); }
+      else { line_g.push_front(g); line_alpha.push_front(alpha1); }
+      brent_c = line_alpha.front();
+      brent_g_c = line_g.front();
+      brent_flag = true;
+    } else {
+      // still going downhill along the line: expand (double, or secant when the slope is flattening)
+      if (Errors.back() <= line_last_E) {
+        line_alpha.push_back(alpha1);
+        line_g.push_back(g);
+        line_last_g = g;
+        line_last_alpha = alpha1;
+        line_last_E = Errors.back();
+        if (std::abs(g) >= std::abs(line_g.front())) alpha1 *= 2.0;
+        else alpha1 = alpha1 - g * (line_alpha.back() - line_alpha.front()) / (line_g.back() - line_g.front());
+        line_alpha.pop_front();
+        line_g.pop_front();
+      } else if (alpha1 < 10 * lambda0) {
+        // the error rose within a few trial steps: give the direction up and restart from the plain gradient
+        line_min = true;
+        s.clear();
+        y.clear();
+        rho.clear();
+        search_direction = normalized(gradient.back());
+        BFGS_last_x = x.back();
+        BFGS_last_gradient = gradient.back();
+      } else {
+        // overshot: go back to the last accepted point and creep forward by lambda0
+        alpha1 = line_last_alpha + sign(line_last_alpha) * lambda0;
+        line_alpha.front() = line_last_alpha;
+        line_g.front() = line_last_g;
+      }
+      return alpha1;
+    }
+  } else if (line_g.size() == 2) {
+    // replace the bracket end whose slope has the sign of the new one
+    if (sign(g * line_g.front()) < 0) { line_g.back() = g; line_alpha.back() = alpha1; }
+    else { line_g.front() = g; line_alpha.front() = alpha1; }
+    if (std::abs(line_g.front()) < std::abs(line_g.back())) {
+      std::swap(line_g.front(), line_g.back());
+      std::swap(line_alpha.front(), line_alpha.back());
+    }
+  } else {
+    PPH_ERROR("Something went wrong");
+  }
+  if (line_g.size() > 2 || line_alpha.size() > 2) PPH_ERROR("Incorrect BFGS");
+
+  // ---- next trial: inverse quadratic interpolation through three slopes, else secant; bisection as the safeguard
+  const REAL a0 = line_alpha.front(), a1 = line_alpha.back(), g0 = line_g.front(), g1 = line_g.back();
+  REAL trial;
+  if (brent_g_c != g0 && brent_g_c != g1) {
+    trial = a0 * g1 * brent_g_c / ((g0 - g1) * (g0 - brent_g_c))
+          + a1 * g0 * brent_g_c / ((g1 - g0) * (g1 - brent_g_c))
+          + brent_c * g0 * g1 / ((brent_g_c - g0) * (brent_g_c - g1));
+  } else {
+    trial = (a0 * g1 - a1 * g0) / (g1 - g0);
+  }
+  const REAL da = std::abs(trial - a1), db = std::abs(a1 - brent_c), dc = std::abs(brent_c - brent_d);
+  const bool outside = (4 * trial > (3 * a0 + a1) && trial > a1) || (4 * trial < (3 * a0 + a1) && trial < a1);
+  if (outside || (brent_flag && 2 * da >= db) || (!brent_flag && 2 * da >= dc) ||
+      (brent_flag && db < convergence) || (!brent_flag && dc < convergence)) {
+    trial = 0.5 * (a0 + a1);
+    brent_flag = true;
+  } else {
+    brent_flag = false;
+  }
+  brent_d = brent_c;
+  brent_c = a1;
+  brent_g_c = g1;
+  alpha1 = trial;
+  return trial;
+}
 
 void Optimizer::update_network(REAL Error, const std::vector<REAL>& grad)
 {

@@ -452,9 +452,39 @@ std::vector<REAL> Potential::evaluate()
   return all;
 }
 
+// Analysis::KS (Analysis.cpp:149-202): both samples are binned into N = |data1| equal bins over their common range
+// (bin width (max-min)/(N-1e-6), Analysis.cpp:108-131), D is the largest gap between the two cumulative
+// histograms, and p the alternating Kolmogorov series (501 terms) -- which the reference only evaluates for N > 30.
+REAL approximate_KS(const std::vector<REAL>& data1, const std::vector<REAL>& data2, REAL* p_out)
+{
+  const int N = (int)data1.size();
+  *p_out = 0.0;
+  if (N == 0 || data2.empty()) return 0.0;
+  REAL lo = data1[0], hi = data1[0];
+  for (REAL v : data1) { if (v < lo) lo = v; if (v > hi) hi = v; }
+  for (REAL v : data2) { if (v < lo) lo = v; if (v > hi) hi = v; }
+  const REAL width = (hi - lo) / (N - 1e-6);
+  std::vector<int> H1(N, 0), H2(N, 0);
+  for (REAL v : data1) H1.at(width > 0 ? (int)((v - lo) / width) : 0)++;
+  for (REAL v : data2) H2.at(width > 0 ? (int)((v - lo) / width) : 0)++;
+  REAL D = 0, c1 = 0.0, c2 = 0.0;
+  for (int i = 0; i < N; i++) {
+    c1 += (REAL)H1[i] / data1.size();
+    c2 += (REAL)H2[i] / data2.size();
+    if (std::fabs(c1 - c2) > D) D = std::fabs(c1 - c2);
+  }
+  if (D == 0) { *p_out = 1.0; return 0.0; }
+  if (N > 30) {
+    REAL p = 0.0;
+    for (int i = 1; i <= 501; i++) p += std::pow(-1, i - 1) * std::exp(-i * i * (REAL)N * D * D);
+    *p_out = 2 * p;
+  }
+  return D;
+}
+
 void Potential::validate()
 {
-  // Potential.cpp:971-1122 without the Kolmogorov-Smirnov appendix (Analysis is outside this path)
+  // Potential.cpp:971-1122, with the approximate Kolmogorov-Smirnov appendix (Analysis.cpp:78-202)
   if (params.input_file.empty()) PPH_ERROR("Cannot do validation without checkpoint file (checkpoint_in flag)");
   std::vector<REAL> E(Nlocal, 0.0);
   for (size_t e = 0; e < atom_types.size(); e++) {
@@ -491,6 +521,15 @@ void Potential::validate()
   std::cout << "Minimum Error =  " << min_E << std::endl;
   std::cout << "Maximum Error =  " << max_E << std::endl;
   std::cout << "RMS Error =  " << std::sqrt(SSE / (double)Nsystems) << std::endl;
+  // the reference compares the raw network sums (before output_mean is added back) with the targets
+  std::vector<REAL> raw(out);
+  for (int i = 0; i < Nsystems; i++) raw[i] -= output_mean;
+  REAL p = 0.0;
+  REAL D = approximate_KS(raw, tg, &p);
+  std::cout << std::endl << std::endl;
+  std::cout << "-- Approximate Kolmogorov-Smirnov test --" << std::endl;
+  std::cout << "  D       =  " << D << std::endl;
+  std::cout << "  p value = " << p << std::endl << std::endl;
 }
 
 }  // namespace pph

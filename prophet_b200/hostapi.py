@@ -23,6 +23,9 @@ def lib():
         L = ctypes.CDLL(LIB_PATH)
         L.pph_optimizer_create.restype = ctypes.c_void_p
         L.pph_optimizer_create.argtypes = [ctypes.c_int, _d, ctypes.c_char_p, ctypes.c_int]
+        L.pph_optimizer_create2.restype = ctypes.c_void_p
+        L.pph_optimizer_create2.argtypes = [ctypes.c_int, _d, ctypes.c_char_p, ctypes.c_int, ctypes.c_double,
+                                            ctypes.c_double, ctypes.c_double]
         L.pph_optimizer_step.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, _d, _d]
         L.pph_optimizer_step_ptr.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
         L.pph_optimizer_destroy.argtypes = [ctypes.c_void_p]
@@ -33,10 +36,15 @@ def lib():
 class Optimizer:
     """pph::Optimizer (Optimizer::update_network + rprop / steepest descent) driven with caller-supplied gradients."""
 
-    def __init__(self, x0, algorithm="rprop", nsystems=1):
+    def __init__(self, x0, algorithm="rprop", nsystems=1, line_min_epsilon=None, debug=None, sd_momentum=None):
         x0 = np.ascontiguousarray(x0, dtype=np.float64)
         self.P = len(x0)
-        self._h = lib().pph_optimizer_create(self.P, x0.ctypes.data_as(_d), algorithm.encode(), nsystems)
+        if line_min_epsilon is None and debug is None and sd_momentum is None:
+            self._h = lib().pph_optimizer_create(self.P, x0.ctypes.data_as(_d), algorithm.encode(), nsystems)
+        else:     # Functional_params.cpp:56-103 defaults for what is not given
+            self._h = lib().pph_optimizer_create2(self.P, x0.ctypes.data_as(_d), algorithm.encode(), nsystems,
+                                                  line_min_epsilon or 0.0, debug or 0.0,
+                                                  sd_momentum or 0.0)
 
     def step(self, sse, grad):
         grad = np.ascontiguousarray(grad, dtype=np.float64)
@@ -58,6 +66,18 @@ class Rprop(Optimizer):
     def __init__(self, P_or_x0):
         x0 = np.zeros(P_or_x0) if np.isscalar(P_or_x0) else P_or_x0
         super().__init__(x0, "rprop", 1)
+
+
+def ks(a, b):
+    """approximate Kolmogorov-Smirnov statistic of Potential::validate -> (D, p)."""
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    p = ctypes.c_double(0.0)
+    L = lib()
+    L.pph_ks.restype = ctypes.c_double
+    L.pph_ks.argtypes = [_d, ctypes.c_int, _d, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
+    D = L.pph_ks(a.ctypes.data_as(_d), len(a), b.ctypes.data_as(_d), len(b), ctypes.byref(p))
+    return D, p.value
 
 
 def checkpoint_roundtrip(in_path, out_path):

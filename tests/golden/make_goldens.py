@@ -54,7 +54,7 @@ def write_checkpoints(cwd, cfg, base, seed, node_transfer=None, means=None, scal
 
 
 def train_case(name, cfg, structures, n_iter, seed, *, precondition_from_checkpoint=False, extra=(), node_transfer=None,
-               with_checkpoint=True):
+               with_checkpoint=True, keep=None):
     """PROPhet.xml + input_file (+ checkpoints) -> ref_driver train -> npz."""
     cwd = tempfile.mkdtemp(prefix="golden_" + name + "_")
     try:
@@ -84,6 +84,8 @@ def train_case(name, cfg, structures, n_iter, seed, *, precondition_from_checkpo
         run_driver(["train", "input_file", "out.bin", str(n_iter)], cwd)
         d = refdump.load(os.path.join(cwd, "out.bin"))
         arrays.update(d)
+        if keep is not None:      # optimizer-only fixtures: drop the per-structure dumps
+            arrays = {k: v for k, v in arrays.items() if k.split(".")[0] in keep}
         arrays["hidden"] = np.array(cfg.hidden, dtype=np.int32)
         arrays["transfer"] = np.array(cfg.transfer)
         if node_transfer is not None:
@@ -209,6 +211,36 @@ def case_variants_train():
     train_case("variants_train", cfg, st, 2, seed=51, node_transfer=nt)
 
 
+OPT_KEEP = ("x_before", "x_after", "SSE", "vSSE", "nval", "gradient", "Ntrain")
+
+
+def _opt_case(name, algorithm_lines, n_calls, seed, tiny=False):
+    """Optimizer-only fixture: every Optimizer::update_network call of a short reference training run (its inputs
+    SSE/gradient and the parameter vector it hands back), for the line-search algorithms."""
+    cfg = synth.config_c2(4)
+    cfg.hidden = [2] if tiny else [5, 4]
+    cfg.G2 = cfg.G2[:2] if tiny else cfg.G2[:6]
+    cfg.G4 = [] if tiny else cfg.G4[:6]
+    st = retag([synth.make_structure(cfg, 70 + s) for s in range(4)], [0, 0, 0, 0 if tiny else 1])
+    train_case(name, cfg, st, n_calls, seed=seed, precondition_from_checkpoint=True, extra=algorithm_lines, keep=OPT_KEEP)
+
+
+def case_opt_bfgs():
+    _opt_case("opt_bfgs", ("algorithm = bfgs", "line_min_epsilon = 1e-3"), 60, seed=61)
+
+
+def case_opt_sd_line():
+    _opt_case("opt_sd_line", ("algorithm = steepest_descent_with_line_opt", "line_min_epsilon = 1e-3"), 40, seed=62)
+
+
+def case_opt_default_switch():
+    # a 9-parameter net: the "default" schedule leaves Rprop for steepest descent at iteration 134 (2 x 67) and
+    # steepest descent for L-BFGS at iteration 150; the reference's L-BFGS then stalls on the flat bottom and
+    # turns to NaN at call 211 (y.s = 0 -> rho = inf) -- kept in the fixture on purpose.
+    _opt_case("opt_default_switch", ("algorithm = default", "debug = 0.5", "line_min_epsilon = 1e-3"), 215, seed=63,
+              tiny=True)
+
+
 def case_variants_md():
     # orthorhombic version of the variants rows (ghost expansion helper wants a rectangular box); no G3 quirk-free
     # shortcut: G3 rows are present, so the "Rjk > Rcut skips G4" branch (Structure.cpp:1129-1132) is exercised.
@@ -318,6 +350,33 @@ def case_checkpoint_files():
 
 
 CASES["checkpoint_files"] = case_checkpoint_files
+
+
+def case_ks():
+    """Analysis::KS on a few seeded sample pairs (N = 8 -> p not evaluated, N = 64 and 200 -> series evaluated,
+    identical samples -> D = 0, p = 1)."""
+    arrays = {}
+    cwd = tempfile.mkdtemp(prefix="golden_ks_")
+    try:
+        for k, (n, shift, scale) in enumerate([(8, 0.3, 1.0), (64, 0.05, 1.1), (200, 0.4, 0.7), (40, 0.0, 1.0)]):
+            a = synth.normal(900 + k, n, 1)
+            b = a.copy() if (shift == 0.0 and scale == 1.0) else shift + scale * synth.normal(900 + k, n, 2)
+            with open(os.path.join(cwd, "s.txt"), "w") as f:
+                f.write("%d\n%s\n%d\n%s\n" % (n, " ".join(repr(float(v)) for v in a), n, " ".join(repr(float(v)) for v in b)))
+            run_driver(["ks", "s.txt", "ks.bin"], cwd)
+            d = refdump.load(os.path.join(cwd, "ks.bin"))
+            arrays["a.%d" % k], arrays["b.%d" % k] = a, b
+            arrays["D.%d" % k], arrays["p.%d" % k] = d["D"], d["p"]
+        np.savez_compressed(os.path.join(OUT, "ks.npz"), **arrays)
+        print("wrote ks.npz", [(float(arrays["D.%d" % k][0]), float(arrays["p.%d" % k][0])) for k in range(4)])
+    finally:
+        shutil.rmtree(cwd, ignore_errors=True)
+
+
+CASES["ks"] = case_ks
+CASES["opt_bfgs"] = case_opt_bfgs
+CASES["opt_sd_line"] = case_opt_sd_line
+CASES["opt_default_switch"] = case_opt_default_switch
 
 if __name__ == "__main__":
     if not os.path.exists(DRIVER):

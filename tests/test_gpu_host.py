@@ -92,6 +92,34 @@ def test_cli_train_matches_reference_cli(cfg_name, hidden, tmp_path):
         assert abs(a[1] - b[1]) <= 1e-8 * abs(b[1]) and a[2] == b[2]
     rms = lambda txt: float(re.search(r"RMS Error =\s+([-+0-9.eE]+)", txt).group(1))
     assert abs(rms(v_ours) - rms(v_ref)) <= 1e-5 * abs(rms(v_ref))
+    # the approximate Kolmogorov-Smirnov appendix (Potential.cpp:1107-1117)
+    ks = lambda txt: (float(re.search(r"D       =\s+([-+0-9.eEnaif]+)", txt).group(1)),
+                      float(re.search(r"p value =\s+([-+0-9.eEnaif]+)", txt).group(1)))
+    assert "-- Approximate Kolmogorov-Smirnov test --" in v_ours
+    assert ks(v_ours) == ks(v_ref)
+
+
+@pytest.mark.skipif(not os.path.exists(REF_CLI), reason="oracle/_ref/PROPhet not built")
+@pytest.mark.parametrize("algorithm", ["bfgs", "steepest_descent_with_line_opt"])
+def test_cli_line_search_training_matches_reference_cli(algorithm, tmp_path):
+    """`algorithm = bfgs` / `steepest_descent_with_line_opt` (Optimizer.cpp:457-507, 607-869): gradients from the GPU,
+    line search and L-BFGS recursion on the host; the printed table (one line per finished line search) and the saved
+    potential must follow the reference's."""
+    assert os.path.exists(hostapi.CLI_PATH), "PROPhet_b200 not built"
+    cfg = synth.CONFIGS["C2"](6)
+    ours = tmp_path / "ours"; ref = tmp_path / "ref"
+    for d in (ours, ref):
+        d.mkdir()
+        _write_case(str(d), cfg, 6, [0, 0, 0, 0, 0, 0], [6, 5], seed=12, niter=8,
+                    extra=("algorithm = " + algorithm, "line_min_epsilon = 1e-3"))
+    out_ref = _run(REF_CLI, ["-in", "input_file", "-train"], str(ref))
+    out_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-train"], str(ours))
+    t_ref, t_ours = _iteration_table(out_ref), _iteration_table(out_ours)
+    assert len(t_ref) == 8 and len(t_ours) == 8, (out_ref[-1500:], out_ours[-1500:])
+    assert np.allclose(np.array(t_ours), np.array(t_ref), rtol=5e-6, atol=0), (t_ours, t_ref)
+    a = ckpt.read_checkpoint(str(ours / "trained_Si"))
+    b = ckpt.read_checkpoint(str(ref / "trained_Si"))
+    assert rel_err(a["params"], b["params"]) < 1e-7
 
 
 @pytest.mark.parametrize("name", ["si_md", "tio2_md"])

@@ -27,6 +27,41 @@ def test_rprop_reproduces_reference_steps_exactly(name):
         assert np.array_equal(x1, c.d["x_after.%d" % it]), (name, it)
 
 
+@pytest.mark.parametrize("name,algorithm,kw", [
+    ("opt_bfgs", "bfgs", dict(line_min_epsilon=1e-3)),
+    ("opt_sd_line", "steepest_descent_with_line_opt", dict(line_min_epsilon=1e-3)),
+    ("opt_default_switch", "default", dict(line_min_epsilon=1e-3, debug=0.5)),
+])
+def test_line_search_algorithms_reproduce_reference_calls_exactly(name, algorithm, kw):
+    """L-BFGS + Brent line minimisation (Optimizer.cpp:607-869), steepest descent with line optimisation (:457-507)
+    and the "default" schedule Rprop -> steepest descent -> L-BFGS (:305-322, :436-447): fed the SSE and gradient of
+    every Optimizer::update_network call of a reference run, the parameter vector handed back must be the
+    reference's bit for bit -- including the calls inside a line search, which do not advance the iteration
+    counter, and (default schedule) the reference's own collapse to NaN once y.s = 0."""
+    _ensure_built()
+    d = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    n = sum(1 for k in d.files if k.startswith("gradient."))
+    opt = hostapi.Optimizer(d["x_before.0"], algorithm, int(d["Ntrain"][0]), **kw)
+    for it in range(n):
+        x1 = opt.step(d["SSE.%d" % it][0], d["gradient.%d" % it])
+        assert np.array_equal(x1, d["x_after.%d" % it], equal_nan=True), (name, it)
+    if name == "opt_default_switch":
+        # the schedule really left Rprop: plain Rprop on the same inputs departs from the reference at call 133
+        rp = hostapi.Optimizer(d["x_before.0"], "rprop", int(d["Ntrain"][0]))
+        same = [np.array_equal(rp.step(d["SSE.%d" % it][0], d["gradient.%d" % it]), d["x_after.%d" % it]) for it in range(140)]
+        assert all(same[:133]) and not same[133]
+
+
+def test_approximate_ks_statistic_matches_reference():
+    """The appendix of `-validate` (Potential.cpp:1107-1117 -> Analysis::KS, Analysis.cpp:149-202)."""
+    _ensure_built()
+    d = np.load(os.path.join(GOLDEN_DIR, "ks.npz"))
+    for k in range(4):
+        D, p = hostapi.ks(d["a.%d" % k], d["b.%d" % k])
+        assert D == d["D.%d" % k][0] and p == d["p.%d" % k][0], (k, D, p)
+    assert hostapi.ks(d["a.3"], d["a.3"]) == (0.0, 1.0)
+
+
 def test_default_algorithm_starts_as_rprop():
     _ensure_built()
     c = TrainCase("si_train")
