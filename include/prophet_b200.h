@@ -79,6 +79,9 @@ int pp_cart_to_frac(const double* cell, const double* cart, int n, double* frac_
 int pp_add_structures(pp_context* ctx, int n_struct, const int* natoms, const double* cells, const double* frac,
                       const int* elem, const double* targets, const int* tags);
 int pp_clear_structures(pp_context* ctx);
+/* Structure::init_G run again on every resident structure after pp_set_descriptors changed the row PARAMETERS
+ * (same counts, same Rcut): the per-step descriptor refresh of Potential::optimize_Gs (Potential.cpp:806-808). */
+int pp_recompute_descriptors(pp_context* ctx);
 int pp_num_structures(pp_context* ctx);
 long long pp_num_atoms(pp_context* ctx);
 /* parity hooks.  G_out[NG][natoms(s)] in the reference's Structure::G layout. */

@@ -28,7 +28,8 @@ _vp = ctypes.c_void_p
 SYMBOLS = [
     "pp_last_error", "pp_version", "pp_create", "pp_destroy", "pp_set_descriptors", "pp_num_descriptors",
     "pp_set_network", "pp_set_output_scaling", "pp_num_parameters", "pp_set_parameters", "pp_get_parameters",
-    "pp_set_input_scaling", "pp_cart_to_frac", "pp_add_structures", "pp_clear_structures", "pp_num_structures",
+    "pp_set_input_scaling", "pp_cart_to_frac", "pp_add_structures", "pp_clear_structures", "pp_recompute_descriptors",
+    "pp_num_structures",
     "pp_num_atoms", "pp_get_descriptors", "pp_get_neighbors", "pp_precondition", "pp_get_input_scaling", "pp_epoch",
     "pp_epoch_device", "pp_epoch_result_dev", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
     "pp_md_compute", "pp_md_build_neighbors", "pp_md_get_neighbors", "pp_md_step", "pp_md_step_device",
@@ -164,6 +165,10 @@ class Context:
     def clear_structures(self):
         _check(lib().pp_clear_structures(self._h))
         self._natoms = np.zeros(0, dtype=np.int32)
+
+    def recompute_descriptors(self):
+        """init_G again after set_descriptors changed row parameters in place (Potential.cpp:806-808)."""
+        _check(lib().pp_recompute_descriptors(self._h))
 
     @property
     def n_structures(self):

@@ -23,7 +23,7 @@ def write_checkpoint(path: str, symbol: str, all_symbols: Sequence[str], rows: D
                      means: np.ndarray, scales: np.ndarray, out_mean: float, out_scale: float,
                      sizes: Sequence[int], params: np.ndarray, transfer: str = "tanh",
                      node_transfer: Sequence[str] | None = None, header_precision: int = 12,
-                     weight_precision: int = 18) -> None:
+                     weight_precision: int = 18, free_energy: float | None = None) -> None:
     """sizes = [NG, hidden..., 1]; params layer-major, node-major, [w_0..w_{n-1}, b] per node."""
     sizes = [int(x) for x in sizes]
     hidden = sizes[1:-1]
@@ -31,6 +31,8 @@ def write_checkpoint(path: str, symbol: str, all_symbols: Sequence[str], rows: D
     out.append("nn")
     out.append("structure  ")
     out.append("%s:  %s " % (symbol, " ".join(all_symbols)))
+    if free_energy is not None:      # Functional_params.cpp:148-152
+        out.append("FE:  " + _g(free_energy, 9))
     n_rows = sum(len(rows.get(k, [])) for k in ("G1", "G2", "G3", "G4"))
     out.append(str(n_rows))
     for kind in ("G1", "G2", "G3", "G4"):

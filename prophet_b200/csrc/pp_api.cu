@@ -197,7 +197,13 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
   PP_REQUIRE(nG4 <= PP_MAX_G4_ROWS, "pp_set_descriptors: %d G4 rows (max %d)", nG4, PP_MAX_G4_ROWS);
   PP_REQUIRE(nG3 <= PP_MAX_G3_ROWS, "pp_set_descriptors: %d G3 rows (max %d)", nG3, PP_MAX_G3_ROWS);
   PP_REQUIRE(Rcut > 0, "pp_set_descriptors: Rcut must be positive");
-  PP_REQUIRE(c->n_struct == 0, "pp_set_descriptors: structures already added; call pp_clear_structures first");
+  // with structures resident only the row PARAMETERS may change (the -optimize search, Potential.cpp:709-877):
+  // same element count, row counts and Rcut, so every buffer keeps its shape; pp_recompute_descriptors then refreshes
+  if (c->n_struct > 0)
+    PP_REQUIRE(c->spec_set && c->spec.n_elem == n_elem && c->spec.nG1 == nG1 && c->spec.nG2 == nG2 && c->spec.nG3 == nG3 &&
+                   c->spec.nG4 == nG4 && c->spec.Rcut == Rcut,
+               "pp_set_descriptors: structures already added; only row parameters may change (same counts and Rcut), "
+               "otherwise call pp_clear_structures first");
   DescSpec& S = c->spec;
   memset(&S, 0, sizeof(S));
   S.n_elem = n_elem; S.nG1 = nG1; S.nG2 = nG2; S.nG3 = nG3; S.nG4 = nG4;
@@ -580,6 +586,23 @@ extern "C" int pp_add_structures(pp_context* c, int n_struct, const int* natoms,
   if (ppk_desc_periodic(S, a, &c->desc_cap, st, &c->launches)) return 1;
   if (tick(c, 1)) return 1;
   PP_CUDA(cudaStreamSynchronize(st));
+  return tock(c, 0, 1, 0);
+}
+
+// Structure::init_G called again on every system after the rows changed (Potential.cpp:806-808): the positions,
+// cells and element lists are still resident, so this is one descriptor launch over all atoms.
+extern "C" int pp_recompute_descriptors(pp_context* c)
+{
+  PP_REQUIRE(c && c->spec_set, "pp_recompute_descriptors: call pp_set_descriptors first");
+  if (c->n_atoms == 0) return 0;
+  PP_CUDA(cudaSetDevice(c->device));
+  PeriodicArgs a = periodic_args(c);
+  a.n_atoms = c->n_atoms;
+  a.atom_begin = 0;
+  if (tick(c, 0)) return 1;
+  if (ppk_desc_periodic(c->spec, a, &c->desc_cap, c->stream, &c->launches)) return 1;
+  if (tick(c, 1)) return 1;
+  PP_CUDA(cudaStreamSynchronize(c->stream));
   return tock(c, 0, 1, 0);
 }
 

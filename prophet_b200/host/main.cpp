@@ -1,5 +1,5 @@
 // PROPhet_b200: the reference's command line (main.cpp:20-98) on the B200 device path.
-//   PROPhet_b200 [-in input_file] [-train | -run | -validate]
+//   PROPhet_b200 [-in input_file] [-train | -run | -validate | -optimize]
 // Multi-GPU: start one process per GPU with RANK / WORLD_SIZE / LOCAL_RANK set (torchrun's variables) or
 // PP_RANK / PP_WORLD_SIZE / PP_LOCAL_RANK; structures are sharded round robin as Setup.cpp:582 does over MPI ranks.
 #include <cstring>
@@ -16,7 +16,8 @@ int main(int argc, char* argv[])
     } else if (!strcmp(argv[i], "-run")) run_type = "run";
     else if (!strcmp(argv[i], "-train")) run_type = "train";
     else if (!strcmp(argv[i], "-validate")) run_type = "validate";
-    else if (!strcmp(argv[i], "-optimize") || !strcmp(argv[i], "-init") || !strcmp(argv[i], "-forces"))
+    else if (!strcmp(argv[i], "-optimize")) run_type = "optimize";
+    else if (!strcmp(argv[i], "-init") || !strcmp(argv[i], "-forces"))
       PPH_ERROR(std::string("Command line argument \"") + argv[i] + "\" belongs to a workflow outside this build");
     else PPH_ERROR(std::string("Command line argument \"") + argv[i] + "\" not recognized");
   }
@@ -26,5 +27,6 @@ int main(int argc, char* argv[])
   if (run_type == "train") pot.train();
   else if (run_type == "run") pot.evaluate();
   else if (run_type == "validate") pot.validate();
+  else if (run_type == "optimize") pot.optimize_Gs();
   return 0;
 }

@@ -7,7 +7,7 @@
 
 using namespace LAMMPS_NS;
 
-PairNN::PairNN(LAMMPS* lmp) : Pair(lmp), Rcut(0.0), out_mean(0.0), ctx(NULL), ready(false) {}
+PairNN::PairNN(LAMMPS* lmp) : Pair(lmp), Rcut(0.0), out_mean(0.0), ctx(NULL), ready(false), has_free_energy(false) {}
 
 PairNN::~PairNN()
 {
@@ -81,6 +81,20 @@ void PairNN::finish_setup()
   }
   if (pp_set_output_scaling(ctx, coeff_nets[0].params.output_mean, coeff_nets[0].params.output_variance)) error->all(FLERR, pp_last_error());
   if (pp_md_set_types(ctx, max_type, type_to_elem.data())) error->all(FLERR, pp_last_error());
+  // free energies: each pair_coeff file contributes its own element's "FE:" entry (Functional_params.cpp:257-264);
+  // lammps type -> element symbol as pair_nn.cpp:246 records it
+  has_free_energy = false;
+  type_free_energy.assign(max_type + 1, 0.0);
+  type_has_free_energy.assign(max_type + 1, 0);
+  for (size_t i = 0; i < coeff_nets.size(); i++) {
+    const pph::FunctionalParams& fp = coeff_nets[i].params;
+    std::map<std::string, pph::REAL>::const_iterator it = fp.FE.find(fp.current_atom_type);
+    if (it != fp.FE.end()) {
+      has_free_energy = true;
+      type_free_energy[coeff_types[i]] = it->second;
+      type_has_free_energy[coeff_types[i]] = 1;
+    }
+  }
   ready = true;
 }
 
@@ -99,6 +113,31 @@ void PairNN::compute(int eflag, int vflag)
   for (int ii = 0; ii < list->inum; ii++)
     memcpy(flat.data() + offsets[ii], list->firstneigh[ii], sizeof(int) * (size_t)list->numneigh[ii]);
   double etotal = 0.0;
+  if (has_free_energy) {
+    // Checkpoints with "FE:" lines (Potential::evaluate_MD, Potential.cpp:1159-1162 -> Structure::unravel_Energy,
+    // Structure.cpp:152-199): every atom's energy becomes (E_i + S) / N, with S the free energies summed over ALL
+    // atoms this rank sees (locals and ghosts) and N their number.  Odd, but it is what the reference returns.
+    const int ntotal = nlocal + atom->nghost;
+    double S = 0.0;
+    for (int k = 0; k < ntotal; k++) {
+      const int t = atom->type[k];
+      if (t < 0 || t >= (int)type_free_energy.size() || !type_has_free_energy[t])
+        error->all(FLERR, "No Free Energy supplied for an atom type present in the system");
+      S += type_free_energy[t];
+    }
+    eatom_tmp.assign(nlocal, 0.0);
+    if (pp_md_compute(ctx, atom->x[0], atom->type, nlocal, atom->nghost, offsets.data(), flat.data(), atom->f[0],
+                      eatom_tmp.data(), &etotal, NULL, NULL))
+      error->all(FLERR, pp_last_error());
+    for (int ii = 0; ii < nlocal; ii++) {
+      const double Ei = (eatom_tmp[ii] + S) / ntotal;
+      if (eflag_global) eng_vdwl += Ei;
+      if (eflag_atom) eatom[ii] += Ei;
+    }
+    if (eflag_global && comm->me == 0) eng_vdwl += out_mean;
+    if (vflag_fdotr) virial_fdotr_compute();
+    return;
+  }
   if (pp_md_compute(ctx, atom->x[0], atom->type, nlocal, atom->nghost, offsets.data(), flat.data(), atom->f[0],
                     eflag_atom ? eatom : NULL, &etotal, NULL, NULL))
     error->all(FLERR, pp_last_error());

@@ -38,6 +38,9 @@ class PairNN : public Pair {
   double Rcut, out_mean;
   pp_context* ctx;
   bool ready;
+  bool has_free_energy;                       // some pair_coeff file carries an "FE:" line
+  std::vector<double> type_free_energy, eatom_tmp;
+  std::vector<char> type_has_free_energy;
   std::vector<int> coeff_types;
   std::vector<pph::HostNet> coeff_nets;
   std::vector<long long> offsets;

@@ -43,6 +43,8 @@ struct FunctionalParams {
   int Niterations, Ncheckpoint, Nprint, Ncycles, Nradial, Nangular, Nbackup;
   bool Tbackup, SGD, output_precondition, input_precondition, print_gvectors, is_MD;
   REAL Rcut, threshold, regularization, sd_momentum, line_min_epsilon, lambda_max, debug, dropout;
+  REAL T0, Tf, dT, step_size;                // -optimize: annealing schedule and Gaussian step (Functional_params.cpp:78-82)
+  int Nsteps_per_T;
   std::vector<std::vector<REAL> > G1, G2, G3, G4;
   std::map<std::string, REAL> FE;
   // per-element state carried by a checkpoint
@@ -92,6 +94,8 @@ class Setup {
   bool my_is_potential;
 };
 
+// sum of the `free_energy` entries over a structure's atoms (Structure::train_Local / unravel_Energy, Structure.cpp:110-199)
+REAL free_energy_sum(const std::map<std::string, REAL>& FE, const std::vector<int>& Z);
 StructureData read_prophet_xml(int index);                    // CUSTOM.cpp:81-160 ("PROPhet.xml" in the CWD)
 StructureData read_vasprun(const std::string& dir);           // VASP.cpp:78-176
 
@@ -190,6 +194,7 @@ class Potential {
   REAL train();                       // Potential.cpp:607-693
   std::vector<REAL> evaluate();       // :515-551
   void validate();                    // :971-1122
+  void optimize_Gs();                 // :709-877  Monte-Carlo search over the descriptor row parameters
   void save();                        // :296-317
   void backup(int niter);             // :323-345
   pp_context* context() { return ctx; }
@@ -198,6 +203,7 @@ class Potential {
  private:
   void Precondition();                // :387-502
   void upload_networks();
+  void upload_descriptor_rows();      // pp_set_descriptors from params.G1..G4
   std::vector<REAL> all_parameters() const;
   void set_all_parameters(const std::vector<REAL>& x);
   Parallel* mpi;
@@ -208,6 +214,8 @@ class Potential {
   std::vector<REAL> targets;                   // local systems
   std::vector<std::string> tags;
   std::vector<int> natoms;
+  std::vector<std::vector<unsigned char> > atom_Z;   // per local system, per atom: atomic number (for the free-energy sums)
+  bool targets_shifted;                        // `free_energy` was in the input_file: targets had the sums taken off at load
   int Nsystems, Nlocal, Ntrain, Nval, Nother;
   bool early_stop;
   REAL output_mean, output_variance;

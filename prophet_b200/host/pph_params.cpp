@@ -77,6 +77,7 @@ FunctionalParams::FunctionalParams()
   Nbackup = 0;
   Tbackup = false;
   dropout = 1.0;
+  T0 = 1; Tf = 0.1; dT = 0.98; Nsteps_per_T = 50; step_size = 0.2;
   print_gvectors = false;
   threshold = 0.0;
   debug = 0.0;
@@ -485,6 +486,15 @@ Setup::Setup(const std::string& input_file, Parallel* mpi_in, bool quiet) : mpi(
   if (mpi->io_node() && !quiet) {
     // Setup::print_details (Setup.cpp:614-676)
     std::cout << std::endl << "Found " << Ntotal_systems << (Nsystems() == 1 ? " system" : " systems") << std::endl << std::endl;
+    if (!F.FE.empty()) {                                                         // Setup.cpp:625-635
+      std::cout << "############" << std::endl << "TRAINING TO FORMATION ENERGIES" << std::endl;
+      std::cout << "Species Energies: " << std::endl;
+      std::cout.precision(9);
+      for (std::map<std::string, REAL>::const_iterator it = F.FE.begin(); it != F.FE.end(); ++it)
+        std::cout << it->first << " : " << it->second << std::endl;
+      std::cout.precision(6);
+      std::cout << "############" << std::endl << std::endl;
+    }
     std::cout << "Functional parameters" << std::endl;
     std::cout << F.inputs.size() << (F.inputs.size() == 1 ? " input" : " inputs") << " :  ";
     for (size_t i = 0; i < F.inputs.size(); i++) std::cout << F.inputs[i] << "   ";
@@ -594,6 +604,11 @@ void Setup::read_input(const std::string& filename_in)
     else if (key == "regularization") { Line >> rv; F.regularization = rv; }
     else if (key == "line_min_epsilon") { Line >> rv; F.line_min_epsilon = rv; }
     else if (key == "dropout") { Line >> rv; F.dropout = rv; }
+    else if (key == "t0") { Line >> rv; F.T0 = rv; }                          // Setup.cpp:479-503
+    else if (key == "tf") { Line >> rv; F.Tf = rv; }
+    else if (key == "nsteps_per_t") { Line >> iv; F.Nsteps_per_T = iv; }
+    else if (key == "step_size") { Line >> rv; F.step_size = rv; }
+    else if (key == "dt") { Line >> rv; F.dT = rv; }
     else if (key == "seed") { Line >> iv; srand(iv); }
     else if (key == "free_energy") { while (Line >> KEY >> rv) F.FE[KEY] = rv; }
     else if (key == "g1" || key == "g2" || key == "g3" || key == "g4") {
@@ -657,6 +672,18 @@ void Setup::split_systems()
   systems.swap(mine);
 }
 
+REAL free_energy_sum(const std::map<std::string, REAL>& FE, const std::vector<int>& Z)
+{
+  REAL sum = 0.0;
+  for (size_t a = 0; a < Z.size(); a++) {
+    std::string sym = atomic_symbol(Z[a]);
+    std::map<std::string, REAL>::const_iterator it = FE.find(sym);
+    if (it == FE.end()) PPH_ERROR("No Free Energy supplied for " + sym);
+    sum += it->second;
+  }
+  return sum;
+}
+
 StructureData Setup::load(int i) const
 {
   // System::System (System.cpp:51-150)
@@ -677,6 +704,9 @@ StructureData Setup::load(int i) const
   std::string train = tr == sp.files.end() ? "" : tr->second;
   if (!sd.train.empty()) train = sd.train;      // System.cpp:116-119
   sd.train = train;
+  // `free_energy` given: train on the total energy minus the per-atom reference energies (System.cpp:142-147 ->
+  // Structure::train_Local, Structure.cpp:110-149)
+  if (F.output == "energy" && !F.FE.empty()) sd.target -= free_energy_sum(F.FE, sd.Z);
   return sd;
 }
 

@@ -169,6 +169,7 @@ static int tag_id(const std::string& t) { return t == "train" ? PP_TAG_TRAIN : (
 
 Potential::Potential(const Setup& setup, Parallel* mpi_in) : mpi(mpi_in), params(setup.F), ctx(NULL)
 {
+  targets_shifted = (setup.F.output == "energy" && !setup.F.FE.empty());
   // Potential::Potential(systems, F) (Potential.cpp:60-205)
   Nlocal = setup.Nsystems();
   PPH_CALL(pp_create(mpi->local_rank(), 64, &ctx));
@@ -212,7 +213,13 @@ Potential::Potential(const Setup& setup, Parallel* mpi_in) : mpi(mpi_in), params
       if (mpi->io_node()) {
         std::cout << "Hidden layers :  ";
         for (size_t l = 0; l < params.hidden.size(); l++) std::cout << params.hidden[l] << "  ";
-        std::cout << std::endl << std::endl;
+        std::cout << std::endl;
+        if (!params.FE.empty()) {                                             // Potential.cpp:103-108
+          std::cout.precision(9);
+          std::cout << params.current_atom_type << " Free Energy : " << params.FE[params.current_atom_type] << std::endl;
+          std::cout.precision(6);
+        }
+        std::cout << std::endl;
       }
       // the reference keeps the union found in the data, not the file's own list
       params.atomic_numbers = atom_types;
@@ -223,13 +230,7 @@ Potential::Potential(const Setup& setup, Parallel* mpi_in) : mpi(mpi_in), params
     if (e == 0) {
       // first element: descriptors of every local system (Potential.cpp:113-150, Structure::init_G)
       params.auto_rows();
-      std::vector<double> g1, g2, g3, g4;
-      for (size_t r = 0; r < params.G1.size(); r++) g1.insert(g1.end(), params.G1[r].begin(), params.G1[r].end());
-      for (size_t r = 0; r < params.G2.size(); r++) g2.insert(g2.end(), params.G2[r].begin(), params.G2[r].end());
-      for (size_t r = 0; r < params.G3.size(); r++) g3.insert(g3.end(), params.G3[r].begin(), params.G3[r].end());
-      for (size_t r = 0; r < params.G4.size(); r++) g4.insert(g4.end(), params.G4[r].begin(), params.G4[r].end());
-      PPH_CALL(pp_set_descriptors(ctx, (int)atom_types.size(), (int)params.G1.size(), g1.data(), (int)params.G2.size(), g2.data(),
-                                  (int)params.G3.size(), g3.data(), (int)params.G4.size(), g4.data(), params.Rcut));
+      upload_descriptor_rows();
       std::map<int, int> zidx;
       for (size_t i = 0; i < atom_types.size(); i++) zidx[atom_types[i]] = (int)i;
       Ntrain = Nval = Nother = 0;
@@ -249,6 +250,7 @@ Potential::Potential(const Setup& setup, Parallel* mpi_in) : mpi(mpi_in), params
           targets.push_back(s.target);
           tags.push_back(s.train);
           natoms.push_back(s.natoms());
+          atom_Z.push_back(std::vector<unsigned char>(s.Z.begin(), s.Z.end()));
           if (s.train == "train") Ntrain++;
           else if (s.train == "val") Nval++;
           else Nother++;
@@ -262,11 +264,13 @@ Potential::Potential(const Setup& setup, Parallel* mpi_in) : mpi(mpi_in), params
     net.sizes.push_back(pp_num_descriptors(ctx));
     for (size_t l = 0; l < params.hidden.size(); l++) net.sizes.push_back(params.hidden[l]);
     net.sizes.push_back(1);
+    // the reference's node constructors draw random weights even when a checkpoint then overwrites them
+    // (NN.cpp:51-80, NN_node.cpp:52-62): drawing here as well keeps the libc rand() stream aligned for what
+    // consumes it later (-optimize, the SGD shuffle)
+    net.init_random();
     if (!params.input_file.empty()) {
       std::ifstream file(filename.c_str());
       net.load(file);
-    } else {
-      net.init_random();
     }
     if ((int)net.params.input_mean.size() != net.sizes[0]) {
       net.params.input_mean.assign(net.sizes[0], 0.0);
@@ -328,6 +332,17 @@ void Potential::set_all_parameters(const std::vector<REAL>& x)
   }
 }
 
+void Potential::upload_descriptor_rows()
+{
+  std::vector<double> g1, g2, g3, g4;
+  for (size_t r = 0; r < params.G1.size(); r++) g1.insert(g1.end(), params.G1[r].begin(), params.G1[r].end());
+  for (size_t r = 0; r < params.G2.size(); r++) g2.insert(g2.end(), params.G2[r].begin(), params.G2[r].end());
+  for (size_t r = 0; r < params.G3.size(); r++) g3.insert(g3.end(), params.G3[r].begin(), params.G3[r].end());
+  for (size_t r = 0; r < params.G4.size(); r++) g4.insert(g4.end(), params.G4[r].begin(), params.G4[r].end());
+  PPH_CALL(pp_set_descriptors(ctx, (int)atom_types.size(), (int)params.G1.size(), g1.data(), (int)params.G2.size(), g2.data(),
+                              (int)params.G3.size(), g3.data(), (int)params.G4.size(), g4.data(), params.Rcut));
+}
+
 void Potential::Precondition()
 {
   // Potential.cpp:387-502
@@ -344,6 +359,7 @@ void Potential::Precondition()
         PPH_CALL(pp_set_input_scaling(ctx, (int)e, n.params.input_mean.data(), n.params.input_variance.data()));
       } else {
         PPH_CALL(pp_get_input_scaling(ctx, (int)e, n.params.input_mean.data(), n.params.input_variance.data()));
+        n.preconditioned = true;      // set_means makes is_preconditioned() true: a later train() keeps these (NN.h:92-103)
       }
     }
   }
@@ -392,6 +408,97 @@ REAL Potential::train()
   }
   save();
   return std::sqrt(opt.get_error());
+}
+
+// Redraw until the value falls in (lo, hi] (open_lo) or [lo, hi]
+static REAL perturbed(REAL centre, REAL sd, REAL lo, bool open_lo, REAL hi)
+{
+  for (;;) {
+    REAL v = rand_normal(0, sd) + centre;
+    if ((open_lo ? v > lo : v >= lo) && v <= hi) return v;
+  }
+}
+
+void Potential::optimize_Gs()
+{
+  // Potential.cpp:709-877 (J. Chem. Phys. 144, 224103): simulated annealing over eta / Rs (G2), eta / xi (G3, G4).
+  // Every step perturbs the LAST ACCEPTED rows, recomputes all descriptors on the GPU (one launch over the resident
+  // structures), retrains from the current weights and accepts with the Metropolis rule on the final RMS error.
+  // Random numbers are drawn on rank 0 only and the rows broadcast, as the reference does.
+  const REAL max_eta = 65;
+  std::vector<std::vector<REAL> > G1 = params.G1, G2 = params.G2, G3 = params.G3, G4 = params.G4;
+  REAL T = params.T0, last_E = 9e9;
+  int Naccepted = 0, counter = 0;
+  std::ofstream log_file;
+  log_file.open("logfile.out");
+  if (mpi->io_node()) {
+    log_file << "  T    accepted    Error" << std::endl;
+    log_file << " -------------------------" << std::endl;
+  }
+  while (T >= params.Tf) {
+    if (mpi->io_node()) {
+      Naccepted = 0;
+      log_file << T << " : ";
+    }
+    for (int Step = 1; Step <= params.Nsteps_per_T; Step++) {
+      if (mpi->io_node()) std::cout << "Step : " << Step << std::endl;
+      if (counter) {
+        if (mpi->io_node()) {
+          for (size_t i = 0; i < params.G2.size(); i++) {
+            params.G2[i][2] = perturbed(G2[i][2], params.step_size, 0, true, max_eta);
+            params.G2[i][3] = perturbed(G2[i][3], params.step_size, 0, false, params.Rcut);
+          }
+          for (size_t i = 0; i < params.G3.size(); i++) {
+            params.G3[i][2] = perturbed(G3[i][2], params.step_size, 0, true, max_eta);
+            params.G3[i][3] = perturbed(G3[i][3], params.step_size, 0, false, params.Rcut);
+          }
+          for (size_t i = 0; i < params.G4.size(); i++) {
+            params.G4[i][2] = perturbed(G4[i][2], params.step_size, 0, true, max_eta);
+            params.G4[i][3] = perturbed(G4[i][3], params.step_size, 0, true, max_eta);
+          }
+        }
+        // Bcast of the rows: zero everywhere but rank 0, then sum
+        std::vector<REAL> flat;
+        for (size_t i = 0; i < params.G2.size(); i++) { flat.push_back(params.G2[i][2]); flat.push_back(params.G2[i][3]); }
+        for (size_t i = 0; i < params.G3.size(); i++) { flat.push_back(params.G3[i][2]); flat.push_back(params.G3[i][3]); }
+        for (size_t i = 0; i < params.G4.size(); i++) { flat.push_back(params.G4[i][2]); flat.push_back(params.G4[i][3]); }
+        if (mpi->Nprocs() > 1) {
+          if (!mpi->io_node()) std::fill(flat.begin(), flat.end(), 0.0);
+          mpi->allreduce(flat);
+        }
+        size_t k = 0;
+        for (size_t i = 0; i < params.G2.size(); i++) { params.G2[i][2] = flat[k++]; params.G2[i][3] = flat[k++]; }
+        for (size_t i = 0; i < params.G3.size(); i++) { params.G3[i][2] = flat[k++]; params.G3[i][3] = flat[k++]; }
+        for (size_t i = 0; i < params.G4.size(); i++) { params.G4[i][2] = flat[k++]; params.G4[i][3] = flat[k++]; }
+        upload_descriptor_rows();
+        PPH_CALL(pp_recompute_descriptors(ctx));
+      }
+      REAL Error = train();
+      if (mpi->io_node()) {
+        std::cout << "Error =  " << Error << std::endl;
+        if (rand_uniform() < std::exp(-(Error - last_E) / T)) {
+          G2 = params.G2;
+          G3 = params.G3;
+          G4 = params.G4;
+          last_E = Error;
+          Naccepted++;
+          std::ofstream pf("G_parameters.out");
+          const std::vector<std::vector<REAL> >* sets[4] = {&G1, &G2, &G3, &G4};
+          const char* names[4] = {"G1  ", "G2  ", "G3  ", "G4  "};
+          for (int g = 0; g < 4; g++)
+            for (size_t i = 0; i < sets[g]->size(); i++) {
+              if (g == 0) pf << std::setprecision(10);      // only a G1 row raises the precision (Potential.cpp:826-827)
+              pf << names[g];
+              for (size_t j = 0; j < (*sets[g])[i].size(); j++) pf << (*sets[g])[i][j] << " ";
+              pf << std::endl;
+            }
+        }
+      }
+      counter++;
+    }
+    if (mpi->io_node()) log_file << (double)Naccepted / (double)params.Nsteps_per_T << "  " << last_E << std::endl;
+    T *= params.dT;
+  }
 }
 
 void Potential::save()
@@ -498,7 +605,15 @@ void Potential::validate()
     flag[i] = tags[i] == "train" ? 0 : (tags[i] == "val" ? 1 : (tags[i] == "test" ? 2 : 3));
     nat[i] = natoms[i];
   }
+  // with free energies (input_file key or the checkpoints' "FE:" lines) the table shows total energies: the raw
+  // network sum and the target both get the per-atom reference energies added back, and output_mean is NOT added
+  // (Potential.cpp:981,1001-1018,1046-1051 -> Structure::unravel_Energy)
+  const bool unrav = !params.FE.empty();
+  std::vector<REAL> fes(Nlocal, 0.0);
+  if (unrav)
+    for (int i = 0; i < Nlocal; i++) fes[i] = free_energy_sum(params.FE, std::vector<int>(atom_Z[i].begin(), atom_Z[i].end()));
   std::vector<REAL> out = gather_in_order(mpi, E, Nsystems), tg = gather_in_order(mpi, targets, Nsystems);
+  std::vector<REAL> fe = gather_in_order(mpi, fes, Nsystems);
   std::vector<REAL> fl = gather_in_order(mpi, flag, Nsystems), na = gather_in_order(mpi, nat, Nsystems);
   if (!mpi->io_node()) return;
   using std::setw;
@@ -507,11 +622,20 @@ void Potential::validate()
   std::cout << std::setfill('-') << setw(80) << "-" << std::setfill(' ') << std::endl;
   REAL SSE = 0.0, min_E = 9e9, max_E = 0.0;
   std::cout << std::setprecision(10);
+  std::vector<REAL> shown(out), shown_t(tg);
   for (int i = 0; i < Nsystems; i++) {
-    int f = (int)fl[i];
-    const char* t = f == 0 ? "train" : f == 1 ? "val" : f == 2 ? "test" : "other";
-    std::cout << setw(4) << i + 1 << setw(22) << out[i] << setw(20) << tg[i] << setw(14) << (int)na[i] << setw(14) << t << std::endl;
-    REAL Error = out[i] - tg[i];
+    REAL Error;
+    if (unrav) {
+      shown[i] = (out[i] - output_mean) + fe[i];
+      shown_t[i] = (targets_shifted ? tg[i] : tg[i] - fe[i]) + fe[i];
+      std::cout << i + 1 << "               " << shown[i] << setw(25) << shown_t[i] << setw(15) << (int)na[i] << std::endl;
+      Error = shown[i] - shown_t[i];
+    } else {
+      int f = (int)fl[i];
+      const char* t = f == 0 ? "train" : f == 1 ? "val" : f == 2 ? "test" : "other";
+      std::cout << setw(4) << i + 1 << setw(22) << out[i] << setw(20) << tg[i] << setw(14) << (int)na[i] << setw(14) << t << std::endl;
+      Error = out[i] - tg[i];
+    }
     SSE += Error * Error;
     if (std::fabs(Error) < std::fabs(min_E)) min_E = Error;
     if (std::fabs(Error) > std::fabs(max_E)) max_E = Error;
@@ -521,11 +645,12 @@ void Potential::validate()
   std::cout << "Minimum Error =  " << min_E << std::endl;
   std::cout << "Maximum Error =  " << max_E << std::endl;
   std::cout << "RMS Error =  " << std::sqrt(SSE / (double)Nsystems) << std::endl;
-  // the reference compares the raw network sums (before output_mean is added back) with the targets
+  // the reference compares the raw network sums (before output_mean is added back) with the targets -- or, with
+  // free energies, the two total-energy columns
   std::vector<REAL> raw(out);
   for (int i = 0; i < Nsystems; i++) raw[i] -= output_mean;
   REAL p = 0.0;
-  REAL D = approximate_KS(raw, tg, &p);
+  REAL D = unrav ? approximate_KS(shown, shown_t, &p) : approximate_KS(raw, tg, &p);
   std::cout << std::endl << std::endl;
   std::cout << "-- Approximate Kolmogorov-Smirnov test --" << std::endl;
   std::cout << "  D       =  " << D << std::endl;

@@ -246,7 +246,7 @@ def write_prophet_xml(path: str, structures) -> None:
 
 
 def write_input_file(path: str, cfg: Config, *, niterations=1, checkpoint_in=None, checkpoint_out="potential",
-                     algorithm="rprop", extra: Sequence[str] = ()) -> None:
+                     algorithm="rprop", extra: Sequence[str] = (), data: Sequence[str] = ("data code=prophet",)) -> None:
     """An input_file for the reference CLI (keys: Setup.cpp:182-510)."""
     lines = ["network_type = nn", "hidden = " + " ".join(str(h) for h in cfg.hidden),
              "input = structure", "output = energy", "transfer = %s" % cfg.transfer,
@@ -264,9 +264,27 @@ def write_input_file(path: str, cfg: Config, *, niterations=1, checkpoint_in=Non
     if checkpoint_in:
         lines.append("checkpoint_in = %s" % checkpoint_in)
     lines += list(extra)
-    lines.append("data code=prophet")
+    lines += list(data)     # the data block: "data code=prophet" (systems come from PROPhet.xml) or code=vasp + directories
     with open(path, "w") as f:
         f.write("\n".join(lines) + "\n")
+
+
+def write_vasprun(dirpath: str, cell: np.ndarray, frac: np.ndarray, Z: Sequence[int], target: float) -> None:
+    """A minimal vasprun.xml holding exactly what the reference's VASP reader looks for (VASP.cpp:78-176):
+    atominfo/array[@name=atoms] symbols, structure/crystal basis rows, fractional positions, e_wo_entrp."""
+    os.makedirs(dirpath, exist_ok=True)
+    with open(os.path.join(dirpath, "vasprun.xml"), "w") as f:
+        f.write("<modeling>\n <atominfo>\n  <atoms>  %d </atoms>\n  <types> %d </types>\n  <array name=\"atoms\" >\n   <set>\n"
+                % (len(Z), len(set(int(z) for z in Z))))
+        for z in Z:
+            f.write("    <rc><c>%-2s</c><c>   1</c></rc>\n" % Z_TO_SYMBOL[int(z)])
+        f.write("   </set>\n  </array>\n </atominfo>\n <structure>\n  <crystal>\n   <varray name=\"basis\" >\n")
+        for row in np.asarray(cell).reshape(3, 3):
+            f.write("    <v> %r %r %r </v>\n" % tuple(float(v) for v in row))
+        f.write("   </varray>\n  </crystal>\n  <varray name=\"positions\" >\n")
+        for row in np.asarray(frac).reshape(-1, 3):
+            f.write("   <v> %r %r %r </v>\n" % tuple(float(v) for v in row))
+        f.write("  </varray>\n </structure>\n<i name=\"e_wo_entrp\">  %r </i>\n</modeling>\n" % float(target))
 
 
 def random_network(cfg: Config, Z: int, seed: int) -> Dict[str, np.ndarray]:

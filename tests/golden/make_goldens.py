@@ -97,7 +97,7 @@ def train_case(name, cfg, structures, n_iter, seed, *, precondition_from_checkpo
         shutil.rmtree(cwd, ignore_errors=True)
 
 
-def md_case(name, cfg, structure, seed, *, skin=1.0, node_transfer=None):
+def md_case(name, cfg, structure, seed, *, skin=1.0, node_transfer=None, free_energy=None, keep=None):
     """Ghost-expanded cell + full neighbour list -> ref_driver md -> npz."""
     cell, cart, Z, _, _ = structure
     cwd = tempfile.mkdtemp(prefix="golden_" + name + "_")
@@ -114,7 +114,8 @@ def md_case(name, cfg, structure, seed, *, skin=1.0, node_transfer=None):
                                   rows_of(cfg), rng_means[z], rng_scales[z], -1.25, 1.5, net["sizes"], net["params"],
                                   transfer=cfg.transfer,
                                   node_transfer=None if node_transfer is None else node_transfer[z],
-                                  header_precision=17, weight_precision=18)
+                                  header_precision=17, weight_precision=18,
+                                  free_energy=None if free_energy is None else free_energy[z])
             nets[z] = net
         x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + skin)
         numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + skin)
@@ -144,6 +145,10 @@ def md_case(name, cfg, structure, seed, *, skin=1.0, node_transfer=None):
             arrays["in_scale.%d" % z] = rng_scales[z]
             if node_transfer is not None:
                 arrays["node_transfer.%d" % z] = np.array(node_transfer[z])
+        if keep is not None:
+            arrays = {k: v for k, v in arrays.items() if k in keep}
+        if free_energy is not None:
+            arrays["free_energy"] = np.array([free_energy[z] for z in cfg.elements])
         np.savez_compressed(os.path.join(OUT, name + ".npz"), **arrays)
         print("wrote %s.npz (%d arrays, %d local + %d ghost atoms)" % (name, len(arrays), nlocal, len(x) - nlocal))
     finally:
@@ -269,6 +274,15 @@ def case_tio2_md():
     md_case("tio2_md", cfg, synth.make_structure(cfg, 6), seed=71)
 
 
+def case_tio2_md_fe():
+    """tio2_md again with "FE:" lines in both checkpoints: only the energies change (Potential.cpp:1159-1162), so only
+    they are kept; the inputs are tio2_md.npz's."""
+    cfg = synth.config_c3(1)
+    cfg.lattice = synth.lattice_tio2((2, 2, 3))
+    md_case("tio2_md_fe", cfg, synth.make_structure(cfg, 6), seed=71, free_energy={8: -4.25, 22: -7.5},
+            keep=("eatom", "etotal", "f"))
+
+
 def case_tutorial_c1():
     """First 4 shipped tutorial structures through the reference's VASP reader, auto-generated rows
     (Nradial=5 Nangular=4, Structure.cpp:818-851), net 9-20-1 tanh, reference-initialised weights (seed 135492)."""
@@ -374,6 +388,7 @@ def case_ks():
 
 
 CASES["ks"] = case_ks
+CASES["tio2_md_fe"] = case_tio2_md_fe
 CASES["opt_bfgs"] = case_opt_bfgs
 CASES["opt_sd_line"] = case_opt_sd_line
 CASES["opt_default_switch"] = case_opt_default_switch

@@ -140,3 +140,109 @@ def test_pair_style_nn_through_lammps_stand_in(name, tmp_path):
     assert rel_err(r["eatom"], c.d["eatom"]) < 1e-10
     assert abs(r["eng_vdwl"] - c.d["etotal"][0]) < 1e-10 * abs(c.d["etotal"][0])
     assert rel_err(r["f"], c.d["f"]) < 1e-10
+
+
+def test_pair_style_nn_free_energy_shift(tmp_path):
+    """Checkpoints carrying "FE:" lines: every per-atom energy becomes (E_i + sum of FE over locals and ghosts) / N
+    (Potential.cpp:1159-1162); forces are untouched."""
+    c = MDCase("tio2_md")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "tio2_md_fe.npz"))
+    syms = [synth.Z_TO_SYMBOL[z] for z in c.elements]
+    files = []
+    for k, z in enumerate(c.elements):
+        p = str(tmp_path / ("pot_" + synth.Z_TO_SYMBOL[z]))
+        ckpt.write_checkpoint(p, synth.Z_TO_SYMBOL[z], syms, {"G1": c.G1.tolist(), "G2": c.G2.tolist(), "G3": c.G3.tolist(), "G4": c.G4.tolist()},
+                              c.d["in_mean.%d" % z], c.d["in_scale.%d" % z], c.out_mean, c.out_scale, c.sizes, c.d["params.%d" % z],
+                              header_precision=17, free_energy=float(g["free_energy"][k]))
+        files.append(p)
+    types = list(range(1, len(c.elements) + 1))
+    r = hostapi.pair_nn_run(c.rcut, types, files, c.x, c.types, c.nlocal, c.numneigh, c.neigh)
+    assert rel_err(r["eatom"], g["eatom"]) < 1e-10
+    assert abs(r["eng_vdwl"] - g["etotal"][0]) < 1e-10 * abs(g["etotal"][0])
+    assert rel_err(r["f"], g["f"]) < 1e-10
+
+
+@pytest.mark.skipif(not os.path.exists(REF_CLI), reason="oracle/_ref/PROPhet not built")
+def test_cli_free_energy_training_and_validation(tmp_path):
+    """`free_energy Ti <v> O <v>` (Setup.cpp free_energy key -> System.cpp:142-147): targets have the per-atom
+    reference energies taken off before training, the saved potentials carry "FE:" lines, and -validate prints total
+    energies with them added back (Potential.cpp:1001-1018,1046-1051)."""
+    cfg = synth.CONFIGS["C3"](4)
+    ours = tmp_path / "ours"; ref = tmp_path / "ref"
+    fe = ("free_energy Ti -7.5 O -4.25",)
+    for d in (ours, ref):
+        d.mkdir()
+        _write_case(str(d), cfg, 4, [0, 0, 0, 1], [6, 4], seed=14, niter=5, extra=fe)
+    out_ref = _run(REF_CLI, ["-in", "input_file", "-train"], str(ref))
+    out_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-train"], str(ours))
+    t_ref, t_ours = _iteration_table(out_ref), _iteration_table(out_ours)
+    assert len(t_ref) == 5 and len(t_ours) == 5, (out_ref[-1500:], out_ours[-1500:])
+    assert np.allclose(np.array(t_ours), np.array(t_ref), rtol=2e-6, atol=0), (t_ours, t_ref)
+    for sym in ("O", "Ti"):
+        a = open(str(ours / ("trained_" + sym))).read()
+        b = open(str(ref / ("trained_" + sym))).read()
+        assert [l for l in a.splitlines() if l.startswith("FE:")] == [l for l in b.splitlines() if l.startswith("FE:")] != []
+    for d in (ours, ref):
+        txt = open(str(d / "input_file")).read().replace("checkpoint_in = start", "checkpoint_in = trained")
+        open(str(d / "input_file"), "w").write(txt)
+    v_ref = _run(REF_CLI, ["-in", "input_file", "-validate"], str(ref))
+    v_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-validate"], str(ours))
+
+    def table(txt):
+        rows = []
+        for line in txt.splitlines():
+            tok = line.split()
+            if len(tok) == 4 and tok[0].isdigit() and tok[3].isdigit():
+                rows.append((int(tok[0]), float(tok[1]), float(tok[2]), int(tok[3])))
+        return rows
+
+    tr, to = table(v_ref), table(v_ours)
+    assert len(tr) == 4 and len(to) == 4, (v_ref[-1500:], v_ours[-1500:])
+    for a, b in zip(to, tr):
+        assert a[0] == b[0] and a[3] == b[3]
+        assert abs(a[1] - b[1]) <= 1e-8 * abs(b[1]) and abs(a[2] - b[2]) <= 1e-9 * abs(b[2])
+    rms = lambda txt: float(re.search(r"RMS Error =\s+([-+0-9.eE]+)", txt).group(1))
+    assert abs(rms(v_ours) - rms(v_ref)) <= 1e-5 * abs(rms(v_ref))
+
+
+@pytest.mark.skipif(not os.path.exists(REF_CLI), reason="oracle/_ref/PROPhet not built")
+def test_cli_optimize_follows_reference_monte_carlo(tmp_path):
+    """`-optimize` (Potential::optimize_Gs, Potential.cpp:709-877): same libc rand() stream (seed key), so the perturbed
+    rows, the retrained errors, the Metropolis decisions, logfile.out and G_parameters.out must all follow the
+    reference.  The perturbed xi are non-integer: the descriptor refresh runs the binomial-series angular term.
+    Inputs are vasprun.xml files (fractional coordinates): with Cartesian inputs the reference converts the positions
+    to fractional AGAIN on every descriptor refresh (Structure.cpp:853-856 -> Normalize), which is not reproduced."""
+    cfg = synth.CONFIGS["C2"](5)
+    cfg.hidden = [5, 4]
+    cfg.G2 = cfg.G2[:4]
+    cfg.G4 = [cfg.G4[i] for i in (0, 3, 9, 14, 22, 31)]
+    ours = tmp_path / "ours"; ref = tmp_path / "ref"
+    extra = ("seed = 4242", "T0 = 1", "Tf = 0.85", "dT = 0.9", "Nsteps_per_T = 3", "step_size = 0.1")
+    for d in (ours, ref):
+        d.mkdir()
+        data = ["data code=vasp"]
+        for k in range(5):
+            cell, cart, Z, target, _ = synth.make_structure(cfg, 40 + k)
+            synth.write_vasprun(str(d / ("run%d" % k)), cell, cart @ np.linalg.inv(cell), Z, target)
+            data.append("./run%d%s" % (k, "  val" if k == 4 else ""))
+        net = synth.random_network(cfg, 14, 15)
+        ckpt.write_checkpoint(str(d / "start_Si"), "Si", ["Si"], {"G1": cfg.G1, "G2": cfg.G2, "G3": cfg.G3, "G4": cfg.G4},
+                              0.3 * np.abs(synth.normal(14, cfg.NG, 3)), 0.5 + np.abs(synth.normal(14, cfg.NG, 4)), 0.0, 1.0,
+                              net["sizes"], net["params"], header_precision=17)
+        synth.write_input_file(str(d / "input_file"), cfg, niterations=4, checkpoint_in="start", checkpoint_out="trained",
+                               extra=extra, data=data)
+    out_ref = _run(REF_CLI, ["-in", "input_file", "-optimize"], str(ref))
+    out_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-optimize"], str(ours))
+    err = lambda txt: [float(m) for m in re.findall(r"^Error =\s+([-+0-9.eE]+)", txt, flags=re.M)]
+    e_ref, e_ours = err(out_ref), err(out_ours)
+    assert len(e_ref) == 6 and len(e_ours) == 6, (out_ref[-800:], out_ours[-800:])
+    assert np.allclose(e_ours, e_ref, rtol=2e-5), (e_ours, e_ref)
+    t_ref, t_ours = _iteration_table(out_ref), _iteration_table(out_ours)
+    assert len(t_ref) == 24 and np.allclose(np.array(t_ours), np.array(t_ref), rtol=5e-6), (t_ours, t_ref)
+    num = lambda path: [[float(x) for x in re.findall(r"[-+]?[0-9.]+(?:e[-+]?[0-9]+)?", l)] for l in open(path)
+                        if l.strip() and not l.startswith(" -") and "accepted" not in l]
+    assert np.allclose(np.array(num(str(ours / "logfile.out"))), np.array(num(str(ref / "logfile.out"))), rtol=1e-5)
+    ga, gb = num(str(ours / "G_parameters.out")), num(str(ref / "G_parameters.out"))
+    assert len(ga) == len(gb) == 10
+    for ra, rb in zip(ga, gb):
+        assert len(ra) == len(rb) and np.allclose(ra, rb, rtol=1e-5), (ra, rb)

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 from golden_util import GOLDEN_DIR, TRAIN_CASES, TrainCase
-from prophet_b200 import hostapi
+from prophet_b200 import hostapi, synth
 
 
 def _ensure_built():
@@ -161,16 +161,6 @@ def test_vasprun_reader(tmp_path):
     d = tmp_path / "run1"
     d.mkdir()
     cell, frac, Z, target = c.cells[0], c.frac[0], c.Z[0], c.targets[0]
-    with open(d / "vasprun.xml", "w") as f:
-        f.write("<modeling>\n <atominfo>\n  <atoms>  %d </atoms>\n  <types> 1 </types>\n  <array name=\"atoms\" >\n   <set>\n" % len(Z))
-        for _ in Z:
-            f.write("    <rc><c>C </c><c>   1</c></rc>\n")
-        f.write("   </set>\n  </array>\n </atominfo>\n <structure>\n  <crystal>\n   <varray name=\"basis\" >\n")
-        for row in cell:
-            f.write("    <v> %r %r %r </v>\n" % tuple(float(v) for v in row))
-        f.write("   </varray>\n  </crystal>\n  <varray name=\"positions\" >\n")
-        for row in frac:
-            f.write("   <v> %r %r %r </v>\n" % tuple(float(v) for v in row))
-        f.write("  </varray>\n </structure>\n<i name=\"e_wo_entrp\">  %r </i>\n</modeling>\n" % float(target))
+    synth.write_vasprun(str(d), cell, frac, Z, target)
     cell2, pos2, Z2, t2 = hostapi.read_vasprun(str(d))
     assert np.array_equal(cell2, cell) and np.array_equal(pos2, frac) and np.array_equal(Z2, Z) and t2 == target
