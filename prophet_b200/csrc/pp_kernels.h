@@ -46,6 +46,7 @@ struct NetDev {
   int w_off[PP_MAX_LAYERS];           // offset of layer l's [n_out][n_in+1] block in the flat parameter vector
   int node_off[PP_MAX_LAYERS];        // offset of layer l's nodes in the transfer-id list
   int P;
+  unsigned tanh_layers;               // bit l set: every node of layer l (1-based, hidden) has the "tanh" transfer (id 1)
   const double* params;               // device, this element's parameters
   const int* tf;                      // device, transfer id per node
   const double* mean;                 // device [NG]

@@ -18,8 +18,13 @@
 // augmented weight matrix [n_out][n_in+1].
 #include "pp_common.cuh"
 #include "pp_kernels.h"
+#include "pp_fastmath.cuh"
+#include <cuda.h>
 #include <algorithm>
 #include <cmath>
+#include <cstring>
+#include <type_traits>
+#include <vector>
 
 #define MLP_WARPS 16
 #define MLP_THREADS (MLP_WARPS * 32)
@@ -34,19 +39,28 @@ struct MlpPlan {
   int ws_off[PP_MAX_LAYERS], hs_off[PP_MAX_LAYERS], ds_off[PP_MAX_LAYERS + 1];
   int x_off[2];                       // double-buffered raw descriptor tiles
   int ws_rows[PP_MAX_LAYERS];         // rows of Ws_l held in shared memory (zero padded)
-  int cvec_off, erow_off, mu_off, is_off, red_off, sttgt_off;
+  int cvec_off, erow_off, mu_off, is_off, red_off, sttgt_off, exptab_off, mbar_off;
+  int all_tanh[PP_MAX_LAYERS + 1];    // layer l (1..L-1) consists of tanh nodes only
   int stint_off_bytes;                // per-tile structure table: row offsets [TM+1] and tags [TM] (ints)
   int tf_off_bytes, desc_off_bytes;
-  int n_dw_tiles;
+  int n_dw_tiles;                     // entries of the weight-gradient table (tiles, or 2 * MLP_WARPS block slots)
+  int tma;                            // 1: descriptor tiles arrive as ONE 2-D tensor copy per tile (set at launch)
+  int blocked;                        // 1: the table holds register-blocked work items, two slots per warp
   size_t smem_bytes;
 };
 
-// one weight-gradient tile: dW_l[8 mi .. +8][8 ni .. +8] += delta_{l+1}^T [H_l, 1]
+// One weight-gradient work item: an nm x nn block (nm, nn in {1, 2}) of 8x8 DMMA tiles
+//   dW_l[8 (mi+i) .. +8][8 (ni+j) .. +8] += delta_{l+1}^T [H_l, 1]        (K = atoms of the tile)
+// A 2x2 block loads two A and two B fragments per k-step for four independent DMMAs: half the shared-memory
+// traffic of single tiles and four accumulator chains in flight instead of one.  Single tiles have nm = nn = 1.
+// The output node is the "layer" L-1 with delta = the per-atom error factor c (cvec, pitch 8, column 0).
 struct DwTile {
   int a_off;      // delta_{l+1} base + 8*mi          (doubles)
   int b_off;      // H_l base + 8*ni  (layer 0: column offset inside an X buffer)
   int dp, kp;     // pitches
-  int layer, mi, ni, pad;
+  int layer, mi, ni;
+  int nm, nn;     // block shape; nm = 0: empty slot
+  int pad[3];
 };
 
 __host__ __device__ static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
@@ -63,8 +77,9 @@ static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>
 {
   const int NTW = 16 * plan_nt(net);             // columns a warp pair covers (zero padded)
   p.TM = TM;
+  p.tma = 0;
   p.L = net.n_layers;
-  for (int l = 0; l <= p.L; l++) p.n[l] = net.sizes[l];
+  for (int l = 0; l <= p.L; l++) { p.n[l] = net.sizes[l]; p.all_tanh[l] = (net.tanh_layers >> l) & 1; }
   size_t off = 0;
   for (int l = 0; l < p.L; l++) {
     p.kpitch[l] = (l == 0 ? round_up(p.n[l] + 1, 8) : std::max(round_up(p.n[l] + 1, 8), NTW)) + 4;
@@ -73,7 +88,10 @@ static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>
     p.ws_rows[l] = rows;
     off += (size_t)rows * p.kpitch[l];
   }
-  for (int b = 0; b < 2; b++) { p.x_off[b] = (int)off; off += (size_t)TM * p.kpitch[0]; }
+  for (int b = 0; b < 2; b++) {          // 128-byte aligned: destination of the tensor copy
+    off = (off + 15) & ~(size_t)15;
+    p.x_off[b] = (int)off; off += (size_t)TM * p.kpitch[0];
+  }
   p.hs_off[0] = p.x_off[0];
   for (int l = 1; l < p.L; l++) { p.hs_off[l] = (int)off; off += (size_t)TM * p.kpitch[l]; }
   for (int l = 1; l < p.L; l++) {
@@ -81,12 +99,14 @@ static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>
     p.ds_off[l] = (int)off;
     off += (size_t)TM * p.dpitch[l];
   }
-  p.cvec_off = (int)off; off += TM;
+  p.cvec_off = (int)off; off += 8 * (size_t)TM;      // pitch 8: column 0 = c, columns 1..7 stay zero (DMMA A operand)
   p.erow_off = (int)off; off += TM;
   p.mu_off = (int)off; off += p.kpitch[0];
   p.is_off = (int)off; off += p.kpitch[0];
   p.red_off = (int)off; off += 3 * MLP_WARPS;
   p.sttgt_off = (int)off; off += TM;
+  p.exptab_off = (int)off; off += 64;          // 2^(j/64) for pp_fast_exp_nonpos
+  p.mbar_off = (int)off; off += 2;             // two mbarriers (one per descriptor-tile buffer)
   p.tf_off_bytes = (int)(off * sizeof(double));
   int nodes = 0;
   for (int l = 1; l <= p.L; l++) nodes += p.n[l];
@@ -96,22 +116,69 @@ static void make_plan(const NetDev& net, int TM, MlpPlan& p, std::vector<DwTile>
   bytes += (size_t)(2 * TM + 2) * sizeof(int);
   bytes = (bytes + 15) & ~(size_t)15;
   p.desc_off_bytes = (int)bytes;
-  int t = 0;
-  for (int l = 0; l < p.L - 1; l++) {
-    const int nm = round_up(p.n[l + 1], 8) / 8, nn = round_up(p.n[l] + 1, 8) / 8;
-    for (int mi = 0; mi < nm; mi++)
-      for (int ni = 0; ni < nn; ni++) {
-        if (tiles) {
-          DwTile d;
-          d.a_off = p.ds_off[l + 1] + 8 * mi;
-          d.b_off = (l == 0 ? 0 : p.hs_off[l]) + 8 * ni;
-          d.dp = p.dpitch[l + 1];
-          d.kp = p.kpitch[l];
-          d.layer = l; d.mi = mi; d.ni = ni; d.pad = 0;
-          tiles->push_back(d);
-        }
-        t++;
+  // Work items.  Blocked form when it fits two slots per warp: slot 0 takes any block, slot 1 at most two tiles
+  // (so a warp's accumulators stay within 6 tiles = 12 doubles); otherwise single tiles, warp w owning w, w+16, ...
+  std::vector<DwTile> blocks;
+  for (int l = 0; l < p.L; l++) {
+    const int rows = (l == p.L - 1) ? 1 : round_up(p.n[l + 1], 8) / 8, cols = round_up(p.n[l] + 1, 8) / 8;
+    for (int mi = 0; mi < rows; mi += 2)
+      for (int ni = 0; ni < cols; ni += 2) {
+        DwTile d;
+        memset(&d, 0, sizeof(d));
+        d.a_off = (l == p.L - 1 ? p.cvec_off : p.ds_off[l + 1]) + 8 * mi;
+        d.b_off = (l == 0 ? 0 : p.hs_off[l]) + 8 * ni;
+        d.dp = (l == p.L - 1) ? 8 : p.dpitch[l + 1];
+        d.kp = p.kpitch[l];
+        d.layer = l; d.mi = mi; d.ni = ni;
+        d.nm = std::min(2, rows - mi); d.nn = std::min(2, cols - ni);
+        blocks.push_back(d);
       }
+  }
+  std::stable_sort(blocks.begin(), blocks.end(), [](const DwTile& x, const DwTile& y) { return x.nm * x.nn > y.nm * y.nn; });
+  int n_big = 0;
+  for (const DwTile& d : blocks) n_big += (d.nm * d.nn > 2);
+  p.blocked = (n_big <= MLP_WARPS && (int)blocks.size() <= 2 * MLP_WARPS) ? 1 : 0;
+  int t = 0;
+  if (p.blocked) {
+    std::vector<DwTile> table(2 * MLP_WARPS);
+    for (DwTile& d : table) memset(&d, 0, sizeof(d));
+    int load[MLP_WARPS] = {0}, smsp[4] = {0, 0, 0, 0};
+    size_t b = 0;
+    for (; b < blocks.size() && b < (size_t)MLP_WARPS; b++) {      // largest first into the slot 0 of warp 0, 1, ...
+      table[2 * b] = blocks[b];
+      load[b] += blocks[b].nm * blocks[b].nn;
+      smsp[b & 3] += blocks[b].nm * blocks[b].nn;
+    }
+    for (; b < blocks.size(); b++) {                                 // the rest: least loaded scheduler, then least loaded warp
+      int best = -1;
+      for (int w = 0; w < MLP_WARPS; w++) {
+        if (table[2 * w + 1].nm) continue;
+        if (best < 0 || smsp[w & 3] < smsp[best & 3] || (smsp[w & 3] == smsp[best & 3] && load[w] < load[best])) best = w;
+      }
+      table[2 * best + 1] = blocks[b];
+      load[best] += blocks[b].nm * blocks[b].nn;
+      smsp[best & 3] += blocks[b].nm * blocks[b].nn;
+    }
+    if (tiles) *tiles = table;
+    t = 2 * MLP_WARPS;
+  } else {
+    for (int l = 0; l < p.L - 1; l++) {
+      const int nm = round_up(p.n[l + 1], 8) / 8, nn = round_up(p.n[l] + 1, 8) / 8;
+      for (int mi = 0; mi < nm; mi++)
+        for (int ni = 0; ni < nn; ni++) {
+          if (tiles) {
+            DwTile d;
+            memset(&d, 0, sizeof(d));
+            d.a_off = p.ds_off[l + 1] + 8 * mi;
+            d.b_off = (l == 0 ? 0 : p.hs_off[l]) + 8 * ni;
+            d.dp = p.dpitch[l + 1];
+            d.kp = p.kpitch[l];
+            d.layer = l; d.mi = mi; d.ni = ni; d.nm = 1; d.nn = 1;
+            tiles->push_back(d);
+          }
+          t++;
+        }
+    }
   }
   p.n_dw_tiles = t;
   bytes += (size_t)t * sizeof(DwTile);
@@ -139,28 +206,61 @@ __device__ __forceinline__ void cp_async8(void* dst, const void* src)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
-// Transfer functions and derivatives: Neural_network_node (NN_node.h:144-254)
-__device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, const double* __restrict__ table)
+// Bulk asynchronous copies (the TMA engine, 1-D form): one instruction per descriptor row instead of one cp.async per
+// 16 bytes per thread; completion is counted in bytes on a shared-memory mbarrier.
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count)
 {
-  if (id == 1) {   // tanh with the reference's asymptotic branch beyond |x| > 6 (NN_node.h:193-206)
-    double ax = fabs(in);
-    double sgn = (in > 0.0) ? 1.0 : ((in < 0.0) ? -1.0 : 0.0);
-    double e = exp(-2.0 * ax);
-    if (ax > 6.0) {
-      deriv = 4.0 * e * (1.0 - 2.0 * e);
-      return sgn * (1.0 - 2.0 * e * (1.0 - e));
-    }
-    double r = 1.0 / (1.0 + e);
-    deriv = 4.0 * e * r * r;          // 1/cosh^2
-    return sgn * (1.0 - e) * r;       // tanh
-  }
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
+{
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+
+// 2-D tiled tensor copy: box (kp0 columns x TM rows) of the [atoms][NG] descriptor array starting at row `row`;
+// columns beyond NG and rows beyond the array are zero-filled by the copy engine.
+__device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int row, unsigned long long* bar)
+{
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(smem_addr(dst)),
+      "l"(map), "r"(0), "r"(row), "r"(smem_addr(bar))
+      : "memory");
+}
+
+// Transfer functions and derivatives: Neural_network_node (NN_node.h:144-254).
+// Every transfer function but tanh: one out-of-line copy (the library tanh / cosh / sin / cos / exp bodies are long, and
+// the callers are unrolled over the thread's 2*NT values)
+__device__ __noinline__ double pp_transfer_other(int id, double in, double* deriv_out, const double* __restrict__ table)
+{
+  double deriv = 0.0;
+  double res = 0.0;
   switch (id) {
-    case 0: deriv = 1.0; return in;
+    case 0: deriv = 1.0; { res = in; break; }
     case 2: {   // cubic-spline table on [-17,17] (Tables.h:74-128, Tables.cpp:212-221)
       const double* X = table;
       const double* A = table + 1001;
-      if (in < X[0]) { deriv = 0.0; return A[3]; }
-      if (in >= X[1000]) { deriv = 0.0; return A[4 * 999] + A[4 * 999 + 1] + A[4 * 999 + 2] + A[4 * 999 + 3]; }
+      if (in < X[0]) { deriv = 0.0; { res = A[3]; break; } }
+      if (in >= X[1000]) { deriv = 0.0; { res = A[4 * 999] + A[4 * 999 + 1] + A[4 * 999 + 2] + A[4 * 999 + 3]; break; } }
       double m = 1000.0 / (X[1000] - X[0]);
       int bin = (int)(m * in - m * X[0]);
       bin = bin < 0 ? 0 : (bin > 999 ? 999 : bin);
@@ -169,43 +269,49 @@ __device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, 
       double x = in - X[bin];
       const double* a = A + 4 * bin;
       deriv = (3.0 * a[0] * x + 2.0 * a[1]) * x + a[2];
-      return ((a[0] * x + a[1]) * x + a[2]) * x + a[3];
+      { res = ((a[0] * x + a[1]) * x + a[2]) * x + a[3]; break; }
     }
     case 3: {   // tanh_crazy (NN_node.h:208-215)
       double t = tanh(in), ch = cosh(in);
       double u = 0.1 * in, u2 = u * u, u4 = u2 * u2;
       deriv = (1.0 - u4) / (ch * ch) - t * 0.1 * 4.0 * (u2 * u);
-      return (1.0 - u4) * t;
+      { res = (1.0 - u4) * t; break; }
     }
-    case 4: { double x2 = in * in; deriv = 3.0 * x2; return x2 * in; }
+    case 4: { double x2 = in * in; deriv = 3.0 * x2; { res = x2 * in; break; } }
     case 5: {   // pulse, a=b=c=1 (NN_node.h:181-190)
       double ex = exp(-in * in), s = sin(in), c = cos(in);
       deriv = ex * (-2.0 * in * s + c);
-      return s * ex;
+      { res = s * ex; break; }
     }
-    case 6: deriv = cos(in); return sin(in);
+    case 6: deriv = cos(in); { res = sin(in); break; }
     case 7: {   // periodic_tanh (NN_node.h:155-162)
       double inner = 4.0 * sin(in);
       double ch = cosh(inner);
       deriv = 4.0 * cos(in) / (ch * ch);
-      return tanh(inner);
+      { res = tanh(inner); break; }
     }
-    case 8: deriv = (in <= 0.0) ? 0.0 : 1.0; return (in <= 0.0) ? 0.0 : in;
+    case 8: deriv = (in <= 0.0) ? 0.0 : 1.0; { res = (in <= 0.0) ? 0.0 : in; break; }
   }
-  deriv = 0.0;
-  return 0.0;
+  *deriv_out = deriv;
+  return res;
+}
+
+__device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, const double* __restrict__ table,
+                                              const double* __restrict__ exptab)
+{
+  if (id == 1) return pp_fast_tanh(in, deriv, exptab);   // tanh, asymptotic branch beyond |x| > 6 (NN_node.h:193-206)
+  return pp_transfer_other(id, in, &deriv, table);
 }
 
 // One DMMA GEMM for the 8 rows of m-tile `mt` and the n-tiles [nt0, nt0+NT):  C[8][8 NT] = A[8][K] * B, with
-//   A(row,k) = As[(8*mt+row)*apitch + k]            (NORM: (A - mu[k]) * is[k], the descriptor normalisation)
+//   A(row,k) = As[(8*mt+row)*apitch + k]
 //   B(k,n)   = BT ? Bs[k*bpitch + n] : Bs[n*bpitch + k]
 // K is padded to a multiple of 4 and N to 8*NT per warp by zero-filled shared memory, so the loops carry no
 // bounds tests (GUARD = true restores a run-time tile count ntc <= NT for the one product whose B operand is not
 // padded that far).  The next k-step's fragments are loaded before the current step's DMMAs are issued.
-template <bool BT, bool NORM, bool GUARD, int NT>
+template <bool BT, bool GUARD, int NT>
 __device__ __forceinline__ void tile_gemm(double (&acc)[NT][2], const double* __restrict__ As, int apitch,
-                                          const double* __restrict__ Bs, int bpitch, int mt, int K4, int nt0, int ntc, int lane,
-                                          const double* __restrict__ mu, const double* __restrict__ is)
+                                          const double* __restrict__ Bs, int bpitch, int mt, int K4, int nt0, int ntc, int lane)
 {
   const int g = lane >> 2, q = lane & 3;
 #pragma unroll
@@ -214,17 +320,13 @@ __device__ __forceinline__ void tile_gemm(double (&acc)[NT][2], const double* __
   const double* bp = BT ? Bs + (size_t)q * bpitch + 8 * nt0 + g : Bs + (size_t)(8 * nt0 + g) * bpitch + q;
   const int bstep_k = BT ? 4 * bpitch : 4;
   const int bstep_n = BT ? 8 : 8 * bpitch;
-  const double* mup = mu + q;
-  const double* isp = is + q;
   double a_cur = ap[0];
-  if (NORM) a_cur = (a_cur - mup[0]) * isp[0];
   double b_cur[NT];
 #pragma unroll
   for (int nt = 0; nt < NT; nt++) b_cur[nt] = (!GUARD || nt < ntc) ? bp[nt * bstep_n] : 0.0;
   for (int k0 = 4; k0 < K4; k0 += 4) {
     ap += 4; bp += bstep_k;
     double a_nxt = ap[0];
-    if (NORM) { mup += 4; isp += 4; a_nxt = (a_nxt - mup[0]) * isp[0]; }
     double b_nxt[NT];
 #pragma unroll
     for (int nt = 0; nt < NT; nt++) b_nxt[nt] = (!GUARD || nt < ntc) ? bp[nt * bstep_n] : 0.0;
@@ -240,12 +342,59 @@ __device__ __forceinline__ void tile_gemm(double (&acc)[NT][2], const double* __
     if (!GUARD || nt < ntc) dmma884(acc[nt][0], acc[nt][1], a_cur, b_cur[nt]);
 }
 
+// Weight-gradient block: NM x NN DMMA tiles sharing their A (delta) and B (activation) fragments; accumulators are
+// dW[BASE + i*NN + j].  pa / pb point at this lane's element of the first k-step, sa / sb advance four atoms.
+template <int OWN, int BASE, int NM, int NN>
+__device__ __forceinline__ void dw_block(double (&dW)[OWN][2], const double* __restrict__ pa, const double* __restrict__ pb,
+                                         int sa, int sb, int TM)
+{
+#pragma unroll 2
+  for (int k0 = 0; k0 < TM; k0 += 4) {
+    double av[NM], bv[NN];
+#pragma unroll
+    for (int i = 0; i < NM; i++) av[i] = pa[8 * i];
+#pragma unroll
+    for (int j = 0; j < NN; j++) bv[j] = pb[8 * j];
+    pa += sa; pb += sb;
+#pragma unroll
+    for (int i = 0; i < NM; i++) {
+#pragma unroll
+      for (int j = 0; j < NN; j++) dmma884(dW[BASE + i * NN + j][0], dW[BASE + i * NN + j][1], av[i], bv[j]);
+    }
+  }
+}
+
+// Phase timing for tuning (build with -DPP_MLP_TIMING; not part of the product build): warp 0 and the last warp of
+// CTA 0 accumulate clock64() deltas per phase.
+#ifdef PP_MLP_TIMING
+__device__ unsigned long long pp_mlp_cycles[2][16];
+#define PP_T(i)                                                                              \
+  do {                                                                                       \
+    if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == MLP_WARPS - 1)) {              \
+      const long long now_ = clock64();                                                      \
+      pp_mlp_cycles[warp ? 1 : 0][i] += (unsigned long long)(now_ - tprev_);                 \
+      tprev_ = now_;                                                                         \
+    }                                                                                        \
+  } while (0)
+extern "C" int pp_debug_mlp_cycles(unsigned long long* out, int reset)
+{
+  if (out && cudaMemcpyFromSymbol(out, pp_mlp_cycles, sizeof(pp_mlp_cycles)) != cudaSuccess) return 1;
+  if (reset) {
+    unsigned long long z[2][16] = {};
+    if (cudaMemcpyToSymbol(pp_mlp_cycles, z, sizeof(z)) != cudaSuccess) return 1;
+  }
+  return 0;
+}
+#else
+#define PP_T(i)
+#endif
+
 // MODE: PP_MLP_FORWARD (energies only), PP_MLP_TRAIN (two-phase backward: c per structure given),
 //       PP_MLP_INPUT_GRAD (dE/dG, MD), PP_MLP_FUSED (single pass: forward, per-structure error, backward; needs
 //       tiles made of whole structures of a single-element system)
 template <int MODE, int NT, int OWN>
 __global__ void __launch_bounds__(MLP_THREADS, 1)
-mlp_kernel(MlpArgs a, MlpPlan p)
+mlp_kernel(MlpArgs a, MlpPlan p, const __grid_constant__ CUtensorMap tmap)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sm = reinterpret_cast<double*>(smem_raw);
@@ -294,8 +443,11 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     const int* srcw = reinterpret_cast<const int*>(a.dw_tiles);
     for (int i = tid; i < nwords; i += MLP_THREADS) dst[i] = srcw[i];
   }
+  for (int i = tid; i < 64; i += MLP_THREADS) sm[p.exptab_off + i] = exp2((double)i * 0.015625);
+  for (int i = tid; i < 8 * TM; i += MLP_THREADS) sm[p.cvec_off + i] = 0.0;      // columns 1..7 stay zero
   const double* mu = sm + p.mu_off;
   const double* is = sm + p.is_off;
+  const double* exptab = sm + p.exptab_off;
 
   // ---- parameter-gradient accumulators ------------------------------------------------------------------------
   double dW[OWN][2];
@@ -333,10 +485,23 @@ mlp_kernel(MlpArgs a, MlpPlan p)
   int* st_lo = reinterpret_cast<int*>(smem_raw + p.stint_off_bytes);     // [TM+1] first row of each structure of the tile
   int* st_tag = st_lo + TM + 1;                                            // [TM]
   double* st_tgt = sm + p.sttgt_off;                                       // [TM]
-  // asynchronous copy of one tile's raw descriptor rows into X[buf]
+  // Asynchronous copy of one tile's raw descriptor rows into X[buf]: one tensor copy per tile, issued by one thread and
+  // counted in bytes on the buffer's mbarrier (p.tma), or cp.async per thread when the rows are gathered.
+  unsigned long long* mbar = reinterpret_cast<unsigned long long*>(sm + p.mbar_off);
+  const bool bulk = p.tma != 0;
   auto issue_load = [&](const Geom& gm, int buf) {
     const int row0 = gm.row0, nvalid = gm.nvalid;
     double* X = sm + p.x_off[buf];
+    if (bulk) {
+      // rows are consecutive atoms (no gather): one tensor copy of the whole box; rows past nvalid belong to the next
+      // structure (or are zero past the end of the array) and are masked further down like any padding row
+      if (tid == 0) {
+        fence_proxy_async();            // the buffer was last read through the generic proxy (previous tile's gradients)
+        mbar_arrive_expect_tx(mbar + buf, (unsigned)TM * (unsigned)kp0 * 8u);
+        tma_load_tile(X, &tmap, row0, mbar + buf);
+      }
+      return;
+    }
     for (int r = warp; r < TM; r += MLP_WARPS) {
       double* dst = X + (size_t)r * kp0;
       if (r < nvalid) {
@@ -350,19 +515,35 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     }
     cp_async_commit();
   };
+  if (bulk && tid == 0) {
+    mbar_init(mbar, 1);
+    mbar_init(mbar + 1, 1);
+    fence_proxy_async();
+  }
+  __syncwarp();
 
   int buf = 0;
   Geom g_cur = tile_geom(blockIdx.x), g_nxt = tile_geom(blockIdx.x + gridDim.x);
   if ((int)blockIdx.x < n_tiles) issue_load(g_cur, 0);
   __syncthreads();
 
-  const int mt = warp >> 1, half = warp & 1;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
+  // warps w and w + 8 share m-tile w; with warp % 4 = scheduler, every scheduler hosts two first and two second halves
+  const int mt = warp & (MLP_WARPS / 2 - 1), half = warp / (MLP_WARPS / 2);
+#ifdef PP_MLP_TIMING
+  const long long tstart_ = clock64();
+#endif
+  int n_done = 0;      // tiles this CTA has finished: buffer = n_done & 1, mbarrier phase = (n_done >> 1) & 1
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1, n_done++) {
     const int row0 = g_cur.row0, nvalid = g_cur.nvalid;
     const int s_first = g_cur.s0, s_last = g_cur.s1;
     const Geom g_nn = tile_geom(tile + 2 * gridDim.x);      // consumed one iteration from now
-    cp_async_wait_all();
+#ifdef PP_MLP_TIMING
+    long long tprev_ = clock64();
+#endif
+    if (bulk) mbar_wait(mbar + buf, (unsigned)(n_done >> 1) & 1u);
+    else cp_async_wait_all();
     __syncthreads();
+    PP_T(0);
     if (tile + (int)gridDim.x < n_tiles) issue_load(g_nxt, buf ^ 1);
     if (MODE == PP_MLP_FUSED) {
       // structure table of this tile; its global-load latency hides behind the forward pass (read after the next barrier)
@@ -373,6 +554,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
       }
     }
     const double* X = sm + p.x_off[buf];
+    PP_T(1);
     if (MODE == PP_MLP_TRAIN || MODE == PP_MLP_INPUT_GRAD) {
       for (int r = tid; r < TM; r += MLP_THREADS) {
         double c = 0.0;
@@ -380,35 +562,77 @@ mlp_kernel(MlpArgs a, MlpPlan p)
           const size_t atom = a.rows ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r);
           c = (MODE == PP_MLP_TRAIN) ? a.cstruct[a.atom_struct[atom]] : a.out_scale;
         }
-        cvec[r] = c;
+        cvec[8 * r] = c;
       }
     }
 
+    // ---- descriptor normalisation (NN.cpp:647-651), in place and once per tile: the warp pair that owns 8 rows
+    // rewrites them, so the layer-0 product and the layer-0 weight gradients read plain operands
+    if (mt < TM / 8) {
+      double* xr = sm + p.x_off[buf] + (size_t)(8 * mt + g) * kp0;
+#pragma unroll 4
+      for (int c = 4 * half + q; c < NG; c += 8) xr[c] = (xr[c] - mu[c]) * is[c];
+      if (bulk && half == 0 && q == 0) xr[NG] = 1.0;      // the tensor copy zero-fills the padding; column NG is the bias input
+      pair_barrier(mt);
+    }
+    PP_T(14);
     // ---- forward through the hidden layers: a pair of warps per m-tile (8 atoms), n-tiles split between them ----
     if (mt < TM / 8) {
-      double acc[NT][2];
-      for (int l = 0; l < L - 1; l++) {
+      // one hidden layer for this warp's n-tiles [nt0, nt0 + NTC)
+      auto fwd_layer = [&](int l, auto ntc_tag) {
+        constexpr int NTC = decltype(ntc_tag)::value;
         const int n_in = p.n[l], n_out = p.n[l + 1];
         const int nt0 = half * NT;
-        if (l == 0) tile_gemm<false, true, false, NT>(acc, X, kp0, sm + p.ws_off[0], kp0, mt, round_up(n_in + 1, 4), nt0, NT, lane, mu, is);
-        else tile_gemm<false, false, false, NT>(acc, sm + p.hs_off[l], p.kpitch[l], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_in + 1, 4), nt0, NT, lane, mu, is);
+        double acc[NTC][2];
+        if (l == 0) tile_gemm<false, false, NTC>(acc, X, kp0, sm + p.ws_off[0], kp0, mt, round_up(n_in + 1, 4), nt0, NTC, lane);
+        else tile_gemm<false, false, NTC>(acc, sm + p.hs_off[l], p.kpitch[l], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_in + 1, 4), nt0, NTC, lane);
+        PP_T(2);
         double* Hn = sm + p.hs_off[l + 1] + (size_t)(8 * mt + g) * p.kpitch[l + 1];
         double* Dn = sm + p.ds_off[l + 1] + (size_t)(8 * mt + g) * p.dpitch[l + 1];
-        const int* tfl = tfs + net.node_off[l];
+        if (p.all_tanh[l + 1]) {
+          // every node of the layer is a tanh: evaluate the thread's 2*NTC values as straight-line code, so that
+          // their dependent FP64 chains (exp, reciprocal) overlap instead of running one after the other
+          double tv[NTC][2], dv[NTC][2];
 #pragma unroll
-        for (int nt = 0; nt < NT; nt++) {
+          for (int nt = 0; nt < NTC; nt++) {
 #pragma unroll
-          for (int h = 0; h < 2; h++) {
-            const int n = 8 * (nt0 + nt) + 2 * q + h;
-            if (n < n_out) {
-              double d;
-              double t = pp_transfer(tfl[n], acc[nt][h], d, a.tanh_table);
-              Hn[n] = t;
-              if (BACKWARD) Dn[n] = d;
+            for (int h = 0; h < 2; h++) tv[nt][h] = pp_fast_tanh(acc[nt][h], dv[nt][h], exptab);
+          }
+#pragma unroll
+          for (int nt = 0; nt < NTC; nt++) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * (nt0 + nt) + 2 * q + h;
+              if (n < n_out) {
+                Hn[n] = tv[nt][h];
+                if (BACKWARD) Dn[n] = dv[nt][h];
+              }
+            }
+          }
+        } else {
+          const int* tfl = tfs + net.node_off[l];
+#pragma unroll
+          for (int nt = 0; nt < NTC; nt++) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * (nt0 + nt) + 2 * q + h;
+              if (n < n_out) {
+                double d;
+                double t = pp_transfer(tfl[n], acc[nt][h], d, a.tanh_table, exptab);
+                Hn[n] = t;
+                if (BACKWARD) Dn[n] = d;
+              }
             }
           }
         }
+      };
+      for (int l = 0; l < L - 1; l++) {
+        // a warp whose last n-tile lies wholly in the padding (the second half of an odd tile count) skips it
+        if (NT > 1 && 8 * (half * NT + NT - 1) >= p.n[l + 1]) fwd_layer(l, std::integral_constant<int, (NT > 1 ? NT - 1 : 1)>{});
+        else fwd_layer(l, std::integral_constant<int, NT>{});
+        PP_T(3);
         pair_barrier(mt);
+        PP_T(4);
       }
       // ---- output node (always linear, NN.cpp:76): y = w_out . [H, 1];  4 lanes per atom, first warp of the pair ----
       if (half == 0) {
@@ -417,7 +641,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
         double y = 0.0;
         if (L == 1) {
           const double* xr = X + (size_t)(8 * mt + g) * kp0;
-          for (int k = q; k <= n_in; k += 4) y = fma((xr[k] - mu[k]) * is[k], wo[k], y);
+          for (int k = q; k <= n_in; k += 4) y = fma(xr[k], wo[k], y);
         } else {
           const double* Hl = sm + p.hs_off[L - 1] + (size_t)(8 * mt + g) * p.kpitch[L - 1];
           for (int k = q; k <= n_in; k += 4) y = fma(Hl[k], wo[k], y);
@@ -435,6 +659,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
         }
       }
     }
+    PP_T(5);
     if (MODE == PP_MLP_FUSED) {
       // ---- per-structure energy, error and loss terms (Potential.cpp:641-668) --------------------------------
       // After this one barrier every warp works out the error factor c of ITS OWN 8 rows by summing the energies
@@ -442,10 +667,11 @@ mlp_kernel(MlpArgs a, MlpPlan p)
       // shared-memory loads), so no second barrier is needed before the backward pass.  The structure's outputs
       // are written by the warp whose rows contain the structure's first atom.
       __syncthreads();
+      PP_T(6);
       if (mt < TM / 8) {
         const int rb = 8 * mt, re = 8 * mt + 8;
         const int ns = s_last - s_first;
-        if (lane < 8) cvec[rb + lane] = 0.0;
+        if (lane < 8) cvec[8 * (rb + lane)] = 0.0;
         __syncwarp();
         for (int i = 0; i < ns; i++) {
           const int r_lo = st_lo[i], r_hi = st_lo[i + 1];
@@ -463,7 +689,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
             if (lane == 0) a.E_struct[s_first + i] = e;
           }
           const int r = rb + lane;
-          if (lane < 8 && r >= r_lo && r < r_hi) cvec[r] = c;
+          if (lane < 8 && r >= r_lo && r < r_hi) cvec[8 * r] = c;
         }
         __syncwarp();
       }
@@ -471,6 +697,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
       __syncthreads();   // cvec
     }
 
+    PP_T(7);
     if (BACKWARD && mt < TM / 8) {
       double acc[NT][2];
       // ---- delta of the last hidden layer: c * w_out[n] * T'(z[n])  (output node linear) ------------------------
@@ -480,26 +707,35 @@ mlp_kernel(MlpArgs a, MlpPlan p)
           const int nt0 = half * NT, ntc = NT;
           double* Dr = sm + p.ds_off[L - 1] + (size_t)(8 * mt + g) * p.dpitch[L - 1];
           const double* wo = sm + p.ws_off[L - 1];
-          const double c = cvec[8 * mt + g];
+          const double c = cvec[8 * (8 * mt + g)];
           const int n_end = min(n_h, 8 * (nt0 + ntc));
           for (int n = 8 * nt0 + q; n < n_end; n += 4) Dr[n] *= c * wo[n];
         }
         pair_barrier(mt);
-        for (int l = L - 2; l >= 1; l--) {
-          // delta_l = (delta_{l+1} * W_l[:, :n_l]) .* T'(z_l)
+        PP_T(8);
+        // delta_l = (delta_{l+1} * W_l[:, :n_l]) .* T'(z_l) for this warp's n-tiles [nt0, nt0 + NTC)
+        auto bwd_layer = [&](int l, auto ntc_tag) {
+          constexpr int NTC = decltype(ntc_tag)::value;
           const int n_l = p.n[l], n_up = p.n[l + 1];
           const int nt0 = half * NT;
-          tile_gemm<true, false, false, NT>(acc, sm + p.ds_off[l + 1], p.dpitch[l + 1], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_up, 4), nt0, NT, lane, mu, is);
+          double accb[NTC][2];
+          tile_gemm<true, false, NTC>(accb, sm + p.ds_off[l + 1], p.dpitch[l + 1], sm + p.ws_off[l], p.kpitch[l], mt, round_up(n_up, 4), nt0, NTC, lane);
           double* Dr = sm + p.ds_off[l] + (size_t)(8 * mt + g) * p.dpitch[l];
 #pragma unroll
-          for (int nt = 0; nt < NT; nt++) {
+          for (int nt = 0; nt < NTC; nt++) {
 #pragma unroll
             for (int h = 0; h < 2; h++) {
               const int n = 8 * (nt0 + nt) + 2 * q + h;
-              if (n < n_l) Dr[n] *= acc[nt][h];
+              if (n < n_l) Dr[n] *= accb[nt][h];
             }
           }
+        };
+        for (int l = L - 2; l >= 1; l--) {
+          if (NT > 1 && 8 * (half * NT + NT - 1) >= p.n[l]) bwd_layer(l, std::integral_constant<int, (NT > 1 ? NT - 1 : 1)>{});
+          else bwd_layer(l, std::integral_constant<int, NT>{});
+          PP_T(9);
           pair_barrier(mt);
+          PP_T(10);
         }
       }
       if (MODE == PP_MLP_INPUT_GRAD) {
@@ -513,7 +749,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
           const int hc = half ? ntl - h0 : (ntl + 1) >> 1;
           for (int c0 = 0; c0 < hc; c0 += NT) {
             const int ntc = min(NT, hc - c0);
-            tile_gemm<true, false, true, NT>(acc, sm + p.ds_off[1], p.dpitch[1], sm + p.ws_off[0], kp0, mt, round_up(p.n[1], 4), h0 + c0, ntc, lane, mu, is);
+            tile_gemm<true, true, NT>(acc, sm + p.ds_off[1], p.dpitch[1], sm + p.ws_off[0], kp0, mt, round_up(p.n[1], 4), h0 + c0, ntc, lane);
             if (r < nvalid) {
 #pragma unroll
               for (int nt = 0; nt < NT; nt++) {
@@ -529,7 +765,7 @@ mlp_kernel(MlpArgs a, MlpPlan p)
           }
         } else if (r < nvalid && half == 0) {
           const double* wo = sm + p.ws_off[0];
-          for (int k = q; k < NG; k += 4) a.dEdG[atom * NG + k] = cvec[r] * wo[k] * is[k];
+          for (int k = q; k < NG; k += 4) a.dEdG[atom * NG + k] = cvec[8 * r] * wo[k] * is[k];
         }
       }
     }
@@ -537,48 +773,56 @@ mlp_kernel(MlpArgs a, MlpPlan p)
     // ---- parameter gradients: dW_l += delta_{l+1}^T * [H_l, 1]  (K = atoms of the tile) ------------------------
     if constexpr (GRADW) {
       __syncthreads();
-      {
-        // output-node gradient on the threads of the LAST warps (they own the fewest weight-gradient tiles)
-        const int n_in = p.n[L - 1];
-        const int j = MLP_THREADS - 1 - tid;
-        if (j <= n_in) {
-          double s = 0.0;
-          if (L == 1) {
-            const double m = mu[j], sc = is[j];
-            for (int r = 0; r < TM; r++) s = fma(cvec[r], (X[(size_t)r * kp0 + j] - m) * sc, s);
-          } else {
-            const double* Hl = sm + p.hs_off[L - 1] + j;
-            const int kp = p.kpitch[L - 1];
-            for (int r = 0; r < TM; r++) s = fma(cvec[r], Hl[(size_t)r * kp], s);
+      PP_T(11);
+      if constexpr (OWN == 6) {
+        // register-blocked work items, two slots per warp (make_plan); the output node is one of the "layers"
+                {
+          const DwTile d = dwt[2 * warp];
+          if (d.nm) {
+            const double* pa = sm + d.a_off + g + (size_t)q * d.dp;        // A(m = neuron, k = atom) = delta[atom][neuron]
+            const double* pb = (d.layer == 0 ? X : sm) + d.b_off + g + (size_t)q * d.kp;   // B(k = atom, n = input)
+            const int sa = 4 * d.dp, sb = 4 * d.kp;
+            if (d.nm == 2 && d.nn == 2) dw_block<OWN, 0, 2, 2>(dW, pa, pb, sa, sb, TM);
+            else if (d.nn == 2) dw_block<OWN, 0, 1, 2>(dW, pa, pb, sa, sb, TM);
+            else if (d.nm == 2) dw_block<OWN, 0, 2, 1>(dW, pa, pb, sa, sb, TM);
+            else dw_block<OWN, 0, 1, 1>(dW, pa, pb, sa, sb, TM);
           }
-          dwout += s;
         }
-      }
+        PP_T(12);
+        {
+          const DwTile d = dwt[2 * warp + 1];
+          if (d.nm) {
+            const double* pa = sm + d.a_off + g + (size_t)q * d.dp;
+            const double* pb = (d.layer == 0 ? X : sm) + d.b_off + g + (size_t)q * d.kp;
+            const int sa = 4 * d.dp, sb = 4 * d.kp;
+            if (d.nn == 2) dw_block<OWN, 4, 1, 2>(dW, pa, pb, sa, sb, TM);
+            else if (d.nm == 2) dw_block<OWN, 4, 2, 1>(dW, pa, pb, sa, sb, TM);
+            else dw_block<OWN, 4, 1, 1>(dW, pa, pb, sa, sb, TM);
+          }
+        }
+      } else {
+        {
+          // output-node gradient on the threads of the LAST warps (they own the fewest weight-gradient tiles)
+          const int n_in = p.n[L - 1];
+          const int j = MLP_THREADS - 1 - tid;
+          if (j <= n_in) {
+            double s = 0.0;
+            const double* Hl = (L == 1 ? X : sm + p.hs_off[L - 1]) + j;
+            const int kp = (L == 1) ? kp0 : p.kpitch[L - 1];
+            for (int r = 0; r < TM; r++) s = fma(cvec[8 * r], Hl[(size_t)r * kp], s);
+            dwout += s;
+          }
+        }
+        PP_T(12);
 #pragma unroll
-      for (int t = 0; t < OWN; t++) {
-        const int tile_id = warp + t * MLP_WARPS;
-        if (tile_id < p.n_dw_tiles) {
-          const DwTile d = dwt[tile_id];
-          const double* Dl = sm + d.a_off + g;                      // A(m = neuron, k = atom) = delta[atom][neuron]
-          double c0 = dW[t][0], c1 = dW[t][1];
-          if (d.layer == 0) {
-            const double* Hl = X + d.b_off + g;                     // B(k = atom, n = input) = normalised descriptor
-            const double m = mu[d.b_off + g], sc = is[d.b_off + g];
-            const double* pa = Dl + (size_t)q * d.dp;
-            const double* pb = Hl + (size_t)q * d.kp;
+        for (int t = 0; t < OWN; t++) {
+          const int tile_id = warp + t * MLP_WARPS;
+          if (tile_id < p.n_dw_tiles) {
+            const DwTile d = dwt[tile_id];
+            const double* pa = sm + d.a_off + g + (size_t)q * d.dp;
+            const double* pb = (d.layer == 0 ? X : sm) + d.b_off + g + (size_t)q * d.kp;
             const int sa = 4 * d.dp, sb = 4 * d.kp;
-#pragma unroll 4
-            for (int k0 = 0; k0 < TM; k0 += 4) {
-              const double av = *pa;
-              const double bv = (*pb - m) * sc;
-              pa += sa; pb += sb;
-              dmma884(c0, c1, av, bv);
-            }
-          } else {
-            const double* Hl = sm + d.b_off + g;
-            const double* pa = Dl + (size_t)q * d.dp;
-            const double* pb = Hl + (size_t)q * d.kp;
-            const int sa = 4 * d.dp, sb = 4 * d.kp;
+            double c0 = dW[t][0], c1 = dW[t][1];
 #pragma unroll 4
             for (int k0 = 0; k0 < TM; k0 += 4) {
               const double av = *pa;
@@ -586,36 +830,63 @@ mlp_kernel(MlpArgs a, MlpPlan p)
               pa += sa; pb += sb;
               dmma884(c0, c1, av, bv);
             }
+            dW[t][0] = c0; dW[t][1] = c1;
           }
-          dW[t][0] = c0; dW[t][1] = c1;
         }
       }
+      PP_T(13);
     }
     g_cur = g_nxt;
     g_nxt = g_nn;
   }
   cp_async_wait_all();
+#ifdef PP_MLP_TIMING
+  if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == MLP_WARPS - 1)) {
+    pp_mlp_cycles[warp ? 1 : 0][15] += (unsigned long long)(clock64() - tstart_);
+  }
+#endif
 
   // ---- per-CTA partial gradient (+ loss terms) -> scratch ------------------------------------------------------
   if constexpr (GRADW) {
     double* out = a.partial + (size_t)blockIdx.x * (a.P_total + 3) + a.p_off;
-    {
-      const int n_in = p.n[L - 1];
-      const int j = MLP_THREADS - 1 - tid;
-      if (j <= n_in) out[net.w_off[L - 1] + j] = dwout;
-    }
+    if constexpr (OWN == 6) {
+      // slot 0 holds tiles 0..3 (t = i*nn + j), slot 1 tiles 4..5
 #pragma unroll
-    for (int t = 0; t < OWN; t++) {
-      const int tile_id = warp + t * MLP_WARPS;
-      if (tile_id < p.n_dw_tiles) {
-        const DwTile d = dwt[tile_id];
-        const int neuron = 8 * d.mi + g;
-        const int n_in = p.n[d.layer];
-        if (neuron < p.n[d.layer + 1]) {
+      for (int t = 0; t < 6; t++) {
+        const DwTile d = dwt[2 * warp + (t >> 2)];
+        const int tt = t & 3;
+        if (tt < d.nm * d.nn) {
+          const int bi = (d.nn == 2) ? (tt >> 1) : tt, bj = (d.nn == 2) ? (tt & 1) : 0;
+          const int neuron = 8 * (d.mi + bi) + g;
+          const int n_in = p.n[d.layer];
+          if (neuron < p.n[d.layer + 1]) {
 #pragma unroll
-          for (int h = 0; h < 2; h++) {
-            const int k = 8 * d.ni + 2 * q + h;
-            if (k <= n_in) out[net.w_off[d.layer] + (size_t)neuron * (n_in + 1) + k] = dW[t][h];
+            for (int h = 0; h < 2; h++) {
+              const int k = 8 * (d.ni + bj) + 2 * q + h;
+              if (k <= n_in) out[net.w_off[d.layer] + (size_t)neuron * (n_in + 1) + k] = dW[t][h];
+            }
+          }
+        }
+      }
+    } else {
+      {
+        const int n_in = p.n[L - 1];
+        const int j = MLP_THREADS - 1 - tid;
+        if (j <= n_in) out[net.w_off[L - 1] + j] = dwout;
+      }
+#pragma unroll
+      for (int t = 0; t < OWN; t++) {
+        const int tile_id = warp + t * MLP_WARPS;
+        if (tile_id < p.n_dw_tiles) {
+          const DwTile d = dwt[tile_id];
+          const int neuron = 8 * d.mi + g;
+          const int n_in = p.n[d.layer];
+          if (neuron < p.n[d.layer + 1]) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int k = 8 * d.ni + 2 * q + h;
+              if (k <= n_in) out[net.w_off[d.layer] + (size_t)neuron * (n_in + 1) + k] = dW[t][h];
+            }
           }
         }
       }
@@ -635,6 +906,25 @@ mlp_kernel(MlpArgs a, MlpPlan p)
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// cuTensorMapEncodeTiled through the runtime (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled()
+{
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)ptr;
+  }
+  return fn;
+}
+
 static int g_sm_count = 0;
 static int sm_count()
 {
@@ -697,13 +987,27 @@ int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launc
   const bool gradw = (mode == PP_MLP_TRAIN || mode == PP_MLP_FUSED);
   if (!gradw && grid > n_tiles) grid = n_tiles;   // gradient modes: every CTA writes its (possibly zero) partial
   if (grid == 0) return 0;
+  // Tensor map of the [atoms][NG] descriptor array for the per-tile copy (box: kpitch[0] columns x TM rows).  Only
+  // when rows are consecutive atoms and the row size is a 16-byte multiple; anything else keeps the cp.async path.
+  CUtensorMap tmap;
+  memset(&tmap, 0, sizeof(tmap));
+  if (a.rows == nullptr && (net.sizes[0] & 1) == 0 && a.M > 0 && plan.kpitch[0] <= 256 && encode_tiled() != nullptr) {
+    const cuuint64_t gdim[2] = {(cuuint64_t)net.sizes[0], (cuuint64_t)a.M};
+    const cuuint64_t gstride[1] = {(cuuint64_t)net.sizes[0] * sizeof(double)};
+    const cuuint32_t box[2] = {(cuuint32_t)plan.kpitch[0], (cuuint32_t)TM};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode_tiled()(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(a.G), gdim, gstride, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    plan.tma = (r == CUDA_SUCCESS) ? 1 : 0;
+  }
   const int NTsel = plan_nt(net);
-  const bool many = (plan.n_dw_tiles + MLP_WARPS - 1) / MLP_WARPS > 6;
+  const bool many = !plan.blocked;      // OWN = 6: register-blocked table; OWN = 16: single tiles, up to 16 per warp
 #define PP_LAUNCH(MODE_, NT_, OWN_)                                                                             \
   {                                                                                                             \
     auto k = mlp_kernel<MODE_, NT_, OWN_>;                                                                      \
     PP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes));        \
-    k<<<grid, MLP_THREADS, plan.smem_bytes, st>>>(a, plan);                                                     \
+    k<<<grid, MLP_THREADS, plan.smem_bytes, st>>>(a, plan, tmap);                                               \
   }
 #define PP_LAUNCH_NT(MODE_, OWN_)                                \
   {                                                              \
