@@ -31,7 +31,7 @@ SYMBOLS = [
     "pp_set_input_scaling", "pp_cart_to_frac", "pp_add_structures", "pp_clear_structures", "pp_recompute_descriptors",
     "pp_num_structures",
     "pp_num_atoms", "pp_get_descriptors", "pp_get_neighbors", "pp_precondition", "pp_get_input_scaling", "pp_epoch",
-    "pp_epoch_device", "pp_epoch_result_dev", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
+    "pp_epoch_device", "pp_epoch_result_dev", "pp_epoch_form", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
     "pp_md_compute", "pp_md_build_neighbors", "pp_md_get_neighbors", "pp_md_step", "pp_md_step_device",
     "pp_comm_unique_id", "pp_comm_init", "pp_comm_rank", "pp_comm_size", "pp_kernel_launches", "pp_last_phase_ms",
     "pp_stream", "pp_column_sums_static", "pp_comm_allreduce_host",
@@ -215,6 +215,10 @@ class Context:
 
     def epoch_device(self):
         _check(lib().pp_epoch_device(self._h))
+
+    def epoch_form(self):
+        """0 two-phase, 1 fused (one CTA per SM), 2 fused with in-place deltas (two CTAs per SM)."""
+        return lib().pp_epoch_form(self._h)
 
     def epoch_result_dev(self):
         ptr = _d(); n = ctypes.c_int()

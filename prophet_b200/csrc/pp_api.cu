@@ -55,7 +55,8 @@ struct NetHost {
   std::vector<double> params, mean, scale;
   DevBuf<double> d_mean, d_scale;
   DevBuf<int> d_tf;
-  DevBuf<unsigned char> d_dw_tiles;
+  DevBuf<unsigned char> d_dw_tiles, d_dw_tiles2;
+  bool has_tiles2 = false;
   int tile_atoms = 0;
   NetDev dev;
 };
@@ -92,6 +93,14 @@ struct pp_context {
   DevBuf<int> d_mxyz, d_tag, d_elem, d_atom_struct;
   DevBuf<int> d_rows[PP_MAX_ELEM];
   DevBuf<double> d_partial, d_result, d_stat_partial, d_stat_sums;
+  int epoch_form = -1;                 // kernel form of the last epoch (pp_epoch_form)
+  // two-CTA fused form: saturation flag of the last such epoch (device), its host mirror (pinned) and the event after
+  // the copy; once the host sees a set flag it stays on the one-CTA form for a while instead of paying for both kernels
+  DevBuf<int> d_sat_flag;
+  int* h_sat_flag = nullptr;
+  cudaEvent_t sat_event = nullptr;
+  bool sat_pending = false;
+  int one_cta_epochs_left = 0;
   DevBuf<long long> d_count;
   std::vector<double> h_result;
   // fused single-pass epoch: tiles of whole structures
@@ -164,7 +173,9 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_overflow.release(); c->d_params.release(); c->d_tanh_table.release();
   c->d_struct_atom0.release(); c->d_FtoA.release(); c->d_target.release(); c->d_frac.release(); c->d_G.release();
   c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
-  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release();
+  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_sat_flag.release();
+  if (c->h_sat_flag) { cudaFreeHost(c->h_sat_flag); c->h_sat_flag = nullptr; }
+  if (c->sat_event) { cudaEventDestroy(c->sat_event); c->sat_event = nullptr; }
   c->d_stat_partial.release(); c->d_stat_sums.release(); c->d_count.release();
   c->d_x.release(); c->d_f.release(); c->d_Gmd.release(); c->d_dEdG.release(); c->d_eatom.release();
   c->d_md_elem.release(); c->d_neigh.release(); c->d_neigh_off.release();
@@ -172,7 +183,7 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_cell_start.release(); c->d_scan_sums.release(); c->d_scan_total.release(); c->d_sum_partial.release(); c->d_etotal.release();
   for (int e = 0; e < PP_MAX_ELEM; e++) {
     c->d_rows[e].release(); c->d_md_rows[e].release();
-    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release();
+    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release(); c->nets[e].d_dw_tiles2.release();
   }
   c->d_tile_struct0.release();
   if (c->d_spec) cudaFree(c->d_spec);
@@ -406,6 +417,16 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
     ppk_mlp_num_dw_tiles(n.dev, tiles.data());
     if (n.d_dw_tiles.ensure(tiles.size(), 0, c->stream)) return 1;
     PP_CUDA(cudaMemcpy(n.d_dw_tiles.p, tiles.data(), tiles.size(), cudaMemcpyHostToDevice));
+    // work table of the two-CTA fused training kernel, when this network is eligible for it
+    int n2 = 0;
+    n.has_tiles2 = false;
+    if (ppk_mlp2_table(n.dev, nullptr, &n2) && n2 > 0) {
+      std::vector<unsigned char> t2((size_t)n2 * ppk_mlp_dw_tile_bytes());
+      ppk_mlp2_table(n.dev, t2.data(), &n2);
+      if (n.d_dw_tiles2.ensure(t2.size(), 0, c->stream)) return 1;
+      PP_CUDA(cudaMemcpy(n.d_dw_tiles2.p, t2.data(), t2.size(), cudaMemcpyHostToDevice));
+      n.has_tiles2 = true;
+    }
   }
   c->tiles_dirty = true;
   n.set = true;
@@ -707,7 +728,7 @@ extern "C" int pp_precondition(pp_context* c, int input_precondition)
   if (nets_ready(c)) return 1;
   PP_CUDA(cudaSetDevice(c->device));
   const int NG = c->spec.NG;
-  const int n_cta = 2 * ppk_mlp_max_ctas();
+  const int n_cta = 2 * ppk_mlp_single_ctas();
   cudaStream_t st = c->stream;
   if (c->d_stat_partial.ensure((size_t)n_cta * NG, 0, st) || c->d_stat_sums.ensure(2 * (size_t)NG, 0, st) || c->d_count.ensure(1, 0, st)) return 1;
   for (int e = 0; e < c->spec.n_elem; e++) {
@@ -763,6 +784,7 @@ static MlpArgs mlp_args_train(pp_context* c, int e)
   a.p_off = c->nets[e].p_off;
   a.tanh_table = c->d_tanh_table.p;
   a.dw_tiles = c->nets[e].d_dw_tiles.p;
+  a.dw_tiles2 = c->nets[e].has_tiles2 ? c->nets[e].d_dw_tiles2.p : nullptr;
   a.n_tiles = c->n_fused_tiles;
   a.tile_struct0 = c->d_tile_struct0.p;
   a.struct_atom0 = c->d_struct_atom0.p;
@@ -841,22 +863,44 @@ extern "C" int pp_epoch_device(pp_context* c)
     // one pass: forward, per-structure error and backward in the same kernel; loss terms ride in the partials' tail
     if (tick(c, 1)) return 1;
     MlpArgs a = mlp_args_train(c, 0);
-    if (ppk_mlp_launch(PP_MLP_FUSED, a, c->stream, &c->launches)) return 1;
-    if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_max_ctas(), c->P_total + 3, c->P_total + 3, c->d_result.p, c->stream, &c->launches)) return 1;
+    int n_cta = 0;
+    if (c->d_sat_flag.ensure(1, 0, c->stream)) return 1;
+    if (!c->h_sat_flag) {
+      PP_CUDA(cudaMallocHost((void**)&c->h_sat_flag, sizeof(int)));
+      *c->h_sat_flag = 0;
+      PP_CUDA(cudaEventCreateWithFlags(&c->sat_event, cudaEventDisableTiming));
+    }
+    if (c->sat_pending && cudaEventQuery(c->sat_event) == cudaSuccess) {
+      c->sat_pending = false;
+      if (*c->h_sat_flag) c->one_cta_epochs_left = 64;
+    }
+    const bool one_only = c->one_cta_epochs_left > 0;
+    if (one_only) c->one_cta_epochs_left--;
+    if (ppk_mlp_launch_fused(a, c->d_sat_flag.p, one_only, c->stream, &c->launches, &n_cta)) return 1;
+    c->epoch_form = (n_cta > ppk_mlp_single_ctas()) ? 2 : 1;
+    if (c->epoch_form == 2 && !c->sat_pending) {
+      PP_CUDA(cudaMemcpyAsync(c->h_sat_flag, c->d_sat_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+      PP_CUDA(cudaEventRecord(c->sat_event, c->stream));
+      c->sat_pending = true;
+    }
+    if (ppk_reduce_partials(c->d_partial.p, n_cta, c->P_total + 3, c->P_total + 3, c->d_result.p, c->stream, &c->launches)) return 1;
   } else {
+    c->epoch_form = 0;
     if (forward_all(c)) return 1;
     if (tick(c, 1)) return 1;
     for (int e = 0; e < c->spec.n_elem; e++) {
       MlpArgs a = mlp_args_train(c, e);
       if (ppk_mlp_launch(PP_MLP_TRAIN, a, c->stream, &c->launches)) return 1;
     }
-    if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_max_ctas(), c->P_total + 3, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
+    if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_single_ctas(), c->P_total + 3, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
   }
   if (tick(c, 2)) return 1;
   if (c->comm.allreduce_device(c->d_result.p, c->P_total + 3, c->stream)) return 1;
   if (tick(c, 3)) return 1;
   return 0;
 }
+
+extern "C" int pp_epoch_form(pp_context* c) { return c ? c->epoch_form : -1; }
 
 extern "C" int pp_epoch_result_dev(pp_context* c, double** result_dev, int* n)
 {

@@ -70,6 +70,9 @@ struct MlpArgs {
   int P_total, p_off;
   const double* tanh_table;           // [1001 + 4000]
   const void* dw_tiles;               // device table of weight-gradient tiles (ppk_mlp_num_dw_tiles)
+  const void* dw_tiles2;              // device work table of the two-CTA fused kernel (ppk_mlp2_table), or nullptr
+  int* sat_flag;                      // two-CTA form: set to 1 when a tanh node saturates (1 - |t| < 2^-26), see pp_mlp.cu
+  const int* run_if;                  // one-CTA fused form as the fallback: run only if *run_if != 0 (nullptr: always)
   // fused single-pass epoch (single-element systems, tiles made of whole structures)
   int n_tiles;
   const int* tile_struct0;            // [n_tiles+1] first structure of each tile
@@ -82,10 +85,14 @@ struct MlpArgs {
 
 // returns the number of CTAs the train launch will use (rows of `partial`)
 int ppk_mlp_max_ctas(void);
+int ppk_mlp_single_ctas(void);
 // atoms per tile the kernel will use for this net (0 = does not fit), and its weight-gradient tile table
 int ppk_mlp_tile_atoms(const NetDev& net);
 int ppk_mlp_num_dw_tiles(const NetDev& net, void* host_tiles_out);
 int ppk_mlp_dw_tile_bytes(void);
+// two-CTA fused form: work table (0 = network not eligible) and launch; *n_cta = partial rows written
+int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries);
+int ppk_mlp_launch_fused(const MlpArgs& a, int* sat_flag_dev, bool one_cta_only, cudaStream_t st, long long* launches, int* n_cta);
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
 
 // per-structure energies / errors (Potential.cpp:641-668)

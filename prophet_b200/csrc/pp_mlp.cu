@@ -406,6 +406,13 @@ mlp_kernel(MlpArgs a, MlpPlan p, const __grid_constant__ CUtensorMap tmap)
   const NetDev& net = a.net;
   constexpr bool BACKWARD = (MODE != PP_MLP_FORWARD);
   constexpr bool GRADW = (MODE == PP_MLP_TRAIN || MODE == PP_MLP_FUSED);
+  if (MODE == PP_MLP_FUSED && a.run_if != nullptr) {
+    // fallback launch behind the two-CTA form: nothing to do unless that kernel met a saturated tanh node; when it
+    // runs, its gridDim.x rows of partials replace the 2 * gridDim.x rows written there, so the upper half is zeroed
+    if (*a.run_if == 0) return;
+    double* z = a.partial + (size_t)(gridDim.x + blockIdx.x) * (a.P_total + 3);
+    for (int i = threadIdx.x; i < a.P_total + 3; i += MLP_THREADS) z[i] = 0.0;
+  }
 
   // ---- one-time staging: weights (zero padded), constant columns, transfer ids, input scaling ----------------
   for (int l = 0; l < L; l++) {
@@ -937,7 +944,8 @@ static int sm_count()
   return g_sm_count;
 }
 
-int ppk_mlp_max_ctas(void) { return sm_count(); }
+int ppk_mlp_single_ctas(void) { return sm_count(); }       // CTAs (= partial rows) of the one-CTA-per-SM kernels
+int ppk_mlp_max_ctas(void) { return 2 * sm_count(); }      // rows of the partial-gradient scratch (two-CTA form)
 
 // Largest tile (multiple of 8 atoms, <= 64) whose shared-memory plan fits; 0 if none.
 static int choose_tm(const NetDev& net, MlpPlan& plan, std::vector<DwTile>* tiles)
@@ -966,6 +974,596 @@ int ppk_mlp_num_dw_tiles(const NetDev& net, void* host_tiles_out)
 }
 
 int ppk_mlp_dw_tile_bytes(void) { return (int)sizeof(DwTile); }
+
+// =========================================================================================================
+// Fused training kernel, second form: TWO resident CTAs per SM.
+//
+// The first form keeps activations H_l, derivative/delta buffers D_l and a double-buffered descriptor tile in
+// shared memory (~200 KB), so one CTA owns an SM and its 16 warps move through the phases of a tile in lockstep:
+// while they evaluate transfer functions or the per-structure error the DMMA pipe idles.  For networks whose hidden
+// nodes are all tanh the derivative is a function of the activation (T' = 1 - H^2), so the deltas can overwrite the
+// activations IN PLACE once the products that need the activations are done.  The working set shrinks to
+// X + H_1 .. H_{L-1} + the weights (~100 KB for 50-40-40-1), two CTAs fit on an SM, and one CTA's scalar phases
+// overlap the other's tensor phases.  A warp owns 8 atoms (rows) and ALL columns of every layer, so the forward and
+// delta passes need no inter-warp synchronisation at all; CTA barriers only surround the weight-gradient products,
+// whose K dimension runs over all atoms of the tile.
+//
+// Eligibility (checked on the host, anything else runs the first form): single element, rows = consecutive atoms
+// with an even descriptor count (tensor copy), 1 or 2 hidden layers of tanh nodes no wider than 8*NTW, 64-atom tiles.
+#define MLP2_WARPS 8
+#define MLP2_THREADS (MLP2_WARPS * 32)
+#define MLP2_TM 64
+#define MLP2_SAT_CAP 32        // saturated activations per layer and tile whose exact derivative is kept aside
+#define MLP2_SAT_LIMIT (1.0 - 1.4901161193847656e-08)      // |tanh| beyond 1 - 2^-26: 1 - H^2 is no longer accurate enough
+
+struct Mlp2Plan {
+  int L;
+  int n[PP_MAX_LAYERS + 1];
+  int kp[PP_MAX_LAYERS];              // pitch of layer l's input buffer (l = 0: X) and of W_l
+  int w_off[PP_MAX_LAYERS], w_rows[PP_MAX_LAYERS];
+  int x_off, h_off[PP_MAX_LAYERS];    // h_off[l]: H_l, l = 1 .. L-1 (later delta_l)
+  int mu_off, is_off, exptab_off, cvec_off, erow_off, sttgt_off, red_off, mbar_off;
+  int sattp_off;                      // exact T' of saturated activations: [L-1][MLP2_SAT_CAP] doubles
+  int stint_off_bytes, satint_off_bytes, tab_off_bytes;
+  size_t smem_bytes;
+};
+
+// smallest pitch >= v that keeps 8-row fragment loads free of bank conflicts (pitch mod 16 in {4, 12})
+static int mlp2_pitch(int v)
+{
+  int p = v;
+  while (!((p & 15) == 4 || (p & 15) == 12)) p++;
+  return p;
+}
+
+// Work table of the weight-gradient products: for every hidden-layer matrix l < L-1, two slots per warp.
+static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<DwTile>* table)
+{
+  memset(&p, 0, sizeof(p));
+  p.L = net.n_layers;
+  for (int l = 0; l <= p.L; l++) p.n[l] = net.sizes[l];
+  size_t off = 0;
+  for (int l = 0; l < p.L; l++) {
+    p.kp[l] = mlp2_pitch(p.n[l] + 1);
+    p.w_off[l] = (int)off;
+    p.w_rows[l] = (l == p.L - 1) ? 1 : 8 * NTW;
+    off += (size_t)p.w_rows[l] * p.kp[l];
+  }
+  off = (off + 15) & ~(size_t)15;
+  p.x_off = (int)off; off += (size_t)MLP2_TM * p.kp[0];
+  for (int l = 1; l < p.L; l++) { p.h_off[l] = (int)off; off += (size_t)MLP2_TM * p.kp[l]; }
+  p.mu_off = (int)off; off += p.kp[0];
+  p.is_off = (int)off; off += p.kp[0];
+  p.exptab_off = (int)off; off += 64;
+  p.cvec_off = (int)off; off += MLP2_TM;
+  p.erow_off = (int)off; off += MLP2_TM;
+  p.sttgt_off = (int)off; off += MLP2_TM;
+  p.red_off = (int)off; off += MLP2_WARPS * 64;           // cross-warp sums of the output-node gradient, loss terms
+  p.mbar_off = (int)off; off += 2;
+  p.sattp_off = (int)off; off += (size_t)(p.L - 1) * MLP2_SAT_CAP;
+  size_t bytes = off * sizeof(double);
+  p.stint_off_bytes = (int)bytes;
+  bytes += (size_t)(2 * MLP2_TM + 2) * sizeof(int);
+  p.satint_off_bytes = (int)bytes;                           // counters [L-1], then indices [L-1][MLP2_SAT_CAP]
+  bytes += (size_t)(p.L - 1) * (MLP2_SAT_CAP + 1) * sizeof(int);
+  bytes = (bytes + 15) & ~(size_t)15;
+  p.tab_off_bytes = (int)bytes;
+  std::vector<DwTile> all;
+  for (int l = 0; l < p.L - 1; l++) {
+    std::vector<DwTile> blocks;
+    const int rows = round_up(p.n[l + 1], 8) / 8, cols = round_up(p.n[l] + 1, 8) / 8;
+    for (int mi = 0; mi < rows; mi += 2)
+      for (int ni = 0; ni < cols; ni += 2) {
+        DwTile d;
+        memset(&d, 0, sizeof(d));
+        d.a_off = p.h_off[l + 1] + 8 * mi;
+        d.b_off = (l == 0 ? p.x_off : p.h_off[l]) + 8 * ni;
+        d.dp = p.kp[l + 1];
+        d.kp = p.kp[l];
+        d.layer = l; d.mi = mi; d.ni = ni;
+        d.nm = std::min(2, rows - mi); d.nn = std::min(2, cols - ni);
+        blocks.push_back(d);
+      }
+    std::stable_sort(blocks.begin(), blocks.end(), [](const DwTile& x, const DwTile& y) { return x.nm * x.nn > y.nm * y.nn; });
+    int n_big = 0;
+    for (const DwTile& d : blocks) n_big += (d.nm * d.nn > 2);
+    if (n_big > MLP2_WARPS || (int)blocks.size() > 2 * MLP2_WARPS) return false;
+    std::vector<DwTile> slots(2 * MLP2_WARPS);
+    for (DwTile& d : slots) memset(&d, 0, sizeof(d));
+    int load[MLP2_WARPS] = {0}, smsp[4] = {0, 0, 0, 0};
+    size_t b = 0;
+    for (; b < blocks.size() && b < (size_t)MLP2_WARPS; b++) {
+      slots[2 * b] = blocks[b];
+      load[b] += blocks[b].nm * blocks[b].nn;
+      smsp[b & 3] += blocks[b].nm * blocks[b].nn;
+    }
+    for (; b < blocks.size(); b++) {
+      int best = -1;
+      for (int w = 0; w < MLP2_WARPS; w++) {
+        if (slots[2 * w + 1].nm) continue;
+        if (best < 0 || smsp[w & 3] < smsp[best & 3] || (smsp[w & 3] == smsp[best & 3] && load[w] < load[best])) best = w;
+      }
+      slots[2 * best + 1] = blocks[b];
+      load[best] += blocks[b].nm * blocks[b].nn;
+      smsp[best & 3] += blocks[b].nm * blocks[b].nn;
+    }
+    all.insert(all.end(), slots.begin(), slots.end());
+  }
+  bytes += all.size() * sizeof(DwTile);
+  p.smem_bytes = (bytes + 15) & ~(size_t)15;
+  if (table) *table = all;
+  return true;
+}
+
+// Side list of saturated activations (rare path, kept out of line so that it costs the hot loops no registers)
+__device__ __noinline__ void mlp2_sat_append(int* cnt, int* idx, double* tp, int key, double tprime)
+{
+  const int slot = atomicAdd(cnt, 1);
+  if (slot < MLP2_SAT_CAP) { idx[slot] = key; tp[slot] = tprime; }
+}
+__device__ __noinline__ double mlp2_sat_lookup(const int* cnt, const int* idx, const double* tp, int key, double fallback)
+{
+  const int n = min(*cnt, MLP2_SAT_CAP);
+  for (int i = 0; i < n; i++)
+    if (idx[i] == key) return tp[i];
+  return fallback;
+}
+
+// NTW: n-tiles (8 columns) of the widest hidden layer; NLW: hidden-layer weight matrices (L - 1)
+template <int NTW, int NLW>
+__global__ void __launch_bounds__(MLP2_THREADS, 2)
+mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tmap)
+{
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double* sm = reinterpret_cast<double*>(smem_raw);
+  const DwTile* tab = reinterpret_cast<const DwTile*>(smem_raw + p.tab_off_bytes);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, q = lane & 3;
+  const int L = p.L, NG = p.n[0], kp0 = p.kp[0];
+  const NetDev& net = a.net;
+  constexpr int TM = MLP2_TM;
+
+  // ---- one-time staging ------------------------------------------------------------------------------------------
+  for (int l = 0; l < L; l++) {
+    const int n_in = p.n[l], n_out = p.n[l + 1], kp = p.kp[l];
+    double* Ws = sm + p.w_off[l];
+    const double* src = net.params + net.w_off[l];
+    for (int r = warp; r < p.w_rows[l]; r += MLP2_WARPS)
+      for (int k = lane; k < kp; k += 32) Ws[r * kp + k] = (r < n_out && k <= n_in) ? src[(size_t)r * (n_in + 1) + k] : 0.0;
+    if (l >= 1) {
+      double* Hs = sm + p.h_off[l];       // column n_in is the bias input; the in-place deltas never touch it
+      for (int r = warp; r < TM; r += MLP2_WARPS)
+        for (int k = lane; k < kp; k += 32) Hs[r * kp + k] = (k == n_in) ? 1.0 : 0.0;
+    }
+  }
+  for (int k = tid; k < kp0; k += MLP2_THREADS) {
+    sm[p.mu_off + k] = (k < NG) ? net.mean[k] : 0.0;
+    sm[p.is_off + k] = (k < NG) ? 1.0 / net.scale[k] : 0.0;
+  }
+  for (int i = tid; i < 64; i += MLP2_THREADS) sm[p.exptab_off + i] = exp2((double)i * 0.015625);
+  {
+    const int nwords = NLW * 2 * MLP2_WARPS * (int)(sizeof(DwTile) / sizeof(int));
+    int* dst = reinterpret_cast<int*>(smem_raw + p.tab_off_bytes);
+    const int* srcw = reinterpret_cast<const int*>(a.dw_tiles2);
+    for (int i = tid; i < nwords; i += MLP2_THREADS) dst[i] = srcw[i];
+  }
+  const double* mu = sm + p.mu_off;
+  const double* is = sm + p.is_off;
+  const double* exptab = sm + p.exptab_off;
+  double* cvec = sm + p.cvec_off;
+  double* erow = sm + p.erow_off;
+  double* red = sm + p.red_off;
+  int* st_lo = reinterpret_cast<int*>(smem_raw + p.stint_off_bytes);
+  int* st_tag = st_lo + TM + 1;
+  double* st_tgt = sm + p.sttgt_off;
+  unsigned long long* mbar = reinterpret_cast<unsigned long long*>(sm + p.mbar_off);
+  double* X = sm + p.x_off;
+  // Saturated activations (|H| > MLP2_SAT_LIMIT): T' = 1 - H^2 has lost its relative accuracy there, so the forward pass
+  // puts the exact T' = 4e/(1+e)^2 of up to MLP2_SAT_CAP of them per layer and tile on a side list that the delta
+  // pass consults.  More than that (a dead neuron saturates for every atom) sets the fallback flag instead.
+  int* sat_cnt = reinterpret_cast<int*>(smem_raw + p.satint_off_bytes);     // [NLW], hidden layer l+1 at index l
+  int* sat_idx = sat_cnt + NLW;                                               // [NLW][CAP]: row * 256 + column
+  double* sat_tp = sm + p.sattp_off;                                          // [NLW][CAP]
+  if (tid < NLW) sat_cnt[tid] = 0;
+  auto exact_tprime = [&](int li, int row, int n, double fallback) {
+    return mlp2_sat_lookup(sat_cnt + li, sat_idx + li * MLP2_SAT_CAP, sat_tp + li * MLP2_SAT_CAP, row * 256 + n, fallback);
+  };
+
+  double dW[NLW][6][2];                       // per hidden-layer matrix: slot 0 = tiles 0..3, slot 1 = tiles 4..5
+  double dwout[2] = {0.0, 0.0};               // output node: this warp's rows, parameters lane and lane + 32
+  double sse_w = 0.0, vsse_w = 0.0, nval_w = 0.0;
+  int overflow = 0;                           // the side list of saturated activations ran over in some tile
+#pragma unroll
+  for (int l = 0; l < NLW; l++)
+#pragma unroll
+    for (int t = 0; t < 6; t++) { dW[l][t][0] = 0.0; dW[l][t][1] = 0.0; }
+
+  const int n_tiles = a.n_tiles;
+  struct Geom { int s0, s1, row0, nvalid; };
+  auto tile_geom = [&](int tile) {
+    Geom gm;
+    gm.s0 = gm.s1 = gm.row0 = gm.nvalid = 0;
+    if (tile < n_tiles) {
+      gm.s0 = a.tile_struct0[tile];
+      gm.s1 = a.tile_struct0[tile + 1];
+      const long long r0 = a.struct_atom0[gm.s0];
+      gm.row0 = (int)r0;
+      gm.nvalid = (int)(a.struct_atom0[gm.s1] - r0);
+    }
+    return gm;
+  };
+  // entry `tid` of a tile's structure table, fetched one tile ahead into registers
+  int pf_lo = 0, pf_tag = 0;
+  double pf_tgt = 0.0;
+  auto st_fetch = [&](const Geom& gm) {
+    if (tid <= gm.s1 - gm.s0) {
+      const int sidx = gm.s0 + tid;
+      pf_lo = (int)(a.struct_atom0[sidx] - gm.row0);
+      if (sidx < gm.s1) { pf_tgt = a.target[sidx]; pf_tag = a.tag[sidx]; }
+    }
+  };
+  auto issue_load = [&](const Geom& gm) {
+    if (tid == 0) {
+      mbar_arrive_expect_tx(mbar, (unsigned)TM * (unsigned)kp0 * 8u);
+      tma_load_tile(X, &tmap, gm.row0, mbar);
+    }
+  };
+  if (tid == 0) {
+    mbar_init(mbar, 1);
+    fence_proxy_async();
+  }
+  __syncthreads();
+  Geom g_cur = tile_geom(blockIdx.x), g_nxt = tile_geom(blockIdx.x + gridDim.x);
+  if ((int)blockIdx.x < n_tiles) issue_load(g_cur);
+  st_fetch(g_cur);
+
+  const int rb = 8 * warp;                     // this warp's rows
+  int n_done = 0;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, n_done++) {
+    const int row0 = g_cur.row0, nvalid = g_cur.nvalid;
+    const int s_first = g_cur.s0, s_last = g_cur.s1;
+    const Geom g_nn = tile_geom(tile + 2 * gridDim.x);
+    (void)row0;
+    // structure table of this tile (read after barrier A); then the next tile's entries start their flight
+    if (tid <= s_last - s_first) {
+      st_lo[tid] = pf_lo;
+      if (tid < s_last - s_first) { st_tgt[tid] = pf_tgt; st_tag[tid] = pf_tag; }
+    }
+    st_fetch(g_nxt);
+    mbar_wait(mbar, (unsigned)n_done & 1u);
+
+    // ---- normalise this warp's 8 rows in place (NN.cpp:647-651); column NG is the bias input ---------------------
+    {
+      double* xr = X + (size_t)(rb + g) * kp0;
+#pragma unroll 4
+      for (int c = q; c < NG; c += 4) xr[c] = (xr[c] - mu[c]) * is[c];
+      if (q == 0) xr[NG] = 1.0;
+      __syncwarp();
+    }
+
+    // ---- forward: this warp's rows through every hidden layer, no inter-warp synchronisation -------------------------
+    {
+      const double* wo = sm + p.w_off[L - 1];
+      double yp = 0.0;
+      for (int l = 0; l < L - 1; l++) {
+        const int n_in = p.n[l], n_out = p.n[l + 1];
+        double acc[NTW][2];
+        tile_gemm<false, false, NTW>(acc, l == 0 ? X : sm + p.h_off[l], p.kp[l], sm + p.w_off[l], p.kp[l], warp,
+                                     round_up(n_in + 1, 4), 0, NTW, lane);
+        double* Hn = sm + p.h_off[l + 1] + (size_t)(rb + g) * p.kp[l + 1];
+        double tv[NTW][2];
+        bool sat = false;
+#pragma unroll
+        for (int nt = 0; nt < NTW; nt++) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            double dv;
+            tv[nt][h] = pp_fast_tanh(acc[nt][h], dv, exptab);
+            sat = sat || (fabs(tv[nt][h]) > MLP2_SAT_LIMIT && 8 * nt + 2 * q + h < n_out);
+          }
+        }
+        const bool last = (l == L - 2);
+#pragma unroll
+        for (int nt = 0; nt < NTW; nt++) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            const int n = 8 * nt + 2 * q + h;
+            if (n < n_out) {
+              Hn[n] = tv[nt][h];
+              if (last) yp = fma(tv[nt][h], wo[n], yp);      // output node (linear, NN.cpp:76) folded in
+            }
+          }
+        }
+        if (__any_sync(0xffffffffu, sat)) {
+          // rare: some activation of these rows saturated.  Redo the product (its operands are still in shared memory)
+          // and put the exact derivative of every saturated activation on the layer's side list.
+          double acc2[NTW][2];
+          tile_gemm<false, false, NTW>(acc2, l == 0 ? X : sm + p.h_off[l], p.kp[l], sm + p.w_off[l], p.kp[l], warp,
+                                       round_up(n_in + 1, 4), 0, NTW, lane);
+#pragma unroll 1
+          for (int e = 0; e < 2 * NTW; e++) {
+            const int nt = e >> 1, h = e & 1;
+            const int n = 8 * nt + 2 * q + h;
+            double dv;
+            double v = 0.0;
+#pragma unroll
+            for (int k = 0; k < NTW; k++) v = (k == nt) ? acc2[k][h] : v;
+            const double t = pp_fast_tanh(v, dv, exptab);
+            if (fabs(t) > MLP2_SAT_LIMIT && n < n_out)
+              mlp2_sat_append(sat_cnt + l, sat_idx + l * MLP2_SAT_CAP, sat_tp + l * MLP2_SAT_CAP, (rb + g) * 256 + n, dv);
+          }
+        }
+        __syncwarp();
+      }
+      yp += __shfl_xor_sync(0xffffffffu, yp, 1);
+      yp += __shfl_xor_sync(0xffffffffu, yp, 2);
+      if (q == 0) {
+        const int r = rb + g;
+        erow[r] = (r < nvalid) ? a.out_scale * (yp + wo[p.n[L - 1]]) : 0.0;
+      }
+    }
+    __syncthreads();                                                                   // barrier A: erow, structure table
+
+    // ---- per-structure energy, error and loss terms (Potential.cpp:641-668): the factor c of this warp's own rows --
+    {
+      const int re = rb + 8;
+      const int ns = s_last - s_first;
+      double c_mine = 0.0;                     // lanes 0..7: c of row rb + lane
+      for (int i = 0; i < ns; i++) {
+        const int r_lo = st_lo[i], r_hi = st_lo[i + 1];
+        if (r_hi <= rb) continue;
+        if (r_lo >= re) break;
+        double e = 0.0;
+        for (int r = r_lo + lane; r < r_hi; r += 32) e += erow[r];
+        e = pp_warp_sum(e) + a.out_mean;
+        const double err = e - st_tgt[i];
+        const int tag = st_tag[i];
+        const double c = (tag == 0) ? 2.0 * err * a.out_scale : 0.0;
+        if (r_lo >= rb && r_lo < re) {
+          if (tag == 0) sse_w += err * err;
+          else if (tag == 1) { vsse_w += err * err; nval_w += 1.0; }
+          if (lane == 0) a.E_struct[s_first + i] = e;
+        }
+        const int r = rb + lane;
+        if (lane < 8 && r >= r_lo && r < r_hi) c_mine = c;
+      }
+      if (lane < 8) cvec[rb + lane] = c_mine;
+      __syncwarp();
+    }
+
+    // ---- output-node gradient over this warp's rows, then delta_{L-1} = c w_out (1 - H^2) IN PLACE of H_{L-1} ---------
+    {
+      const int n_h = p.n[L - 1], kph = p.kp[L - 1];
+      double* Hl = sm + p.h_off[L - 1];
+      const double* wo = sm + p.w_off[L - 1];
+#pragma unroll
+      for (int j = 0; j < 2; j++) {
+        const int k = lane + 32 * j;
+        if (k <= n_h) {
+          double s_ = 0.0;
+#pragma unroll
+          for (int r = 0; r < 8; r++) s_ = fma(cvec[rb + r], Hl[(size_t)(rb + r) * kph + k], s_);
+          dwout[j] += s_;
+        }
+      }
+      __syncwarp();
+      double* Hr = Hl + (size_t)(rb + g) * kph;
+      const double c = cvec[rb + g];
+#pragma unroll 4
+      if (sat_cnt[L - 2] == 0) {               // the usual case: no saturated activation anywhere in the tile
+        for (int n = q; n < n_h; n += 4) {
+          const double h = Hr[n];
+          Hr[n] = c * wo[n] * fma(-h, h, 1.0);
+        }
+      } else {
+#pragma unroll 1
+        for (int n = q; n < n_h; n += 4) {
+          const double h = Hr[n];
+          double tp = fma(-h, h, 1.0);
+          if (fabs(h) > MLP2_SAT_LIMIT) tp = exact_tprime(L - 2, rb + g, n, tp);
+          Hr[n] = c * wo[n] * tp;
+        }
+        if (sat_cnt[L - 2] > MLP2_SAT_CAP) overflow = 1;
+      }
+      __syncwarp();
+    }
+
+    // ---- backward: weight gradients dW_l += delta_{l+1}^T [H_l, 1] (all atoms of the tile), deltas in place --------------
+#pragma unroll
+    for (int li = 0; li < NLW; li++) {
+      const int l = NLW - 1 - li;
+      __syncthreads();                                                                 // delta_{l+1} complete in all rows
+      double accb[NTW][2];
+      if (l >= 1)      // (delta_{l+1} W_l) for this warp's rows, kept in registers until the barrier below
+        tile_gemm<true, false, NTW>(accb, sm + p.h_off[l + 1], p.kp[l + 1], sm + p.w_off[l], p.kp[l], warp, round_up(p.n[l + 1], 4), 0,
+                                    NTW, lane);
+      {
+        const DwTile d = tab[(l * MLP2_WARPS + warp) * 2];
+        if (d.nm) {
+          const double* pa = sm + d.a_off + g + (size_t)q * d.dp;
+          const double* pb = sm + d.b_off + g + (size_t)q * d.kp;
+          const int sa = 4 * d.dp, sb = 4 * d.kp;
+          if (d.nm == 2 && d.nn == 2) dw_block<6, 0, 2, 2>(dW[l], pa, pb, sa, sb, TM);
+          else if (d.nn == 2) dw_block<6, 0, 1, 2>(dW[l], pa, pb, sa, sb, TM);
+          else if (d.nm == 2) dw_block<6, 0, 2, 1>(dW[l], pa, pb, sa, sb, TM);
+          else dw_block<6, 0, 1, 1>(dW[l], pa, pb, sa, sb, TM);
+        }
+      }
+      {
+        const DwTile d = tab[(l * MLP2_WARPS + warp) * 2 + 1];
+        if (d.nm) {
+          const double* pa = sm + d.a_off + g + (size_t)q * d.dp;
+          const double* pb = sm + d.b_off + g + (size_t)q * d.kp;
+          const int sa = 4 * d.dp, sb = 4 * d.kp;
+          if (d.nn == 2) dw_block<6, 4, 1, 2>(dW[l], pa, pb, sa, sb, TM);
+          else if (d.nm == 2) dw_block<6, 4, 2, 1>(dW[l], pa, pb, sa, sb, TM);
+          else dw_block<6, 4, 1, 1>(dW[l], pa, pb, sa, sb, TM);
+        }
+      }
+      if (l >= 1) {
+        __syncthreads();                                                               // every product reading H_l is done
+        const int n_l = p.n[l];
+        double* Hr = sm + p.h_off[l] + (size_t)(rb + g) * p.kp[l];
+        if (sat_cnt[l - 1] == 0) {
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * nt + 2 * q + h;
+              if (n < n_l) {
+                const double hv = Hr[n];
+                Hr[n] = accb[nt][h] * fma(-hv, hv, 1.0);
+              }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * nt + 2 * q + h;
+              if (n < n_l) {
+                const double hv = Hr[n];
+                double tp = fma(-hv, hv, 1.0);
+                if (fabs(hv) > MLP2_SAT_LIMIT) tp = exact_tprime(l - 1, rb + g, n, tp);
+                Hr[n] = accb[nt][h] * tp;
+              }
+            }
+          }
+          if (sat_cnt[l - 1] > MLP2_SAT_CAP) overflow = 1;
+        }
+        __syncwarp();
+      }
+    }
+    if (tid < NLW) sat_cnt[tid] = 0;           // the lists' last readers finished before the previous barrier; writers follow the next
+    __syncthreads();                                                                   // X is free: next tile's copy
+    if (tile + (int)gridDim.x < n_tiles) issue_load(g_nxt);
+    g_cur = g_nxt;
+    g_nxt = g_nn;
+  }
+
+  // ---- per-CTA partial gradient and loss terms -> scratch (summed in a fixed order by reduce_partials_kernel) -----------
+  double* out = a.partial + (size_t)blockIdx.x * (a.P_total + 3) + a.p_off;
+#pragma unroll
+  for (int l = 0; l < NLW; l++) {
+#pragma unroll
+    for (int t = 0; t < 6; t++) {
+      const DwTile d = tab[(l * MLP2_WARPS + warp) * 2 + (t >> 2)];
+      const int tt = t & 3;
+      if (tt < d.nm * d.nn) {
+        const int bi = (d.nn == 2) ? (tt >> 1) : tt, bj = (d.nn == 2) ? (tt & 1) : 0;
+        const int neuron = 8 * (d.mi + bi) + g;
+        const int n_in = p.n[l];
+        if (neuron < p.n[l + 1]) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            const int k = 8 * (d.ni + bj) + 2 * q + h;
+            if (k <= n_in) out[net.w_off[l] + (size_t)neuron * (n_in + 1) + k] = dW[l][t][h];
+          }
+        }
+      }
+    }
+  }
+  // Saturated tanh nodes beyond what the side lists hold: without the exact T' the gradient is still correct to 2e-16
+  // absolute, but Rprop looks at SIGNS, and the gradient of a dead neuron is made of such terms only; the flag makes
+  // the one-CTA form (which stores T' = 4e/(1+e)^2 for every node) redo the epoch, see ppk_mlp_launch_fused.
+  if (__syncthreads_or(overflow) && tid == 0 && a.sat_flag != nullptr) *a.sat_flag = 1;
+  red[warp * 64 + lane] = dwout[0];
+  red[warp * 64 + 32 + lane] = dwout[1];
+  __syncthreads();
+  if (tid <= p.n[L - 1]) {
+    double s_ = 0.0;
+    for (int w = 0; w < MLP2_WARPS; w++) s_ += red[w * 64 + tid];
+    out[net.w_off[L - 1] + tid] = s_;
+  }
+  __syncthreads();
+  if (lane == 0) { red[3 * warp] = sse_w; red[3 * warp + 1] = vsse_w; red[3 * warp + 2] = nval_w; }
+  __syncthreads();
+  if (tid < 3) {
+    double s_ = 0.0;
+    for (int w = 0; w < MLP2_WARPS; w++) s_ += red[3 * w + tid];
+    a.partial[(size_t)blockIdx.x * (a.P_total + 3) + a.P_total + tid] = s_;
+  }
+}
+
+// Tries the two-CTA form; returns 0 and sets *n_cta (rows of the partial buffer written) when it was launched,
+// -1 when the network / data layout is not eligible, 1 on error.
+static int mlp2_ntw(const NetDev& net)
+{
+  int mx = 1;
+  for (int l = 1; l < net.n_layers; l++) mx = std::max(mx, net.sizes[l]);
+  const int nt = (mx + 7) / 8;
+  return nt <= 5 ? 5 : nt <= 8 ? 8 : 0;
+}
+static bool mlp2_eligible(const NetDev& net, Mlp2Plan& plan, std::vector<DwTile>* table)
+{
+  const int L = net.n_layers;
+  if (L < 2 || L > 3) return false;
+  for (int l = 1; l < L; l++)
+    if (!((net.tanh_layers >> l) & 1)) return false;
+  if (net.sizes[0] & 1) return false;
+  if (net.sizes[L - 1] + 1 > 64) return false;
+  const int NTW = mlp2_ntw(net);
+  if (!NTW) return false;
+  if (!mlp2_make_plan(net, NTW, plan, table)) return false;
+  if (plan.kp[0] > 256) return false;
+  return plan.smem_bytes <= 113 * 1024;
+}
+int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries)
+{
+  Mlp2Plan plan;
+  std::vector<DwTile> table;
+  *n_entries = 0;
+  if (!mlp2_eligible(net, plan, &table)) return 0;
+  *n_entries = (int)table.size();
+  if (host_out && !table.empty()) memcpy(host_out, table.data(), table.size() * sizeof(DwTile));
+  return 1;
+}
+int ppk_mlp_launch_fused(const MlpArgs& a_in, int* sat_flag_dev, bool one_cta_only, cudaStream_t st, long long* launches, int* n_cta)
+{
+  *n_cta = sm_count();
+  MlpArgs a = a_in;
+  a.sat_flag = nullptr;
+  a.run_if = nullptr;
+  const NetDev& net = a.net;
+  Mlp2Plan plan;
+  MlpPlan plan1;
+  const bool try2 = !one_cta_only && sat_flag_dev != nullptr && a.rows == nullptr && a.dw_tiles2 != nullptr && a.M > 0 &&
+                    encode_tiled() != nullptr && getenv("PP_MLP_ONE_CTA") == nullptr &&
+                    choose_tm(net, plan1, nullptr) == MLP2_TM && mlp2_eligible(net, plan, nullptr);
+  if (!try2) return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
+  CUtensorMap tmap;
+  const cuuint64_t gdim[2] = {(cuuint64_t)net.sizes[0], (cuuint64_t)a.M};
+  const cuuint64_t gstride[1] = {(cuuint64_t)net.sizes[0] * sizeof(double)};
+  const cuuint32_t box[2] = {(cuuint32_t)plan.kp[0], (cuuint32_t)MLP2_TM};
+  const cuuint32_t estr[2] = {1, 1};
+  if (encode_tiled()(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(a.G), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
+  PP_CUDA(cudaMemsetAsync(sat_flag_dev, 0, sizeof(int), st));
+  a.sat_flag = sat_flag_dev;
+  const int grid = 2 * sm_count();
+  const int NTW = mlp2_ntw(net), NLW = net.n_layers - 1;
+#define PP_LAUNCH2(NTW_, NLW_)                                                                                  \
+  {                                                                                                             \
+    auto k = mlp_fused2_kernel<NTW_, NLW_>;                                                                     \
+    PP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes));        \
+    k<<<grid, MLP2_THREADS, plan.smem_bytes, st>>>(a, plan, tmap);                                              \
+  }
+  if (NTW == 5 && NLW == 1) PP_LAUNCH2(5, 1)
+  else if (NTW == 5 && NLW == 2) PP_LAUNCH2(5, 2)
+  else if (NTW == 8 && NLW == 1) PP_LAUNCH2(8, 1)
+  else PP_LAUNCH2(8, 2)
+#undef PP_LAUNCH2
+  (*launches)++;
+  PP_CUDA(cudaGetLastError());
+  *n_cta = grid;
+  // the one-CTA form behind it, predicated on the saturation flag (an empty launch in the normal case)
+  a.sat_flag = nullptr;
+  a.run_if = sat_flag_dev;
+  return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
+}
 
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches)
 {

@@ -93,6 +93,60 @@ def test_epoch_energy_sse_gradient(train_case):
         assert rel_err(ctx.atom_energies(s), c.d["E_atom.%d" % s]) < TOL
 
 
+def test_both_fused_kernel_forms_match_the_reference():
+    """Single-element tanh networks train through the two-CTA kernel with in-place deltas (pp_epoch_form == 2);
+    PP_MLP_ONE_CTA=1 forces the one-CTA form.  Both must reproduce the reference's SSE and gradient, and agree with
+    each other far inside the tolerance (they differ only in summation order and in T' = 1 - H^2 vs 4e/(1+e)^2)."""
+    import os
+    c = TrainCase("si_train")
+    ctx = make_ctx(c)
+    try:
+        add_all(ctx, c)
+        x = c.d["x_before.0"]
+        os.environ.pop("PP_MLP_ONE_CTA", None)
+        r2 = ctx.epoch(x)
+        assert ctx.epoch_form() == 2
+        os.environ["PP_MLP_ONE_CTA"] = "1"
+        try:
+            r1 = ctx.epoch(x)
+            assert ctx.epoch_form() == 1
+        finally:
+            os.environ.pop("PP_MLP_ONE_CTA", None)
+        for r in (r1, r2):
+            assert abs(r["SSE"] - c.d["SSE.0"][0]) <= TOL * abs(c.d["SSE.0"][0])
+            assert rel_err(r["gradient"], c.d["gradient.0"]) < TOL
+        assert rel_err(r1["gradient"], r2["gradient"]) < 1e-12
+    finally:
+        ctx.close()
+
+
+def test_saturated_tanh_nodes_fall_back_to_the_exact_derivative():
+    """The two-CTA form recomputes T' = 1 - H^2, which loses the tiny derivatives of saturated nodes (the whole gradient
+    of a dead neuron, whose SIGN still steers Rprop).  It flags them and the one-CTA form redoes the epoch behind it:
+    with a neuron driven to |x| > 20 the result must be bit-identical to the one-CTA form's."""
+    import os
+    c = TrainCase("si_train")
+    x = c.d["x_before.0"].copy()
+    NG, H1 = c.sizes[0], c.sizes[1]
+    x[3 * (NG + 1) + NG] = 40.0                      # bias of hidden neuron 3 of layer 0: tanh saturates for every atom
+    ctx = make_ctx(c)
+    try:
+        add_all(ctx, c)
+        os.environ.pop("PP_MLP_ONE_CTA", None)
+        r2 = ctx.epoch(x)
+        assert ctx.epoch_form() == 2
+        os.environ["PP_MLP_ONE_CTA"] = "1"
+        try:
+            r1 = ctx.epoch(x)
+        finally:
+            os.environ.pop("PP_MLP_ONE_CTA", None)
+        assert np.array_equal(r1["gradient"], r2["gradient"]) and r1["SSE"] == r2["SSE"]
+        row = r1["gradient"][3 * (NG + 1):4 * (NG + 1)]
+        assert np.all(row != 0.0) and np.abs(row).max() < 1e-12 * np.abs(r1["gradient"]).max()
+    finally:
+        ctx.close()
+
+
 def test_epoch_is_bit_reproducible(train_case):
     c, ctx = train_case
     x = c.d["x_before.0"]
