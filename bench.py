@@ -209,6 +209,10 @@ def run_ours(args):
         bwd = float(np.median(bwd_ms))
         peaks = _fp64_peaks()
         achieved = train_flops_atom * atoms / (bwd * 1e-3) / 1e12
+        form = ctx.epoch_form()
+        kernel_name = {2: "mlp_fused2_kernel (FP64 DMMA: forward, per-structure error, in-place deltas, weight gradients; two CTAs per SM)",
+                       1: "mlp_kernel<FUSED> (FP64 DMMA: forward, per-structure error, backprop, weight gradients; one CTA per SM)"}.get(
+                           form, "mlp_kernel<FORWARD> + mlp_kernel<TRAIN> (FP64 DMMA)")
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -220,10 +224,10 @@ def run_ours(args):
                     "includes": "pp_epoch with pinned host buffers + host Rprop step"},
             "gpu_launches": int(launches_timed),
             "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": "mlp_kernel<TRAIN> (FP64 DMMA: forward recompute + backprop + weight gradients)",
+            "roofline": {"bound": "tensor", "kernel": kernel_name,
                          "achieved": achieved, "peak": peaks["fp64_dmma_tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["fp64_dmma_tflops"],
                          "peak_source": peaks["source"], "algorithmic_flops_per_atom": train_flops_atom, "atoms_per_launch": atoms,
-                         "kernel_ms": bwd, "traffic": _ncu_traffic(n_struct),
+                         "kernel_ms": bwd, "traffic": _ncu_traffic(n_struct, form),
                          "hbm_view": {"algorithmic_bytes_per_atom": 8 * cfg.NG, "achieved_gbs": 8 * cfg.NG * atoms / (bwd * 1e-3) / 1e9,
                                       "peak_gbs": _measured_hbm()}},
             "phases_ms": {"forward": float(np.median(fwd_ms)), "backward_reduce": bwd, "collective": float(np.median(coll_ms))},
@@ -437,12 +441,12 @@ def _torch_nccl_path():
     return "libnccl.so.2"
 
 
-def _ncu_traffic(n_struct):
+def _ncu_traffic(n_struct, form=1):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed ncu capture
     (only valid for the workload it was captured on)."""
     try:
         with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            d = json.load(f).get("mlp_kernel_fused_C2_%d" % n_struct)
+            d = json.load(f).get(("mlp_fused2_kernel_C2_%d" if form == 2 else "mlp_kernel_fused_C2_%d") % n_struct)
         return (d["dram_bytes_read"] + d["dram_bytes_write"]) if d else None
     except Exception:
         return None

@@ -102,7 +102,8 @@ struct pp_context {
   bool sat_pending = false;
   int one_cta_epochs_left = 0;
   DevBuf<long long> d_count;
-  std::vector<double> h_result;
+  double* h_result = nullptr;          // pinned mirror of d_result ([P_total + 3]) and of the parameters ([P_total]) behind it
+  size_t h_result_cap = 0;
   // fused single-pass epoch: tiles of whole structures
   bool tiles_dirty = true, fused_ok = false;
   int n_fused_tiles = 0;
@@ -175,6 +176,7 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
   c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_sat_flag.release();
   if (c->h_sat_flag) { cudaFreeHost(c->h_sat_flag); c->h_sat_flag = nullptr; }
+  if (c->h_result) { cudaFreeHost(c->h_result); c->h_result = nullptr; c->h_result_cap = 0; }
   if (c->sat_event) { cudaEventDestroy(c->sat_event); c->sat_event = nullptr; }
   c->d_stat_partial.release(); c->d_stat_sums.release(); c->d_count.release();
   c->d_x.release(); c->d_f.release(); c->d_Gmd.release(); c->d_dEdG.release(); c->d_eatom.release();
@@ -914,19 +916,29 @@ extern "C" int pp_epoch_result_dev(pp_context* c, double** result_dev, int* n)
 extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out, double* sse, double* vsse, long long* nval)
 {
   if (nets_ready(c)) return 1;
+  // pinned staging: [P_total + 3] results, then [P_total] parameters (a DMA each way whatever the caller's memory is)
+  const size_t need = 2 * (size_t)c->P_total + 3;
+  if (c->h_result_cap < need) {
+    if (c->h_result) cudaFreeHost(c->h_result);
+    c->h_result = nullptr;
+    c->h_result_cap = 0;
+    PP_CUDA(cudaMallocHost((void**)&c->h_result, need * sizeof(double)));
+    c->h_result_cap = need;
+  }
   if (params_in) {
+    double* stage = c->h_result + c->P_total + 3;
     for (int e = 0; e < c->spec.n_elem; e++) {
       NetHost& n = c->nets[e];
       std::copy(params_in + n.p_off, params_in + n.p_off + n.P, n.params.begin());
     }
-    PP_CUDA(cudaMemcpyAsync(c->d_params.p, params_in, c->P_total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    std::copy(params_in, params_in + c->P_total, stage);
+    PP_CUDA(cudaMemcpyAsync(c->d_params.p, stage, c->P_total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   }
   if (pp_epoch_device(c)) return 1;
-  c->h_result.resize((size_t)c->P_total + 3);
-  PP_CUDA(cudaMemcpyAsync(c->h_result.data(), c->d_result.p, c->h_result.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  PP_CUDA(cudaMemcpyAsync(c->h_result, c->d_result.p, ((size_t)c->P_total + 3) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   PP_CUDA(cudaStreamSynchronize(c->stream));
   tock(c, 0, 1, 1); tock(c, 1, 2, 2); tock(c, 2, 3, 3);
-  if (grad_out) std::copy(c->h_result.begin(), c->h_result.begin() + c->P_total, grad_out);
+  if (grad_out) std::copy(c->h_result, c->h_result + c->P_total, grad_out);
   if (sse) *sse = c->h_result[c->P_total];
   if (vsse) *vsse = c->h_result[c->P_total + 1];
   if (nval) *nval = (long long)llround(c->h_result[c->P_total + 2]);
