@@ -97,6 +97,8 @@ struct pp_context {
   // two-CTA fused form: saturation flag of the last such epoch (device), its host mirror (pinned) and the event after
   // the copy; once the host sees a set flag it stays on the one-CTA form for a while instead of paying for both kernels
   DevBuf<int> d_sat_flag;
+  DevBuf<double> d_err_scratch;        // struct_errors_kernel: per-block loss terms
+  DevBuf<unsigned> d_err_ticket;
   int* h_sat_flag = nullptr;
   cudaEvent_t sat_event = nullptr;
   bool sat_pending = false;
@@ -174,7 +176,7 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_overflow.release(); c->d_params.release(); c->d_tanh_table.release();
   c->d_struct_atom0.release(); c->d_FtoA.release(); c->d_target.release(); c->d_frac.release(); c->d_G.release();
   c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
-  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_sat_flag.release();
+  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_sat_flag.release(); c->d_err_scratch.release(); c->d_err_ticket.release();
   if (c->h_sat_flag) { cudaFreeHost(c->h_sat_flag); c->h_sat_flag = nullptr; }
   if (c->h_result) { cudaFreeHost(c->h_result); c->h_result = nullptr; c->h_result_cap = 0; }
   if (c->sat_event) { cudaEventDestroy(c->sat_event); c->sat_event = nullptr; }
@@ -842,6 +844,8 @@ static int forward_all(pp_context* c)
   sa.E_struct = c->d_E_struct.p;
   sa.cstruct = c->d_cstruct.p;
   sa.result_tail = c->d_result.p + c->P_total;
+  sa.scratch = c->d_err_scratch.p;
+  sa.ticket = c->d_err_ticket.p;
   return ppk_struct_errors(sa, c->stream, &c->launches);
 }
 
@@ -850,6 +854,11 @@ static int epoch_buffers(pp_context* c)
   const int n_cta = ppk_mlp_max_ctas();
   if (c->d_partial.ensure((size_t)n_cta * (c->P_total + 3), 0, c->stream)) return 1;
   if (c->d_result.ensure((size_t)c->P_total + 3, 0, c->stream)) return 1;
+  if (c->d_err_scratch.ensure(3 * (size_t)ppk_struct_errors_blocks(std::max(c->n_struct, 1)), 0, c->stream)) return 1;
+  if (!c->d_err_ticket.p) {
+    if (c->d_err_ticket.ensure(1, 0, c->stream)) return 1;
+    PP_CUDA(cudaMemsetAsync(c->d_err_ticket.p, 0, sizeof(unsigned), c->stream));
+  }
   return 0;
 }
 

@@ -106,7 +106,10 @@ struct StructArgs {
   double* E_struct;     // [n_struct]
   double* cstruct;      // [n_struct]
   double* result_tail;  // [3] sse, vsse, nval
+  double* scratch;      // [3 * ppk_struct_errors_blocks(n_struct)] per-block loss terms
+  unsigned* ticket;     // zero before the first launch; the kernel leaves it at zero
 };
+int ppk_struct_errors_blocks(int n_struct);
 int ppk_struct_errors(const StructArgs& a, cudaStream_t st, long long* launches);
 int ppk_reduce_partials(const double* partial, int n_cta, int stride, int ncols, double* out, cudaStream_t st, long long* launches);
 

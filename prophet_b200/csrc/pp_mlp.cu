@@ -1626,41 +1626,59 @@ int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launc
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Per-structure energy, error and loss terms: Potential.cpp:641-668.  One CTA, fixed summation order
-// (deterministic).  cstruct[s] = 2*Err*out_scale for train structures, else 0.
-__global__ void __launch_bounds__(1024) struct_errors_kernel(StructArgs a)
+// Per-structure energy, error and loss terms: Potential.cpp:641-668.  cstruct[s] = 2*Err*out_scale for train
+// structures, else 0.  One warp per structure (lanes stride over its atoms), a block owns a contiguous range of
+// structures, and every sum has a FIXED order -- lanes, then the block's warps, then the blocks by index (added up by
+// whichever block finishes last) -- so SSE is bit-reproducible run to run.
+#define PP_ERR_WARPS 8
+__global__ void __launch_bounds__(PP_ERR_WARPS * 32) struct_errors_kernel(StructArgs a)
 {
-  __shared__ double s_sse[32], s_vsse[32], s_nval[32];
+  __shared__ double s_part[PP_ERR_WARPS][3];
+  __shared__ bool s_last;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per = (a.n_struct + gridDim.x - 1) / gridDim.x;
+  const int s0 = blockIdx.x * per, s1 = min(a.n_struct, s0 + per);
   double sse = 0.0, vsse = 0.0, nval = 0.0;
-  for (int s = threadIdx.x; s < a.n_struct; s += blockDim.x) {
+  for (int s = s0 + warp; s < s1; s += PP_ERR_WARPS) {
+    const long long b = a.struct_atom0[s], e_ = a.struct_atom0[s + 1];
     double e = 0.0;
-    for (long long at = a.struct_atom0[s]; at < a.struct_atom0[s + 1]; at++) e += a.E_atom[at];
-    e += a.out_mean;
-    a.E_struct[s] = e;
-    double err = e - a.target[s];
-    int tag = a.tag[s];
+    for (long long at = b + lane; at < e_; at += 32) e += a.E_atom[at];
+    e = pp_warp_sum(e) + a.out_mean;
+    const double err = e - a.target[s];
+    const int tag = a.tag[s];
     double c = 0.0;
     if (tag == 0) { sse += err * err; c = 2.0 * err * a.out_scale; }
     else if (tag == 1) { vsse += err * err; nval += 1.0; }
-    a.cstruct[s] = c;
+    if (lane == 0) { a.E_struct[s] = e; a.cstruct[s] = c; }
   }
-  sse = pp_warp_sum(sse); vsse = pp_warp_sum(vsse); nval = pp_warp_sum(nval);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (lane == 0) { s_sse[warp] = sse; s_vsse[warp] = vsse; s_nval[warp] = nval; }
+  if (lane == 0) { s_part[warp][0] = sse; s_part[warp][1] = vsse; s_part[warp][2] = nval; }
   __syncthreads();
-  if (warp == 0) {
-    int nw = blockDim.x >> 5;
-    sse = lane < nw ? s_sse[lane] : 0.0;
-    vsse = lane < nw ? s_vsse[lane] : 0.0;
-    nval = lane < nw ? s_nval[lane] : 0.0;
-    sse = pp_warp_sum(sse); vsse = pp_warp_sum(vsse); nval = pp_warp_sum(nval);
-    if (lane == 0) { a.result_tail[0] = sse; a.result_tail[1] = vsse; a.result_tail[2] = nval; }
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int w = 0; w < PP_ERR_WARPS; w++) t += s_part[w][threadIdx.x];
+    a.scratch[3 * blockIdx.x + threadIdx.x] = t;
+    __threadfence();
   }
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (s_last && threadIdx.x < 3) {
+    __threadfence();
+    double t = 0.0;
+    for (unsigned b = 0; b < gridDim.x; b++) t += ((volatile double*)a.scratch)[3 * b + threadIdx.x];
+    a.result_tail[threadIdx.x] = t;
+    if (threadIdx.x == 0) *a.ticket = 0;
+  }
+}
+
+int ppk_struct_errors_blocks(int n_struct)
+{
+  return std::max(1, std::min(2 * sm_count(), (n_struct + 4 * PP_ERR_WARPS - 1) / (4 * PP_ERR_WARPS)));
 }
 
 int ppk_struct_errors(const StructArgs& a, cudaStream_t st, long long* launches)
 {
-  struct_errors_kernel<<<1, 1024, 0, st>>>(a);
+  struct_errors_kernel<<<ppk_struct_errors_blocks(a.n_struct), PP_ERR_WARPS * 32, 0, st>>>(a);
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   return 0;
