@@ -181,15 +181,12 @@ def run_ours(args):
         fwd_ms.append(ctx.phase_ms(1)); bwd_ms.append(ctx.phase_ms(2)); coll_ms.append(ctx.phase_ms(3))
     # ---- e2e: host buffers through pp_epoch, host->device params and device->host results every step ---------
     opt = _host_optimizer(net["params"], int(0.95 * n_struct * world))
-    for _ in range(args.warmup):
-        ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
+    # the loop itself is the host layer's C++ training loop (what `PROPhet_b200 -train` runs): pp_epoch with HOST
+    # buffers, then Optimizer::update_network + Rprop, every step
+    opt.impl.train_loop(ctx.handle, x_pin.data_ptr(), g_pin.data_ptr(), args.warmup)
     barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        sse, vsse, nval = ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
-        opt.step(x_pin, g_pin, sse)
+    e2e_s, _ = opt.impl.train_loop(ctx.handle, x_pin.data_ptr(), g_pin.data_ptr(), args.steps)
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
 
     times = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
@@ -221,7 +218,7 @@ def run_ours(args):
                                    % n_struct, "structures_total": total_struct, "parallelism": "dp%d" % world,
                        "l2": "inputs (%.0f MB FP64 descriptors per GPU) larger than L2, no flush" % (atoms * cfg.NG * 8 / 1e6)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * P, "d2h_bytes_per_step": 8 * (P + 3),
-                    "includes": "pp_epoch with pinned host buffers + host Rprop step"},
+                    "includes": "the host layer's C++ training loop: pp_epoch with pinned host buffers + Optimizer::update_network (Rprop) per step"},
             "gpu_launches": int(launches_timed),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": kernel_name,

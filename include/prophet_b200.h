@@ -109,7 +109,7 @@ int pp_epoch_device(pp_context* ctx);
 int pp_epoch_result_dev(pp_context* ctx, double** result_dev, int* n);
 /* Diagnostic: which kernel form the last epoch ran.  0 = two launches per element (forward, then backward: any
  * system), 1 = single-pass fused kernel, one CTA per SM, 2 = single-pass fused kernel with in-place deltas, two
- * CTAs per SM (single element, tanh hidden nodes).  -1 before the first epoch.  The environment variable
+ * CTAs per SM (single element, tanh hidden nodes; same arithmetic, different summation order).  -1 before the first epoch.  The environment variable
  * PP_MLP_ONE_CTA=1 keeps form 2 from being chosen.  No reference counterpart. */
 int pp_epoch_form(pp_context* ctx);
 /* Potential::evaluate (Potential.cpp:515-551): E_out[n_struct] = sum_atoms E_i + out_mean (every tag) */

@@ -91,6 +91,11 @@ class Context:
         _check(lib().pp_create(ctypes.c_int(device), ctypes.c_int(fp_mode), ctypes.byref(self._h)))
         self.n_elem = 0
 
+    @property
+    def handle(self):
+        """the pp_context* (for the host layer's C++ entry points that take a context)"""
+        return self._h
+
     def close(self):
         if self._h:
             lib().pp_destroy(self._h)

@@ -66,6 +66,7 @@ struct pp_context {
   cudaStream_t stream = nullptr;
   long long launches = 0;
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  bool epoch_phases_pending = false;   // pp_epoch finished: events 0..3 hold its phases, read out on demand (pp_last_phase_ms)
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 
   bool spec_set = false;
@@ -94,15 +95,9 @@ struct pp_context {
   DevBuf<int> d_rows[PP_MAX_ELEM];
   DevBuf<double> d_partial, d_result, d_stat_partial, d_stat_sums;
   int epoch_form = -1;                 // kernel form of the last epoch (pp_epoch_form)
-  // two-CTA fused form: saturation flag of the last such epoch (device), its host mirror (pinned) and the event after
-  // the copy; once the host sees a set flag it stays on the one-CTA form for a while instead of paying for both kernels
-  DevBuf<int> d_sat_flag;
   DevBuf<double> d_err_scratch;        // struct_errors_kernel: per-block loss terms
+  DevBuf<double> d_scratch2;           // mlp_fused2_kernel: derivative scratch (stays in L2)
   DevBuf<unsigned> d_err_ticket;
-  int* h_sat_flag = nullptr;
-  cudaEvent_t sat_event = nullptr;
-  bool sat_pending = false;
-  int one_cta_epochs_left = 0;
   DevBuf<long long> d_count;
   double* h_result = nullptr;          // pinned mirror of d_result ([P_total + 3]) and of the parameters ([P_total]) behind it
   size_t h_result_cap = 0;
@@ -131,7 +126,12 @@ struct pp_context {
   PPComm comm;
 };
 
-static int tick(pp_context* c, int i) { PP_CUDA(cudaEventRecord(c->ev[i], c->stream)); return 0; }
+static int tick(pp_context* c, int i)
+{
+  if (i == 0) c->epoch_phases_pending = false;      // a new timed operation re-records the events
+  PP_CUDA(cudaEventRecord(c->ev[i], c->stream));
+  return 0;
+}
 static int tock(pp_context* c, int i0, int i1, int which)
 {
   PP_CUDA(cudaEventSynchronize(c->ev[i1]));
@@ -176,10 +176,9 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_overflow.release(); c->d_params.release(); c->d_tanh_table.release();
   c->d_struct_atom0.release(); c->d_FtoA.release(); c->d_target.release(); c->d_frac.release(); c->d_G.release();
   c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
-  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_sat_flag.release(); c->d_err_scratch.release(); c->d_err_ticket.release();
-  if (c->h_sat_flag) { cudaFreeHost(c->h_sat_flag); c->h_sat_flag = nullptr; }
+  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_err_scratch.release(); c->d_scratch2.release(); c->d_err_ticket.release();
   if (c->h_result) { cudaFreeHost(c->h_result); c->h_result = nullptr; c->h_result_cap = 0; }
-  if (c->sat_event) { cudaEventDestroy(c->sat_event); c->sat_event = nullptr; }
+
   c->d_stat_partial.release(); c->d_stat_sums.release(); c->d_count.release();
   c->d_x.release(); c->d_f.release(); c->d_Gmd.release(); c->d_dEdG.release(); c->d_eatom.release();
   c->d_md_elem.release(); c->d_neigh.release(); c->d_neigh_off.release();
@@ -197,7 +196,15 @@ extern "C" void pp_destroy(pp_context* c)
 }
 
 extern "C" long long pp_kernel_launches(pp_context* c) { return c ? c->launches : 0; }
-extern "C" double pp_last_phase_ms(pp_context* c, int which) { return (c && which >= 0 && which < 8) ? c->phase_ms[which] : 0.0; }
+extern "C" double pp_last_phase_ms(pp_context* c, int which)
+{
+  if (!c || which < 0 || which >= 8) return 0.0;
+  if (c->epoch_phases_pending) {       // the epoch's events are only turned into times when somebody asks
+    c->epoch_phases_pending = false;
+    tock(c, 0, 1, 1); tock(c, 1, 2, 2); tock(c, 2, 3, 3);
+  }
+  return c->phase_ms[which];
+}
 extern "C" void* pp_stream(pp_context* c) { return c ? (void*)c->stream : nullptr; }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -789,6 +796,7 @@ static MlpArgs mlp_args_train(pp_context* c, int e)
   a.tanh_table = c->d_tanh_table.p;
   a.dw_tiles = c->nets[e].d_dw_tiles.p;
   a.dw_tiles2 = c->nets[e].has_tiles2 ? c->nets[e].d_dw_tiles2.p : nullptr;
+  a.scratch2 = c->nets[e].has_tiles2 ? c->d_scratch2.p : nullptr;
   a.n_tiles = c->n_fused_tiles;
   a.tile_struct0 = c->d_tile_struct0.p;
   a.struct_atom0 = c->d_struct_atom0.p;
@@ -855,6 +863,9 @@ static int epoch_buffers(pp_context* c)
   if (c->d_partial.ensure((size_t)n_cta * (c->P_total + 3), 0, c->stream)) return 1;
   if (c->d_result.ensure((size_t)c->P_total + 3, 0, c->stream)) return 1;
   if (c->d_err_scratch.ensure(3 * (size_t)ppk_struct_errors_blocks(std::max(c->n_struct, 1)), 0, c->stream)) return 1;
+  if (c->spec.n_elem == 1 && c->nets[0].has_tiles2 &&
+      c->d_scratch2.ensure(std::max<size_t>(ppk_mlp2_scratch_doubles(c->nets[0].dev), 1), 0, c->stream))
+    return 1;
   if (!c->d_err_ticket.p) {
     if (c->d_err_ticket.ensure(1, 0, c->stream)) return 1;
     PP_CUDA(cudaMemsetAsync(c->d_err_ticket.p, 0, sizeof(unsigned), c->stream));
@@ -875,25 +886,8 @@ extern "C" int pp_epoch_device(pp_context* c)
     if (tick(c, 1)) return 1;
     MlpArgs a = mlp_args_train(c, 0);
     int n_cta = 0;
-    if (c->d_sat_flag.ensure(1, 0, c->stream)) return 1;
-    if (!c->h_sat_flag) {
-      PP_CUDA(cudaMallocHost((void**)&c->h_sat_flag, sizeof(int)));
-      *c->h_sat_flag = 0;
-      PP_CUDA(cudaEventCreateWithFlags(&c->sat_event, cudaEventDisableTiming));
-    }
-    if (c->sat_pending && cudaEventQuery(c->sat_event) == cudaSuccess) {
-      c->sat_pending = false;
-      if (*c->h_sat_flag) c->one_cta_epochs_left = 64;
-    }
-    const bool one_only = c->one_cta_epochs_left > 0;
-    if (one_only) c->one_cta_epochs_left--;
-    if (ppk_mlp_launch_fused(a, c->d_sat_flag.p, one_only, c->stream, &c->launches, &n_cta)) return 1;
+    if (ppk_mlp_launch_fused(a, c->stream, &c->launches, &n_cta)) return 1;
     c->epoch_form = (n_cta > ppk_mlp_single_ctas()) ? 2 : 1;
-    if (c->epoch_form == 2 && !c->sat_pending) {
-      PP_CUDA(cudaMemcpyAsync(c->h_sat_flag, c->d_sat_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-      PP_CUDA(cudaEventRecord(c->sat_event, c->stream));
-      c->sat_pending = true;
-    }
     if (ppk_reduce_partials(c->d_partial.p, n_cta, c->P_total + 3, c->P_total + 3, c->d_result.p, c->stream, &c->launches)) return 1;
   } else {
     c->epoch_form = 0;
@@ -922,8 +916,18 @@ extern "C" int pp_epoch_result_dev(pp_context* c, double** result_dev, int* n)
   return 0;
 }
 
+static double now_us()
+{
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+static double g_trace[4] = {0, 0, 0, 0};
+static long g_trace_n = 0;
+
 extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out, double* sse, double* vsse, long long* nval)
 {
+  const double t0 = now_us();
   if (nets_ready(c)) return 1;
   // pinned staging: [P_total + 3] results, then [P_total] parameters (a DMA each way whatever the caller's memory is)
   const size_t need = 2 * (size_t)c->P_total + 3;
@@ -945,8 +949,17 @@ extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out
   }
   if (pp_epoch_device(c)) return 1;
   PP_CUDA(cudaMemcpyAsync(c->h_result, c->d_result.p, ((size_t)c->P_total + 3) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  const double t1 = now_us();
   PP_CUDA(cudaStreamSynchronize(c->stream));
-  tock(c, 0, 1, 1); tock(c, 1, 2, 2); tock(c, 2, 3, 3);
+  const double t2 = now_us();
+  c->epoch_phases_pending = true;
+  const double t3 = now_us();
+  if (getenv("PP_EPOCH_TRACE")) {
+    g_trace[0] += t1 - t0; g_trace[1] += t2 - t1; g_trace[2] += t3 - t2; g_trace_n++;
+    if (g_trace_n % 20 == 0)
+      fprintf(stderr, "pp_epoch trace: enqueue %.1f us, wait %.1f us, events %.1f us (mean of %ld)\n", g_trace[0] / g_trace_n,
+              g_trace[1] / g_trace_n, g_trace[2] / g_trace_n, g_trace_n);
+  }
   if (grad_out) std::copy(c->h_result, c->h_result + c->P_total, grad_out);
   if (sse) *sse = c->h_result[c->P_total];
   if (vsse) *vsse = c->h_result[c->P_total + 1];

@@ -71,8 +71,7 @@ struct MlpArgs {
   const double* tanh_table;           // [1001 + 4000]
   const void* dw_tiles;               // device table of weight-gradient tiles (ppk_mlp_num_dw_tiles)
   const void* dw_tiles2;              // device work table of the two-CTA fused kernel (ppk_mlp2_table), or nullptr
-  int* sat_flag;                      // two-CTA form: set to 1 when a tanh node saturates (1 - |t| < 2^-26), see pp_mlp.cu
-  const int* run_if;                  // one-CTA fused form as the fallback: run only if *run_if != 0 (nullptr: always)
+  double* scratch2;                   // two-CTA form: derivative scratch, ppk_mlp2_scratch_doubles(net) doubles
   // fused single-pass epoch (single-element systems, tiles made of whole structures)
   int n_tiles;
   const int* tile_struct0;            // [n_tiles+1] first structure of each tile
@@ -92,7 +91,8 @@ int ppk_mlp_num_dw_tiles(const NetDev& net, void* host_tiles_out);
 int ppk_mlp_dw_tile_bytes(void);
 // two-CTA fused form: work table (0 = network not eligible) and launch; *n_cta = partial rows written
 int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries);
-int ppk_mlp_launch_fused(const MlpArgs& a, int* sat_flag_dev, bool one_cta_only, cudaStream_t st, long long* launches, int* n_cta);
+size_t ppk_mlp2_scratch_doubles(const NetDev& net);
+int ppk_mlp_launch_fused(const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta);
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
 
 // per-structure energies / errors (Potential.cpp:641-668)

@@ -406,13 +406,6 @@ mlp_kernel(MlpArgs a, MlpPlan p, const __grid_constant__ CUtensorMap tmap)
   const NetDev& net = a.net;
   constexpr bool BACKWARD = (MODE != PP_MLP_FORWARD);
   constexpr bool GRADW = (MODE == PP_MLP_TRAIN || MODE == PP_MLP_FUSED);
-  if (MODE == PP_MLP_FUSED && a.run_if != nullptr) {
-    // fallback launch behind the two-CTA form: nothing to do unless that kernel met a saturated tanh node; when it
-    // runs, its gridDim.x rows of partials replace the 2 * gridDim.x rows written there, so the upper half is zeroed
-    if (*a.run_if == 0) return;
-    double* z = a.partial + (size_t)(gridDim.x + blockIdx.x) * (a.P_total + 3);
-    for (int i = threadIdx.x; i < a.P_total + 3; i += MLP_THREADS) z[i] = 0.0;
-  }
 
   // ---- one-time staging: weights (zero padded), constant columns, transfer ids, input scaling ----------------
   for (int l = 0; l < L; l++) {
@@ -932,6 +925,32 @@ static EncodeTiledFn encode_tiled()
   return fn;
 }
 
+// Tensor map of an [atoms][NG] FP64 array with box (box_cols x box_rows); the last few are cached, since an epoch loop
+// asks for the same one every time (encoding costs a few microseconds of host time in front of the launch).
+static bool tiled_map(const double* G, int NG, long long atoms, int box_cols, int box_rows, CUtensorMap* out)
+{
+  struct Entry { const double* G; int NG, bc, br; long long atoms; CUtensorMap map; bool used; };
+  static Entry cache[8];
+  static int next = 0;
+  for (int i = 0; i < 8; i++) {
+    const Entry& e = cache[i];
+    if (e.used && e.G == G && e.NG == NG && e.atoms == atoms && e.bc == box_cols && e.br == box_rows) { *out = e.map; return true; }
+  }
+  if (encode_tiled() == nullptr) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)NG, (cuuint64_t)atoms};
+  const cuuint64_t gstride[1] = {(cuuint64_t)NG * sizeof(double)};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  if (encode_tiled()(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(G), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  Entry& e = cache[next];
+  next = (next + 1) & 7;
+  e.G = G; e.NG = NG; e.atoms = atoms; e.bc = box_cols; e.br = box_rows; e.map = *out; e.used = true;
+  return true;
+}
+
 static int g_sm_count = 0;
 static int sm_count()
 {
@@ -980,8 +999,8 @@ int ppk_mlp_dw_tile_bytes(void) { return (int)sizeof(DwTile); }
 //
 // The first form keeps activations H_l, derivative/delta buffers D_l and a double-buffered descriptor tile in
 // shared memory (~200 KB), so one CTA owns an SM and its 16 warps move through the phases of a tile in lockstep:
-// while they evaluate transfer functions or the per-structure error the DMMA pipe idles.  For networks whose hidden
-// nodes are all tanh the derivative is a function of the activation (T' = 1 - H^2), so the deltas can overwrite the
+// while they evaluate transfer functions or the per-structure error the DMMA pipe idles.  Here the derivatives T' wait
+// in a per-CTA scratch in global memory (L2 resident, see `dsc` in the kernel) and the deltas overwrite the
 // activations IN PLACE once the products that need the activations are done.  The working set shrinks to
 // X + H_1 .. H_{L-1} + the weights (~100 KB for 50-40-40-1), two CTAs fit on an SM, and one CTA's scalar phases
 // overlap the other's tensor phases.  A warp owns 8 atoms (rows) and ALL columns of every layer, so the forward and
@@ -993,8 +1012,6 @@ int ppk_mlp_dw_tile_bytes(void) { return (int)sizeof(DwTile); }
 #define MLP2_WARPS 8
 #define MLP2_THREADS (MLP2_WARPS * 32)
 #define MLP2_TM 64
-#define MLP2_SAT_CAP 32        // saturated activations per layer and tile whose exact derivative is kept aside
-#define MLP2_SAT_LIMIT (1.0 - 1.4901161193847656e-08)      // |tanh| beyond 1 - 2^-26: 1 - H^2 is no longer accurate enough
 
 struct Mlp2Plan {
   int L;
@@ -1003,8 +1020,7 @@ struct Mlp2Plan {
   int w_off[PP_MAX_LAYERS], w_rows[PP_MAX_LAYERS];
   int x_off, h_off[PP_MAX_LAYERS];    // h_off[l]: H_l, l = 1 .. L-1 (later delta_l)
   int mu_off, is_off, exptab_off, cvec_off, erow_off, sttgt_off, red_off, mbar_off;
-  int sattp_off;                      // exact T' of saturated activations: [L-1][MLP2_SAT_CAP] doubles
-  int stint_off_bytes, satint_off_bytes, tab_off_bytes;
+  int stint_off_bytes, tab_off_bytes;
   size_t smem_bytes;
 };
 
@@ -1040,12 +1056,9 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
   p.sttgt_off = (int)off; off += MLP2_TM;
   p.red_off = (int)off; off += MLP2_WARPS * 64;           // cross-warp sums of the output-node gradient, loss terms
   p.mbar_off = (int)off; off += 2;
-  p.sattp_off = (int)off; off += (size_t)(p.L - 1) * MLP2_SAT_CAP;
   size_t bytes = off * sizeof(double);
   p.stint_off_bytes = (int)bytes;
   bytes += (size_t)(2 * MLP2_TM + 2) * sizeof(int);
-  p.satint_off_bytes = (int)bytes;                           // counters [L-1], then indices [L-1][MLP2_SAT_CAP]
-  bytes += (size_t)(p.L - 1) * (MLP2_SAT_CAP + 1) * sizeof(int);
   bytes = (bytes + 15) & ~(size_t)15;
   p.tab_off_bytes = (int)bytes;
   std::vector<DwTile> all;
@@ -1093,20 +1106,6 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
   p.smem_bytes = (bytes + 15) & ~(size_t)15;
   if (table) *table = all;
   return true;
-}
-
-// Side list of saturated activations (rare path, kept out of line so that it costs the hot loops no registers)
-__device__ __noinline__ void mlp2_sat_append(int* cnt, int* idx, double* tp, int key, double tprime)
-{
-  const int slot = atomicAdd(cnt, 1);
-  if (slot < MLP2_SAT_CAP) { idx[slot] = key; tp[slot] = tprime; }
-}
-__device__ __noinline__ double mlp2_sat_lookup(const int* cnt, const int* idx, const double* tp, int key, double fallback)
-{
-  const int n = min(*cnt, MLP2_SAT_CAP);
-  for (int i = 0; i < n; i++)
-    if (idx[i] == key) return tp[i];
-  return fallback;
 }
 
 // NTW: n-tiles (8 columns) of the widest hidden layer; NLW: hidden-layer weight matrices (L - 1)
@@ -1158,21 +1157,15 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   double* st_tgt = sm + p.sttgt_off;
   unsigned long long* mbar = reinterpret_cast<unsigned long long*>(sm + p.mbar_off);
   double* X = sm + p.x_off;
-  // Saturated activations (|H| > MLP2_SAT_LIMIT): T' = 1 - H^2 has lost its relative accuracy there, so the forward pass
-  // puts the exact T' = 4e/(1+e)^2 of up to MLP2_SAT_CAP of them per layer and tile on a side list that the delta
-  // pass consults.  More than that (a dead neuron saturates for every atom) sets the fallback flag instead.
-  int* sat_cnt = reinterpret_cast<int*>(smem_raw + p.satint_off_bytes);     // [NLW], hidden layer l+1 at index l
-  int* sat_idx = sat_cnt + NLW;                                               // [NLW][CAP]: row * 256 + column
-  double* sat_tp = sm + p.sattp_off;                                          // [NLW][CAP]
-  if (tid < NLW) sat_cnt[tid] = 0;
-  auto exact_tprime = [&](int li, int row, int n, double fallback) {
-    return mlp2_sat_lookup(sat_cnt + li, sat_idx + li * MLP2_SAT_CAP, sat_tp + li * MLP2_SAT_CAP, row * 256 + n, fallback);
-  };
-
+  // The derivative T' of every activation is parked in a per-CTA scratch in global memory (2 * NTW * NLW doubles per
+  // thread, element-major so that a warp's accesses are contiguous; 20 KB per layer and CTA, which never leaves L2) and
+  // read back by the SAME thread when it forms that activation's delta -- no synchronisation involved.  T' could be
+  // recomputed as 1 - H^2, but that is 0 or 2e-16 for a saturated node: harmless for the 1e-10 tolerance, not for
+  // Rprop, which follows the SIGN of a dead neuron's gradient, a sum of nothing but such terms.
+  double* dsc = a.scratch2 + (size_t)blockIdx.x * (NLW * NTW * 2 * MLP2_THREADS);
   double dW[NLW][6][2];                       // per hidden-layer matrix: slot 0 = tiles 0..3, slot 1 = tiles 4..5
   double dwout[2] = {0.0, 0.0};               // output node: this warp's rows, parameters lane and lane + 32
   double sse_w = 0.0, vsse_w = 0.0, nval_w = 0.0;
-  int overflow = 0;                           // the side list of saturated activations ran over in some tile
 #pragma unroll
   for (int l = 0; l < NLW; l++)
 #pragma unroll
@@ -1252,14 +1245,13 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
                                      round_up(n_in + 1, 4), 0, NTW, lane);
         double* Hn = sm + p.h_off[l + 1] + (size_t)(rb + g) * p.kp[l + 1];
         double tv[NTW][2];
-        bool sat = false;
 #pragma unroll
         for (int nt = 0; nt < NTW; nt++) {
 #pragma unroll
           for (int h = 0; h < 2; h++) {
             double dv;
             tv[nt][h] = pp_fast_tanh(acc[nt][h], dv, exptab);
-            sat = sat || (fabs(tv[nt][h]) > MLP2_SAT_LIMIT && 8 * nt + 2 * q + h < n_out);
+            dsc[(size_t)((l * NTW + nt) * 2 + h) * MLP2_THREADS + tid] = dv;      // T' of this activation, see `dsc`
           }
         }
         const bool last = (l == L - 2);
@@ -1272,25 +1264,6 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
               Hn[n] = tv[nt][h];
               if (last) yp = fma(tv[nt][h], wo[n], yp);      // output node (linear, NN.cpp:76) folded in
             }
-          }
-        }
-        if (__any_sync(0xffffffffu, sat)) {
-          // rare: some activation of these rows saturated.  Redo the product (its operands are still in shared memory)
-          // and put the exact derivative of every saturated activation on the layer's side list.
-          double acc2[NTW][2];
-          tile_gemm<false, false, NTW>(acc2, l == 0 ? X : sm + p.h_off[l], p.kp[l], sm + p.w_off[l], p.kp[l], warp,
-                                       round_up(n_in + 1, 4), 0, NTW, lane);
-#pragma unroll 1
-          for (int e = 0; e < 2 * NTW; e++) {
-            const int nt = e >> 1, h = e & 1;
-            const int n = 8 * nt + 2 * q + h;
-            double dv;
-            double v = 0.0;
-#pragma unroll
-            for (int k = 0; k < NTW; k++) v = (k == nt) ? acc2[k][h] : v;
-            const double t = pp_fast_tanh(v, dv, exptab);
-            if (fabs(t) > MLP2_SAT_LIMIT && n < n_out)
-              mlp2_sat_append(sat_cnt + l, sat_idx + l * MLP2_SAT_CAP, sat_tp + l * MLP2_SAT_CAP, (rb + g) * 256 + n, dv);
           }
         }
         __syncwarp();
@@ -1331,7 +1304,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       __syncwarp();
     }
 
-    // ---- output-node gradient over this warp's rows, then delta_{L-1} = c w_out (1 - H^2) IN PLACE of H_{L-1} ---------
+    // ---- output-node gradient over this warp's rows, then delta_{L-1} = c w_out T' IN PLACE of H_{L-1} ---------------
     {
       const int n_h = p.n[L - 1], kph = p.kp[L - 1];
       double* Hl = sm + p.h_off[L - 1];
@@ -1349,21 +1322,14 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       __syncwarp();
       double* Hr = Hl + (size_t)(rb + g) * kph;
       const double c = cvec[rb + g];
-#pragma unroll 4
-      if (sat_cnt[L - 2] == 0) {               // the usual case: no saturated activation anywhere in the tile
-        for (int n = q; n < n_h; n += 4) {
-          const double h = Hr[n];
-          Hr[n] = c * wo[n] * fma(-h, h, 1.0);
+#pragma unroll
+      for (int nt = 0; nt < NTW; nt++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int n = 8 * nt + 2 * q + h;
+          const double tp = dsc[(size_t)(((L - 2) * NTW + nt) * 2 + h) * MLP2_THREADS + tid];
+          if (n < n_h) Hr[n] = c * wo[n] * tp;
         }
-      } else {
-#pragma unroll 1
-        for (int n = q; n < n_h; n += 4) {
-          const double h = Hr[n];
-          double tp = fma(-h, h, 1.0);
-          if (fabs(h) > MLP2_SAT_LIMIT) tp = exact_tprime(L - 2, rb + g, n, tp);
-          Hr[n] = c * wo[n] * tp;
-        }
-        if (sat_cnt[L - 2] > MLP2_SAT_CAP) overflow = 1;
       }
       __syncwarp();
     }
@@ -1404,38 +1370,18 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         __syncthreads();                                                               // every product reading H_l is done
         const int n_l = p.n[l];
         double* Hr = sm + p.h_off[l] + (size_t)(rb + g) * p.kp[l];
-        if (sat_cnt[l - 1] == 0) {
 #pragma unroll
-          for (int nt = 0; nt < NTW; nt++) {
+        for (int nt = 0; nt < NTW; nt++) {
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-              const int n = 8 * nt + 2 * q + h;
-              if (n < n_l) {
-                const double hv = Hr[n];
-                Hr[n] = accb[nt][h] * fma(-hv, hv, 1.0);
-              }
-            }
+          for (int h = 0; h < 2; h++) {
+            const int n = 8 * nt + 2 * q + h;
+            const double tp = dsc[(size_t)(((l - 1) * NTW + nt) * 2 + h) * MLP2_THREADS + tid];
+            if (n < n_l) Hr[n] = accb[nt][h] * tp;
           }
-        } else {
-#pragma unroll
-          for (int nt = 0; nt < NTW; nt++) {
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-              const int n = 8 * nt + 2 * q + h;
-              if (n < n_l) {
-                const double hv = Hr[n];
-                double tp = fma(-hv, hv, 1.0);
-                if (fabs(hv) > MLP2_SAT_LIMIT) tp = exact_tprime(l - 1, rb + g, n, tp);
-                Hr[n] = accb[nt][h] * tp;
-              }
-            }
-          }
-          if (sat_cnt[l - 1] > MLP2_SAT_CAP) overflow = 1;
         }
         __syncwarp();
       }
     }
-    if (tid < NLW) sat_cnt[tid] = 0;           // the lists' last readers finished before the previous barrier; writers follow the next
     __syncthreads();                                                                   // X is free: next tile's copy
     if (tile + (int)gridDim.x < n_tiles) issue_load(g_nxt);
     g_cur = g_nxt;
@@ -1464,10 +1410,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       }
     }
   }
-  // Saturated tanh nodes beyond what the side lists hold: without the exact T' the gradient is still correct to 2e-16
-  // absolute, but Rprop looks at SIGNS, and the gradient of a dead neuron is made of such terms only; the flag makes
-  // the one-CTA form (which stores T' = 4e/(1+e)^2 for every node) redo the epoch, see ppk_mlp_launch_fused.
-  if (__syncthreads_or(overflow) && tid == 0 && a.sat_flag != nullptr) *a.sat_flag = 1;
+  __syncthreads();
   red[warp * 64 + lane] = dwout[0];
   red[warp * 64 + 32 + lane] = dwout[1];
   __syncthreads();
@@ -1486,8 +1429,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   }
 }
 
-// Tries the two-CTA form; returns 0 and sets *n_cta (rows of the partial buffer written) when it was launched,
-// -1 when the network / data layout is not eligible, 1 on error.
+// Eligibility of the two-CTA form and its launch; *n_cta = rows of the partial buffer the launched kernel writes.
 static int mlp2_ntw(const NetDev& net)
 {
   int mx = 1;
@@ -1509,6 +1451,38 @@ static bool mlp2_eligible(const NetDev& net, Mlp2Plan& plan, std::vector<DwTile>
   if (plan.kp[0] > 256) return false;
   return plan.smem_bytes <= 113 * 1024;
 }
+// Shared-memory plans of a network shape, computed once (the launchers run every epoch / MD step)
+struct CachedPlans { int n_layers, sizes[PP_MAX_LAYERS + 1]; unsigned tanh_layers; int TM; MlpPlan p1; bool ok2; Mlp2Plan p2; bool used; };
+static const CachedPlans& cached_plans(const NetDev& net)
+{
+  static CachedPlans cache[8];
+  static int next = 0;
+  for (int i = 0; i < 8; i++) {
+    const CachedPlans& c = cache[i];
+    if (c.used && c.n_layers == net.n_layers && c.tanh_layers == net.tanh_layers &&
+        memcmp(c.sizes, net.sizes, sizeof(int) * (net.n_layers + 1)) == 0)
+      return c;
+  }
+  CachedPlans& c = cache[next];
+  next = (next + 1) & 7;
+  c.used = true;
+  c.n_layers = net.n_layers;
+  c.tanh_layers = net.tanh_layers;
+  memset(c.sizes, 0, sizeof(c.sizes));
+  memcpy(c.sizes, net.sizes, sizeof(int) * (net.n_layers + 1));
+  c.TM = choose_tm(net, c.p1, nullptr);
+  c.ok2 = mlp2_eligible(net, c.p2, nullptr);
+  return c;
+}
+
+// doubles of derivative scratch the two-CTA form needs (0: not eligible)
+size_t ppk_mlp2_scratch_doubles(const NetDev& net)
+{
+  const CachedPlans& cp = cached_plans(net);
+  if (!cp.ok2) return 0;
+  return (size_t)2 * sm_count() * (net.n_layers - 1) * mlp2_ntw(net) * 2 * MLP2_THREADS;
+}
+
 int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries)
 {
   Mlp2Plan plan;
@@ -1519,30 +1493,17 @@ int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries)
   if (host_out && !table.empty()) memcpy(host_out, table.data(), table.size() * sizeof(DwTile));
   return 1;
 }
-int ppk_mlp_launch_fused(const MlpArgs& a_in, int* sat_flag_dev, bool one_cta_only, cudaStream_t st, long long* launches, int* n_cta)
+int ppk_mlp_launch_fused(const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta)
 {
   *n_cta = sm_count();
-  MlpArgs a = a_in;
-  a.sat_flag = nullptr;
-  a.run_if = nullptr;
   const NetDev& net = a.net;
-  Mlp2Plan plan;
-  MlpPlan plan1;
-  const bool try2 = !one_cta_only && sat_flag_dev != nullptr && a.rows == nullptr && a.dw_tiles2 != nullptr && a.M > 0 &&
-                    encode_tiled() != nullptr && getenv("PP_MLP_ONE_CTA") == nullptr &&
-                    choose_tm(net, plan1, nullptr) == MLP2_TM && mlp2_eligible(net, plan, nullptr);
+  const CachedPlans& cp = cached_plans(net);
+  const bool try2 = a.rows == nullptr && a.dw_tiles2 != nullptr && a.scratch2 != nullptr && a.M > 0 &&
+                    encode_tiled() != nullptr && getenv("PP_MLP_ONE_CTA") == nullptr && cp.TM == MLP2_TM && cp.ok2;
   if (!try2) return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
+  Mlp2Plan plan = cp.p2;
   CUtensorMap tmap;
-  const cuuint64_t gdim[2] = {(cuuint64_t)net.sizes[0], (cuuint64_t)a.M};
-  const cuuint64_t gstride[1] = {(cuuint64_t)net.sizes[0] * sizeof(double)};
-  const cuuint32_t box[2] = {(cuuint32_t)plan.kp[0], (cuuint32_t)MLP2_TM};
-  const cuuint32_t estr[2] = {1, 1};
-  if (encode_tiled()(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(a.G), gdim, gstride, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-    return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
-  PP_CUDA(cudaMemsetAsync(sat_flag_dev, 0, sizeof(int), st));
-  a.sat_flag = sat_flag_dev;
+  if (!tiled_map(a.G, net.sizes[0], a.M, plan.kp[0], MLP2_TM, &tmap)) return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
   const int grid = 2 * sm_count();
   const int NTW = mlp2_ntw(net), NLW = net.n_layers - 1;
 #define PP_LAUNCH2(NTW_, NLW_)                                                                                  \
@@ -1559,10 +1520,7 @@ int ppk_mlp_launch_fused(const MlpArgs& a_in, int* sat_flag_dev, bool one_cta_on
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   *n_cta = grid;
-  // the one-CTA form behind it, predicated on the saturation flag (an empty launch in the normal case)
-  a.sat_flag = nullptr;
-  a.run_if = sat_flag_dev;
-  return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
+  return 0;
 }
 
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches)
@@ -1575,8 +1533,8 @@ int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launc
     PP_REQUIRE(net.sizes[l] <= MLP_MAX_WIDTH, "hidden layer %d has %d nodes (max %d)", l, net.sizes[l], MLP_MAX_WIDTH);
     if (net.sizes[l] > max_hidden) max_hidden = net.sizes[l];
   }
-  MlpPlan plan;
-  const int TM = choose_tm(net, plan, nullptr);
+  MlpPlan plan = cached_plans(net).p1;
+  const int TM = cached_plans(net).TM;
   PP_REQUIRE(TM > 0, "network too large for shared memory (%zu bytes at 8 atoms per tile)", plan.smem_bytes);
   PP_REQUIRE(plan.n_dw_tiles <= 16 * MLP_WARPS, "network has %d weight-gradient tiles (max %d)", plan.n_dw_tiles, 16 * MLP_WARPS);
   PP_REQUIRE(a.dw_tiles != nullptr || plan.n_dw_tiles == 0, "internal: weight-gradient tile table missing");
@@ -1589,16 +1547,8 @@ int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launc
   // when rows are consecutive atoms and the row size is a 16-byte multiple; anything else keeps the cp.async path.
   CUtensorMap tmap;
   memset(&tmap, 0, sizeof(tmap));
-  if (a.rows == nullptr && (net.sizes[0] & 1) == 0 && a.M > 0 && plan.kpitch[0] <= 256 && encode_tiled() != nullptr) {
-    const cuuint64_t gdim[2] = {(cuuint64_t)net.sizes[0], (cuuint64_t)a.M};
-    const cuuint64_t gstride[1] = {(cuuint64_t)net.sizes[0] * sizeof(double)};
-    const cuuint32_t box[2] = {(cuuint32_t)plan.kpitch[0], (cuuint32_t)TM};
-    const cuuint32_t estr[2] = {1, 1};
-    CUresult r = encode_tiled()(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(a.G), gdim, gstride, box, estr,
-                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    plan.tma = (r == CUDA_SUCCESS) ? 1 : 0;
-  }
+  if (a.rows == nullptr && (net.sizes[0] & 1) == 0 && a.M > 0 && plan.kpitch[0] <= 256)
+    plan.tma = tiled_map(a.G, net.sizes[0], a.M, plan.kpitch[0], TM, &tmap) ? 1 : 0;
   const int NTsel = plan_nt(net);
   const bool many = !plan.blocked;      // OWN = 6: register-blocked table; OWN = 16: single tiles, up to 16 per warp
 #define PP_LAUNCH(MODE_, NT_, OWN_)                                                                             \

@@ -1,5 +1,6 @@
 // extern "C" test hooks into the host layer (used by tests/test_host_layer.py through ctypes).
 #include <cstring>
+#include <ctime>
 #include <fstream>
 #include <sstream>
 
@@ -42,6 +43,41 @@ void pph_optimizer_step(void* hv, int P, double sse, const double* grad, double*
   h->opt->update_network(sse, std::vector<REAL>(grad, grad + P));
   const std::vector<REAL>& x = h->opt->parameters();
   memcpy(x_out, x.data(), sizeof(double) * P);
+}
+// The body of Potential::train (pph_potential.cpp, Potential.cpp:626-672) for `steps` iterations on an existing context:
+// pp_epoch with host buffers (parameters in, [gradient, SSE, vSSE, nval] out), then Optimizer::update_network.  Returns
+// the wall time of the loop in seconds; x_inout holds the parameters before and after.
+int pph_train_loop(void* pp_ctx, void* hv, int P, double* x_inout, double* grad_buf, int steps, double* elapsed_s, double* last_sse)
+{
+  pph_opt* h = (pph_opt*)hv;
+  pp_context* ctx = (pp_context*)pp_ctx;
+  std::vector<REAL> grad(P);
+  struct timespec t0, t1;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  double sse = 0, vsse = 0;
+  long long nval = 0;
+  double t_opt = 0.0;
+  for (int it = 0; it < steps; it++) {
+    if (pp_epoch(ctx, x_inout, grad_buf, &sse, &vsse, &nval)) return 1;
+    struct timespec a, b;
+    clock_gettime(CLOCK_MONOTONIC, &a);
+    h->opt->set_val_sse(vsse, nval);
+    grad.assign(grad_buf, grad_buf + P);
+    h->opt->update_network(sse, grad);
+    const std::vector<REAL>& x = h->opt->parameters();
+    memcpy(x_inout, x.data(), sizeof(double) * P);
+    clock_gettime(CLOCK_MONOTONIC, &b);
+    t_opt += (b.tv_sec - a.tv_sec) * 1e6 + 1e-3 * (b.tv_nsec - a.tv_nsec);
+  }
+  if (getenv("PP_EPOCH_TRACE") && steps > 0) {
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    fprintf(stderr, "pph_train_loop: optimizer step %.1f us, whole step %.1f us (mean of %d)\n", t_opt / steps,
+            ((t1.tv_sec - t0.tv_sec) * 1e6 + 1e-3 * (t1.tv_nsec - t0.tv_nsec)) / steps, steps);
+  }
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  if (elapsed_s) *elapsed_s = (t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec);
+  if (last_sse) *last_sse = sse;
+  return 0;
 }
 // in-place variant for pinned buffers: x is both the current parameters' destination and not read
 void pph_optimizer_step_ptr(void* hv, int P, double sse, const double* grad, double* x_inout)

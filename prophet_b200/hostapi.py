@@ -52,6 +52,18 @@ class Optimizer:
         lib().pph_optimizer_step(self._h, self.P, float(sse), grad.ctypes.data_as(_d), x.ctypes.data_as(_d))
         return x
 
+    def train_loop(self, ctx_handle, x_ptr, grad_ptr, steps):
+        """`steps` iterations of the host layer's training loop (pp_epoch + Optimizer::update_network) in C++;
+        returns (seconds, last SSE).  x_ptr / grad_ptr: host buffers of P doubles (parameters in/out, gradient scratch)."""
+        L = lib()
+        L.pph_train_loop.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+        t = ctypes.c_double(); sse = ctypes.c_double()
+        rc = L.pph_train_loop(ctx_handle, self._h, self.P, x_ptr, grad_ptr, steps, ctypes.byref(t), ctypes.byref(sse))
+        if rc:
+            raise RuntimeError("pph_train_loop failed")
+        return t.value, sse.value
+
     def step_ptr(self, x_ptr, grad_ptr, sse=0.0):
         lib().pph_optimizer_step_ptr(self._h, self.P, float(sse), grad_ptr, x_ptr)
 
