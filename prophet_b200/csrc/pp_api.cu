@@ -835,11 +835,21 @@ static int prepare_fused_tiles(pp_context* c)
   return 0;
 }
 
+// every element's network can run the two-CTA kernels (then all of them do: the partial-gradient rows must agree)
+static bool all_two_cta(pp_context* c)
+{
+  for (int e = 0; e < c->spec.n_elem; e++)
+    if (!c->nets[e].has_tiles2 || !ppk_mlp_two_cta_ok(c->nets[e].dev)) return false;
+  return true;
+}
+
 static int forward_all(pp_context* c)
 {
+  const bool two = all_two_cta(c);
   for (int e = 0; e < c->spec.n_elem; e++) {
     MlpArgs a = mlp_args_train(c, e);
-    if (ppk_mlp_launch(PP_MLP_FORWARD, a, c->stream, &c->launches)) return 1;
+    int n_cta = 0;
+    if (ppk_mlp_launch2(PP_MLP_FORWARD, two, a, c->stream, &c->launches, &n_cta)) return 1;
   }
   StructArgs sa;
   sa.n_struct = c->n_struct;
@@ -863,9 +873,10 @@ static int epoch_buffers(pp_context* c)
   if (c->d_partial.ensure((size_t)n_cta * (c->P_total + 3), 0, c->stream)) return 1;
   if (c->d_result.ensure((size_t)c->P_total + 3, 0, c->stream)) return 1;
   if (c->d_err_scratch.ensure(3 * (size_t)ppk_struct_errors_blocks(std::max(c->n_struct, 1)), 0, c->stream)) return 1;
-  if (c->spec.n_elem == 1 && c->nets[0].has_tiles2 &&
-      c->d_scratch2.ensure(std::max<size_t>(ppk_mlp2_scratch_doubles(c->nets[0].dev), 1), 0, c->stream))
-    return 1;
+  size_t sc2 = 0;
+  for (int e = 0; e < c->spec.n_elem; e++)
+    if (c->nets[e].has_tiles2) sc2 = std::max(sc2, ppk_mlp2_scratch_doubles(c->nets[e].dev));
+  if (sc2 && c->d_scratch2.ensure(sc2, 0, c->stream)) return 1;
   if (!c->d_err_ticket.p) {
     if (c->d_err_ticket.ensure(1, 0, c->stream)) return 1;
     PP_CUDA(cudaMemsetAsync(c->d_err_ticket.p, 0, sizeof(unsigned), c->stream));
@@ -893,11 +904,13 @@ extern "C" int pp_epoch_device(pp_context* c)
     c->epoch_form = 0;
     if (forward_all(c)) return 1;
     if (tick(c, 1)) return 1;
+    const bool two = all_two_cta(c);
+    int n_cta = ppk_mlp_single_ctas();
     for (int e = 0; e < c->spec.n_elem; e++) {
       MlpArgs a = mlp_args_train(c, e);
-      if (ppk_mlp_launch(PP_MLP_TRAIN, a, c->stream, &c->launches)) return 1;
+      if (ppk_mlp_launch2(PP_MLP_TRAIN, two, a, c->stream, &c->launches, &n_cta)) return 1;
     }
-    if (ppk_reduce_partials(c->d_partial.p, ppk_mlp_single_ctas(), c->P_total + 3, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
+    if (ppk_reduce_partials(c->d_partial.p, n_cta, c->P_total + 3, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
   }
   if (tick(c, 2)) return 1;
   if (c->comm.allreduce_device(c->d_result.p, c->P_total + 3, c->stream)) return 1;

@@ -93,6 +93,8 @@ int ppk_mlp_dw_tile_bytes(void);
 int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries);
 size_t ppk_mlp2_scratch_doubles(const NetDev& net);
 int ppk_mlp_launch_fused(const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta);
+bool ppk_mlp_two_cta_ok(const NetDev& net);
+int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta);
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
 
 // per-structure energies / errors (Potential.cpp:641-668)

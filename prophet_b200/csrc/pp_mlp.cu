@@ -1054,7 +1054,7 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
   p.cvec_off = (int)off; off += MLP2_TM;
   p.erow_off = (int)off; off += MLP2_TM;
   p.sttgt_off = (int)off; off += MLP2_TM;
-  p.red_off = (int)off; off += MLP2_WARPS * 64;           // cross-warp sums of the output-node gradient, loss terms
+  p.red_off = p.x_off;                                     // epilogue only (cross-warp sums): aliases the dead descriptor tile
   p.mbar_off = (int)off; off += 2;
   size_t bytes = off * sizeof(double);
   p.stint_off_bytes = (int)bytes;
@@ -1108,11 +1108,15 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
   return true;
 }
 
+// MODE: PP_MLP_FUSED (single pass over tiles of whole structures), PP_MLP_TRAIN (backward of the two-phase epoch: the
+// error factor of every atom's structure is given, rows may be gathered through a.rows), PP_MLP_FORWARD (energies).
 // NTW: n-tiles (8 columns) of the widest hidden layer; NLW: hidden-layer weight matrices (L - 1)
-template <int NTW, int NLW>
+template <int MODE, int NTW, int NLW>
 __global__ void __launch_bounds__(MLP2_THREADS, 2)
 mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tmap)
 {
+  constexpr bool FUSED = (MODE == PP_MLP_FUSED);
+  constexpr bool GRADW = (MODE != PP_MLP_FORWARD);
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sm = reinterpret_cast<double*>(smem_raw);
   const DwTile* tab = reinterpret_cast<const DwTile*>(smem_raw + p.tab_off_bytes);
@@ -1140,6 +1144,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     sm[p.is_off + k] = (k < NG) ? 1.0 / net.scale[k] : 0.0;
   }
   for (int i = tid; i < 64; i += MLP2_THREADS) sm[p.exptab_off + i] = exp2((double)i * 0.015625);
+  for (int i = tid; i < TM * kp0; i += MLP2_THREADS) sm[p.x_off + i] = 0.0;      // padding columns (row copies leave them alone)
   {
     const int nwords = NLW * 2 * MLP2_WARPS * (int)(sizeof(DwTile) / sizeof(int));
     int* dst = reinterpret_cast<int*>(smem_raw + p.tab_off_bytes);
@@ -1171,11 +1176,15 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
 #pragma unroll
     for (int t = 0; t < 6; t++) { dW[l][t][0] = 0.0; dW[l][t][1] = 0.0; }
 
-  const int n_tiles = a.n_tiles;
+  const int n_tiles = FUSED ? a.n_tiles : (a.M + TM - 1) / TM;
   struct Geom { int s0, s1, row0, nvalid; };
   auto tile_geom = [&](int tile) {
     Geom gm;
     gm.s0 = gm.s1 = gm.row0 = gm.nvalid = 0;
+    if (!FUSED) {
+      if (tile < n_tiles) { gm.row0 = tile * TM; gm.nvalid = min(TM, a.M - gm.row0); }
+      return gm;
+    }
     if (tile < n_tiles) {
       gm.s0 = a.tile_struct0[tile];
       gm.s1 = a.tile_struct0[tile + 1];
@@ -1189,22 +1198,33 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   int pf_lo = 0, pf_tag = 0;
   double pf_tgt = 0.0;
   auto st_fetch = [&](const Geom& gm) {
-    if (tid <= gm.s1 - gm.s0) {
+    if (FUSED && tid <= gm.s1 - gm.s0) {
       const int sidx = gm.s0 + tid;
       pf_lo = (int)(a.struct_atom0[sidx] - gm.row0);
       if (sidx < gm.s1) { pf_tgt = a.target[sidx]; pf_tag = a.tag[sidx]; }
     }
   };
+  // One tensor copy per tile when the rows are consecutive atoms; gathered rows (an element of a multi-element system)
+  // come as one bulk copy per row, issued by the warp that owns the row (lanes 0..7), all counted on the same mbarrier.
+  const bool gather = !FUSED && (a.rows != nullptr);      // fused tiles are whole structures of consecutive atoms
   auto issue_load = [&](const Geom& gm) {
-    if (tid == 0) {
-      mbar_arrive_expect_tx(mbar, (unsigned)TM * (unsigned)kp0 * 8u);
-      tma_load_tile(X, &tmap, gm.row0, mbar);
+    if (!gather) {
+      if (tid == 0) {
+        mbar_arrive_expect_tx(mbar, (unsigned)TM * (unsigned)kp0 * 8u);
+        tma_load_tile(X, &tmap, gm.row0, mbar);
+      }
+      return;
+    }
+    if (tid == 0) mbar_arrive_expect_tx(mbar, (unsigned)gm.nvalid * (unsigned)NG * 8u);
+    if (lane < 8) {
+      const int r = 8 * warp + lane;
+      double* dst = X + (size_t)r * kp0;
+      if (r < gm.nvalid) bulk_copy_g2s(dst, a.G + (size_t)a.rows[gm.row0 + r] * NG, (unsigned)NG * 8u, mbar);
+      else for (int c = 0; c < NG; c++) dst[c] = 0.0;
     }
   };
-  if (tid == 0) {
-    mbar_init(mbar, 1);
-    fence_proxy_async();
-  }
+  if (tid == 0) mbar_init(mbar, 1);
+  fence_proxy_async();                         // staging stores (and the barrier's init) before the copy engine's writes
   __syncthreads();
   Geom g_cur = tile_geom(blockIdx.x), g_nxt = tile_geom(blockIdx.x + gridDim.x);
   if ((int)blockIdx.x < n_tiles) issue_load(g_cur);
@@ -1216,13 +1236,24 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     const int row0 = g_cur.row0, nvalid = g_cur.nvalid;
     const int s_first = g_cur.s0, s_last = g_cur.s1;
     const Geom g_nn = tile_geom(tile + 2 * gridDim.x);
-    (void)row0;
-    // structure table of this tile (read after barrier A); then the next tile's entries start their flight
-    if (tid <= s_last - s_first) {
-      st_lo[tid] = pf_lo;
-      if (tid < s_last - s_first) { st_tgt[tid] = pf_tgt; st_tag[tid] = pf_tag; }
+    if (FUSED) {
+      // structure table of this tile (read after barrier A); then the next tile's entries start their flight
+      if (tid <= s_last - s_first) {
+        st_lo[tid] = pf_lo;
+        if (tid < s_last - s_first) { st_tgt[tid] = pf_tgt; st_tag[tid] = pf_tag; }
+      }
+      st_fetch(g_nxt);
+    } else if (MODE == PP_MLP_TRAIN) {
+      // error factor of each row's structure (struct_errors_kernel); read after barrier A
+      if (tid < TM) {
+        double c = 0.0;
+        if (tid < nvalid) {
+          const size_t atom = gather ? (size_t)a.rows[row0 + tid] : (size_t)(row0 + tid);
+          c = a.cstruct[a.atom_struct[atom]];
+        }
+        cvec[tid] = c;
+      }
     }
-    st_fetch(g_nxt);
     mbar_wait(mbar, (unsigned)n_done & 1u);
 
     // ---- normalise this warp's 8 rows in place (NN.cpp:647-651); column NG is the bias input ---------------------
@@ -1268,17 +1299,27 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         }
         __syncwarp();
       }
-      yp += __shfl_xor_sync(0xffffffffu, yp, 1);
-      yp += __shfl_xor_sync(0xffffffffu, yp, 2);
-      if (q == 0) {
-        const int r = rb + g;
-        erow[r] = (r < nvalid) ? a.out_scale * (yp + wo[p.n[L - 1]]) : 0.0;
+      if (MODE != PP_MLP_TRAIN) {
+        yp += __shfl_xor_sync(0xffffffffu, yp, 1);
+        yp += __shfl_xor_sync(0xffffffffu, yp, 2);
+        if (q == 0) {
+          const int r = rb + g;
+          const double e = a.out_scale * (yp + wo[p.n[L - 1]]);
+          if (FUSED) erow[r] = (r < nvalid) ? e : 0.0;
+          else if (r < nvalid && a.E_atom != nullptr) a.E_atom[gather ? (size_t)a.rows[row0 + r] : (size_t)(row0 + r)] = e;
+        }
       }
     }
-    __syncthreads();                                                                   // barrier A: erow, structure table
+    __syncthreads();                                                                   // barrier A: erow / cvec, structure table
+    if (MODE == PP_MLP_FORWARD) {              // energies only: X is free again
+      if (tile + (int)gridDim.x < n_tiles) issue_load(g_nxt);
+      g_cur = g_nxt;
+      g_nxt = g_nn;
+      continue;
+    }
 
     // ---- per-structure energy, error and loss terms (Potential.cpp:641-668): the factor c of this warp's own rows --
-    {
+    if (FUSED) {
       const int re = rb + 8;
       const int ns = s_last - s_first;
       double c_mine = 0.0;                     // lanes 0..7: c of row rb + lane
@@ -1389,6 +1430,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   }
 
   // ---- per-CTA partial gradient and loss terms -> scratch (summed in a fixed order by reduce_partials_kernel) -----------
+  if (!GRADW) return;
   double* out = a.partial + (size_t)blockIdx.x * (a.P_total + 3) + a.p_off;
 #pragma unroll
   for (int l = 0; l < NLW; l++) {
@@ -1419,6 +1461,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     for (int w = 0; w < MLP2_WARPS; w++) s_ += red[w * 64 + tid];
     out[net.w_off[L - 1] + tid] = s_;
   }
+  if (!FUSED) return;                          // two-phase epoch: the loss terms come from struct_errors_kernel
   __syncthreads();
   if (lane == 0) { red[3 * warp] = sse_w; red[3 * warp + 1] = vsse_w; red[3 * warp + 2] = nval_w; }
   __syncthreads();
@@ -1493,34 +1536,58 @@ int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries)
   if (host_out && !table.empty()) memcpy(host_out, table.data(), table.size() * sizeof(DwTile));
   return 1;
 }
-int ppk_mlp_launch_fused(const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta)
+// The two-CTA form of `mode` (FUSED, TRAIN or FORWARD) if the network and data layout allow it, else the one-CTA form;
+// *n_cta = rows of the partial-gradient buffer the launched kernel writes (gradient modes).
+bool ppk_mlp_two_cta_ok(const NetDev& net)
+{
+  const CachedPlans& cp = cached_plans(net);
+  return cp.TM == MLP2_TM && cp.ok2 && getenv("PP_MLP_ONE_CTA") == nullptr;
+}
+
+int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta)
 {
   *n_cta = sm_count();
   const NetDev& net = a.net;
   const CachedPlans& cp = cached_plans(net);
-  const bool try2 = a.rows == nullptr && a.dw_tiles2 != nullptr && a.scratch2 != nullptr && a.M > 0 &&
-                    encode_tiled() != nullptr && getenv("PP_MLP_ONE_CTA") == nullptr && cp.TM == MLP2_TM && cp.ok2;
-  if (!try2) return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
+  const bool try2 = allow_two_cta && (mode == PP_MLP_FUSED || mode == PP_MLP_TRAIN || mode == PP_MLP_FORWARD) &&
+                    a.dw_tiles2 != nullptr && a.scratch2 != nullptr && a.M > 0 && encode_tiled() != nullptr &&
+                    (mode != PP_MLP_FUSED || a.rows == nullptr) && ppk_mlp_two_cta_ok(net);
+  if (!try2) return ppk_mlp_launch(mode, a, st, launches);
   Mlp2Plan plan = cp.p2;
   CUtensorMap tmap;
-  if (!tiled_map(a.G, net.sizes[0], a.M, plan.kp[0], MLP2_TM, &tmap)) return ppk_mlp_launch(PP_MLP_FUSED, a, st, launches);
-  const int grid = 2 * sm_count();
+  memset(&tmap, 0, sizeof(tmap));
+  if (a.rows == nullptr && !tiled_map(a.G, net.sizes[0], a.M, plan.kp[0], MLP2_TM, &tmap)) return ppk_mlp_launch(mode, a, st, launches);
+  const int n_tiles = (mode == PP_MLP_FUSED) ? a.n_tiles : (a.M + MLP2_TM - 1) / MLP2_TM;
+  int grid = 2 * sm_count();
+  if (mode == PP_MLP_FORWARD) grid = std::max(1, std::min(grid, n_tiles));     // gradient modes: every CTA writes its partial
   const int NTW = mlp2_ntw(net), NLW = net.n_layers - 1;
-#define PP_LAUNCH2(NTW_, NLW_)                                                                                  \
+#define PP_LAUNCH2(MODE_, NTW_, NLW_)                                                                           \
   {                                                                                                             \
-    auto k = mlp_fused2_kernel<NTW_, NLW_>;                                                                     \
+    auto k = mlp_fused2_kernel<MODE_, NTW_, NLW_>;                                                              \
     PP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes));        \
     k<<<grid, MLP2_THREADS, plan.smem_bytes, st>>>(a, plan, tmap);                                              \
   }
-  if (NTW == 5 && NLW == 1) PP_LAUNCH2(5, 1)
-  else if (NTW == 5 && NLW == 2) PP_LAUNCH2(5, 2)
-  else if (NTW == 8 && NLW == 1) PP_LAUNCH2(8, 1)
-  else PP_LAUNCH2(8, 2)
+#define PP_LAUNCH2_SHAPE(MODE_)                                  \
+  {                                                              \
+    if (NTW == 5 && NLW == 1) PP_LAUNCH2(MODE_, 5, 1)            \
+    else if (NTW == 5 && NLW == 2) PP_LAUNCH2(MODE_, 5, 2)       \
+    else if (NTW == 8 && NLW == 1) PP_LAUNCH2(MODE_, 8, 1)       \
+    else PP_LAUNCH2(MODE_, 8, 2)                                 \
+  }
+  if (mode == PP_MLP_FUSED) PP_LAUNCH2_SHAPE(PP_MLP_FUSED)
+  else if (mode == PP_MLP_TRAIN) PP_LAUNCH2_SHAPE(PP_MLP_TRAIN)
+  else PP_LAUNCH2_SHAPE(PP_MLP_FORWARD)
+#undef PP_LAUNCH2_SHAPE
 #undef PP_LAUNCH2
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   *n_cta = grid;
   return 0;
+}
+
+int ppk_mlp_launch_fused(const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta)
+{
+  return ppk_mlp_launch2(PP_MLP_FUSED, true, a, st, launches, n_cta);
 }
 
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches)
