@@ -2,12 +2,15 @@
 #include "pp_desc.cuh"
 #include "pp_kernels.h"
 
-#define DESC_WARPS 8
+#define DESC_WARPS 4
+#ifndef DESC_BLOCKS_PER_SM
+#define DESC_BLOCKS_PER_SM 3      // descriptor kernels: 12 warps per SM (<= 170 registers)
+#endif
 
 // ---------------------------------------------------------------------------------------------------------
 // K1+K2+K3 fused, periodic structures (training set-up): one warp per atom.
 template <int NR_T, int NX, bool BASIS>
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
 desc_periodic_kernel(PeriodicArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -76,7 +79,7 @@ neighbors_periodic_kernel(PeriodicArgs a, int s, int pass, int* counts, const in
 // ---------------------------------------------------------------------------------------------------------
 // MD (LAMMPS list) descriptors: Structure::Calc_G non-periodic branch (Structure.cpp:1073-1145).
 template <int NR_T, int NX, bool BASIS>
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
 md_desc_kernel(MdArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -102,7 +105,7 @@ md_desc_kernel(MdArgs a)
 
 // MD forces: Structure::Get_Forces non-periodic branch (Structure.cpp:429-713) with dE/dG given.
 template <int NR_T, int NX, bool BASIS>
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 2)      // 238 registers: a third block per SM would spill (2x slower)
 md_force_kernel(MdArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -168,7 +171,7 @@ static int dispatch_tile(const DescSpec& hs, F&& f)
 static int max_cap_for(int NR, int NG, bool force)
 {
   int cap = 32;
-  while (pp_warp_smem_bytes(cap * 2, NR, NG, force) * DESC_WARPS <= 220 * 1024) cap *= 2;
+  while (pp_warp_smem_bytes(cap * 2, NR, NG, force) * DESC_WARPS <= 110 * 1024) cap *= 2;      // two blocks per SM at least
   return cap;
 }
 
