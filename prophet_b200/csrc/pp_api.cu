@@ -83,7 +83,7 @@ struct pp_context {
   // ---- training set ----
   int n_struct = 0;
   long long n_atoms = 0;
-  int desc_cap = 128;
+  int desc_cap = 64;                   // neighbour capacity per atom: doubled (and the launch repeated) when an atom overflows it
   std::vector<long long> h_struct_atom0{0};
   std::vector<double> h_FtoA, h_target;
   std::vector<int> h_mxyz, h_tag, h_elem, h_atom_struct;
@@ -108,7 +108,7 @@ struct pp_context {
 
   // ---- MD ----
   std::vector<int> type_to_elem;
-  int md_cap = 128;
+  int md_cap = 64;
   int md_nlocal = 0, md_ntotal = 0;
   long long md_nneigh = 0;
   DevBuf<double> d_x, d_f, d_Gmd, d_dEdG, d_eatom;

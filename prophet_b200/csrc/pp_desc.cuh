@@ -57,8 +57,8 @@ __device__ inline void pp_warp_views(WarpNbr& w, unsigned char* base, int cap, i
   w.A = p; p += (size_t)NR * cap;
   if (force) { w.dA = p; p += (size_t)NR * cap; w.fx = p; p += cap; w.fy = p; p += cap; w.fz = p; p += cap; }
   else { w.dA = nullptr; w.fx = w.fy = w.fz = nullptr; }
+  w.cell = p; p += PP_MAX_RAD * PP_MAX_ANG;      // first: 16-byte aligned whatever NG is (cap is even), see pp_g4_block_force_basis
   w.buf = p; p += NG;
-  w.cell = p; p += PP_MAX_RAD * PP_MAX_ANG;
   int* q = reinterpret_cast<int*>(p);
   w.elem = q; q += cap; w.selem = q; q += cap; w.idx = q; q += cap; w.sidx = q; q += cap;
   w.start = q; q += 8;
@@ -519,19 +519,19 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
   for (int i = lane; i < NW; i += 32) w.cell[i] = 0.0;
   __syncwarp();
   const int base = S->trip_base[e1][e2] + S->nG3;
+  // weights dE/dG of the basis cells, layout [k][r][g]: the two lambda groups of a (power, radial key) cell sit side by
+  // side, so the pair loop fetches them with one 16-byte shared-memory load each time it needs them.  Keeping all
+  // NR_T * 2 * NB of them in registers instead costs 100 registers and caps the kernel at 8 warps per SM.
   for (int row = lane; row < S->nG4; row += 32) {
     const int rr = S->g4_rad[row] - r0;
     if (rr >= 0 && rr < NR_T)
-      atomicAdd(&w.cell[(rr * 2 + S->g4_bg[row]) * NB + S->g4_bb[row]], 2.0 * S->ang_pref[S->g4_ang[row]] * w.buf[base + row]);
+      atomicAdd(&w.cell[(S->g4_bb[row] * NR_T + rr) * 2 + S->g4_bg[row]], 2.0 * S->ang_pref[S->g4_ang[row]] * w.buf[base + row]);
   }
   __syncwarp();
-  double W[NR_T][2][NB];
-#pragma unroll
-  for (int r = 0; r < NR_T; r++)
-#pragma unroll
-    for (int g = 0; g < 2; g++)
-#pragma unroll
-      for (int k = 0; k < NB; k++) W[r][g][k] = w.cell[(r * 2 + g) * NB + k];
+  const unsigned cell_s = (unsigned)__cvta_generic_to_shared(w.cell);
+  auto Wld = [&](int k, int r, double& w0, double& w1) {      // volatile: must not be hoisted back into registers
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(w0), "=d"(w1) : "r"(cell_s + 16u * (unsigned)(k * NR_T + r)));
+  };
   const int NR = S->NR;
   const double *Arow[NR_T], *dArow[NR_T];
 #pragma unroll
@@ -587,15 +587,19 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
 #pragma unroll
           for (int r = 0; r < NR_T; r++) {
             Ab[r] = Arow[r][jb]; dAb[r] = dArow[r][jb];
-            S0[r] = W[r][0][0] * pw[0][0]; S1[r] = W[r][1][0] * pw[1][0];
-            T0[r] = W[r][0][0] * dpw[0][0]; T1[r] = W[r][1][0] * dpw[1][0];
+            double w0, w1;
+            Wld(0, r, w0, w1);
+            S0[r] = w0 * pw[0][0]; S1[r] = w1 * pw[1][0];
+            T0[r] = w0 * dpw[0][0]; T1[r] = w1 * dpw[1][0];
           }
 #pragma unroll
           for (int k = 1; k < NB; k++)
 #pragma unroll
             for (int r = 0; r < NR_T; r++) {
-              S0[r] = fma(W[r][0][k], pw[0][k], S0[r]); S1[r] = fma(W[r][1][k], pw[1][k], S1[r]);
-              T0[r] = fma(W[r][0][k], dpw[0][k], T0[r]); T1[r] = fma(W[r][1][k], dpw[1][k], T1[r]);
+              double w0, w1;
+              Wld(k, r, w0, w1);
+              S0[r] = fma(w0, pw[0][k], S0[r]); S1[r] = fma(w1, pw[1][k], S1[r]);
+              T0[r] = fma(w0, dpw[0][k], T0[r]); T1[r] = fma(w1, dpw[1][k], T1[r]);
             }
           double dRa = 0.0, dRb = 0.0, dc = 0.0;
 #pragma unroll
