@@ -105,7 +105,7 @@ md_desc_kernel(MdArgs a)
 
 // MD forces: Structure::Get_Forces non-periodic branch (Structure.cpp:429-713) with dE/dG given.
 template <int NR_T, int NX, bool BASIS>
-__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 4)
 md_force_kernel(MdArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];

@@ -36,6 +36,9 @@ struct WarpNbr {
                               // pointer above) into local memory and turn all shared loads into generic ones.
 };
 
+// per-warp scratch for the cells of one G4 block: NR_T x NA_T (<= 8 x 4) on the general path, NR_T x 2 x NB padded to a
+// multiple of 32 (<= 96) on the power-basis path
+#define PP_CELL_DOUBLES 128
 __host__ __device__ inline size_t pp_warp_smem_bytes(int cap, int NR, int NG, bool force)
 {
   size_t d = 0;
@@ -44,7 +47,7 @@ __host__ __device__ inline size_t pp_warp_smem_bytes(int cap, int NR, int NG, bo
   d += (size_t)NR * cap;                // A
   if (force) d += (size_t)NR * cap + 3 * (size_t)cap;
   d += (size_t)NG;
-  d += PP_MAX_RAD * PP_MAX_ANG;
+  d += PP_CELL_DOUBLES;
   size_t bytes = d * sizeof(double) + 4 * (size_t)cap * sizeof(int) + 8 * sizeof(int);
   return (bytes + 15) & ~(size_t)15;
 }
@@ -57,7 +60,7 @@ __device__ inline void pp_warp_views(WarpNbr& w, unsigned char* base, int cap, i
   w.A = p; p += (size_t)NR * cap;
   if (force) { w.dA = p; p += (size_t)NR * cap; w.fx = p; p += cap; w.fy = p; p += cap; w.fz = p; p += cap; }
   else { w.dA = nullptr; w.fx = w.fy = w.fz = nullptr; }
-  w.cell = p; p += PP_MAX_RAD * PP_MAX_ANG;      // first: 16-byte aligned whatever NG is (cap is even), see pp_g4_block_force_basis
+  w.cell = p; p += PP_CELL_DOUBLES;      // first: 16-byte aligned whatever NG is (cap is even), see pp_g4_block_force_basis
   w.buf = p; p += NG;
   int* q = reinterpret_cast<int*>(p);
   w.elem = q; q += cap; w.selem = q; q += cap; w.idx = q; q += cap; w.sidx = q; q += cap;
@@ -520,7 +523,7 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
   __syncwarp();
   const int base = S->trip_base[e1][e2] + S->nG3;
   // weights dE/dG of the basis cells, layout [k][r][g]: the two lambda groups of a (power, radial key) cell sit side by
-  // side, so the pair loop fetches them with one 16-byte shared-memory load each time it needs them.  Keeping all
+  // side, and the pair loop fetches each from shared memory when it needs it.  Keeping all
   // NR_T * 2 * NB of them in registers instead costs 100 registers and caps the kernel at 8 warps per SM.
   for (int row = lane; row < S->nG4; row += 32) {
     const int rr = S->g4_rad[row] - r0;
@@ -529,8 +532,10 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
   }
   __syncwarp();
   const unsigned cell_s = (unsigned)__cvta_generic_to_shared(w.cell);
-  auto Wld = [&](int k, int r, double& w0, double& w1) {      // volatile: must not be hoisted back into registers
-    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(w0), "=d"(w1) : "r"(cell_s + 16u * (unsigned)(k * NR_T + r)));
+  auto Wld = [&](int k, int r, int gq) {      // volatile: must not be hoisted back into registers
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(cell_s + 8u * (unsigned)((k * NR_T + r) * 2 + gq)));
+    return v;
   };
   const int NR = S->NR;
   const double *Arow[NR_T], *dArow[NR_T];
@@ -568,43 +573,37 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
         bool skip = false;
         if (skip_rjk) { const double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c; skip = rjk2 > rcut2; }
         if (!skip) {
-          double pw[2][NB], dpw[2][NB];
-          pw[0][0] = fmax(fma(lam0, c, 1.0), 0.0);
-          pw[1][0] = fmax(fma(lam1, c, 1.0), 0.0);
-          dpw[0][0] = pw[0][0] > 0.0 ? lam0 : 0.0;
-          dpw[1][0] = pw[1][0] > 0.0 ? lam1 : 0.0;
-          double pp0 = dpw[0][0], pp1 = dpw[1][0];      // lam_g * prod_{k<b} pw_g[k]
+          // S_r = sum_{g,k} W[k][r][g] p_g^(2^k), T_r the same with d/dc of the powers; the two lambda groups one after
+          // the other, the powers produced on the fly (a chain of squarings and its prefix products): 2 NR_T accumulators
+          // live instead of 4 NR_T plus 4 NB powers, which is what lets a fourth block onto the SM
+          double Ab[NR_T], dAb[NR_T], Ss[NR_T], Ts[NR_T];
 #pragma unroll
-          for (int k = 1; k < NB; k++) {
-            pp0 *= pw[0][k - 1]; pp1 *= pw[1][k - 1];
-            pw[0][k] = pw[0][k - 1] * pw[0][k - 1];
-            pw[1][k] = pw[1][k - 1] * pw[1][k - 1];
-            dpw[0][k] = (double)(1 << k) * pp0;
-            dpw[1][k] = (double)(1 << k) * pp1;
-          }
-          // 4 NR_T independent accumulation chains (per radial key and lambda group) instead of 2 long ones per key
-          double Ab[NR_T], dAb[NR_T], S0[NR_T], S1[NR_T], T0[NR_T], T1[NR_T];
+          for (int r = 0; r < NR_T; r++) { Ab[r] = Arow[r][jb]; dAb[r] = dArow[r][jb]; Ss[r] = 0.0; Ts[r] = 0.0; }
 #pragma unroll
-          for (int r = 0; r < NR_T; r++) {
-            Ab[r] = Arow[r][jb]; dAb[r] = dArow[r][jb];
-            double w0, w1;
-            Wld(0, r, w0, w1);
-            S0[r] = w0 * pw[0][0]; S1[r] = w1 * pw[1][0];
-            T0[r] = w0 * dpw[0][0]; T1[r] = w1 * dpw[1][0];
-          }
+          for (int gq = 0; gq < 2; gq++) {
+            const double lam = gq ? lam1 : lam0;
+            double pk = fmax(fma(lam, c, 1.0), 0.0);          // p^(2^k)
+            double pp = pk > 0.0 ? lam : 0.0;                 // lam * prod_{j<k} p^(2^j)
+            double dk = pp;                                   // d/dc p^(2^k) = 2^k * pp
 #pragma unroll
-          for (int k = 1; k < NB; k++)
+            for (int k = 0; k < NB; k++) {
 #pragma unroll
-            for (int r = 0; r < NR_T; r++) {
-              double w0, w1;
-              Wld(k, r, w0, w1);
-              S0[r] = fma(w0, pw[0][k], S0[r]); S1[r] = fma(w1, pw[1][k], S1[r]);
-              T0[r] = fma(w0, dpw[0][k], T0[r]); T1[r] = fma(w1, dpw[1][k], T1[r]);
+              for (int r = 0; r < NR_T; r++) {
+                const double wv = Wld(k, r, gq);
+                Ss[r] = fma(wv, pk, Ss[r]);
+                Ts[r] = fma(wv, dk, Ts[r]);
+              }
+              if (k + 1 < NB) {
+                pp *= pk;
+                pk *= pk;
+                dk = (double)(2 << k) * pp;
+              }
             }
+          }
           double dRa = 0.0, dRb = 0.0, dc = 0.0;
 #pragma unroll
           for (int r = 0; r < NR_T; r++) {
-            const double Sr = S0[r] + S1[r], Tr = T0[r] + T1[r];
+            const double Sr = Ss[r], Tr = Ts[r];
             dRa = fma(Sr * dAa[r], Ab[r], dRa);
             dRb = fma(Sr * Aa[r], dAb[r], dRb);
             dc = fma(Tr * Aa[r], Ab[r], dc);
