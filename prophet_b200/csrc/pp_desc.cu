@@ -4,7 +4,7 @@
 
 #define DESC_WARPS 4
 #ifndef DESC_BLOCKS_PER_SM
-#define DESC_BLOCKS_PER_SM 3      // descriptor kernels: 12 warps per SM (<= 170 registers)
+#define DESC_BLOCKS_PER_SM 4      // 16 warps per SM (<= 128 registers)
 #endif
 
 // ---------------------------------------------------------------------------------------------------------

@@ -443,60 +443,65 @@ template <int NR_T, int NB>
 __device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
                                               int e1, int e2, int r0, bool skip_rjk)
 {
-  constexpr int NACC = NR_T * 2 * NB;
-  constexpr int NPAD = NACC <= 32 ? 32 : (NACC <= 64 ? 64 : 128);
+  // One pass over the pairs per lambda group: NR_T * NB accumulators live instead of twice that many (the pair geometry
+  // is cheap to redo), which is what lets a fourth block onto the SM.
+  constexpr int NACC = NR_T * NB;
+  constexpr int NPAD = NACC <= 32 ? 32 : 64;
   const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
   const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
   const bool same = (e1 == e2);
   const double rcut2 = S->Rcut * S->Rcut;
-  const double lam0 = S->basis_lam[0], lam1 = S->basis_lam[1];
-  double acc[NPAD];
-#pragma unroll
-  for (int i = 0; i < NPAD; i++) acc[i] = 0.0;
   const int NR = S->NR;
   const double* Arow[NR_T];
 #pragma unroll
   for (int r = 0; r < NR_T; r++) Arow[r] = w.A + (size_t)min(r0 + r, NR - 1) * cap;
 
-  for (int a = lane; a < m1; a += 32) {
-    const int ja = s1 + a;
-    const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
-    double Aa[NR_T];
+#pragma unroll 1
+  for (int gq = 0; gq < 2; gq++) {
+    const double lam = S->basis_lam[gq];
+    double acc[NPAD];
 #pragma unroll
-    for (int r = 0; r < NR_T; r++) Aa[r] = (r0 + r < NR) ? Arow[r][ja] : 0.0;
-    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
-    int b = same ? a + 1 : 0;
-    if (same && b >= m1) b -= m1;
-    const int sb = same ? s1 : s2, mb = same ? m1 : m2;
-    for (int t = 0; t < nt; t++) {
-      const int jb = sb + b;
-      b++;
-      if (b >= mb) b -= mb;
-      const double c = ax * w.ux[jb] + ay * w.uy[jb] + az * w.uz[jb];
-      if (skip_rjk) {
-        const double Rb = w.R[jb];
-        const double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c;
-        if (rjk2 > rcut2) continue;
-      }
-      double pw[2][NB];
-      pw[0][0] = fmax(fma(lam0, c, 1.0), 0.0);
-      pw[1][0] = fmax(fma(lam1, c, 1.0), 0.0);
+    for (int i = 0; i < NPAD; i++) acc[i] = 0.0;
+    for (int a = lane; a < m1; a += 32) {
+      const int ja = s1 + a;
+      const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
+      double Aa[NR_T];
 #pragma unroll
-      for (int k = 1; k < NB; k++) { pw[0][k] = pw[0][k - 1] * pw[0][k - 1]; pw[1][k] = pw[1][k - 1] * pw[1][k - 1]; }
+      for (int r = 0; r < NR_T; r++) Aa[r] = (r0 + r < NR) ? Arow[r][ja] : 0.0;
+      const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+      int b = same ? a + 1 : 0;
+      if (same && b >= m1) b -= m1;
+      const int sb = same ? s1 : s2, mb = same ? m1 : m2;
+      for (int t = 0; t < nt; t++) {
+        const int jb = sb + b;
+        b++;
+        if (b >= mb) b -= mb;
+        const double c = ax * w.ux[jb] + ay * w.uy[jb] + az * w.uz[jb];
+        if (skip_rjk) {
+          const double Rb = w.R[jb];
+          const double rjk2 = Ra * Ra + Rb * Rb - 2.0 * Ra * Rb * c;
+          if (rjk2 > rcut2) continue;
+        }
+        double pw[NB];
+        pw[0] = fmax(fma(lam, c, 1.0), 0.0);
 #pragma unroll
-      for (int r = 0; r < NR_T; r++) {
-        const double tr = Aa[r] * Arow[r][jb];
+        for (int k = 1; k < NB; k++) pw[k] = pw[k - 1] * pw[k - 1];
 #pragma unroll
-        for (int g = 0; g < 2; g++)
+        for (int r = 0; r < NR_T; r++) {
+          const double tr = Aa[r] * Arow[r][jb];
 #pragma unroll
-          for (int k = 0; k < NB; k++) acc[(r * 2 + g) * NB + k] = fma(pw[g][k], tr, acc[(r * 2 + g) * NB + k]);
+          for (int k = 0; k < NB; k++) acc[r * NB + k] = fma(pw[k], tr, acc[r * NB + k]);
+        }
       }
     }
-  }
-  pp_reduce_scatter<NPAD>(acc, lane);
-  constexpr int PER = NPAD / 32;
+    pp_reduce_scatter<NPAD>(acc, lane);
+    constexpr int PER = NPAD / 32;
 #pragma unroll
-  for (int p = 0; p < PER; p++) w.cell[PER * lane + p] = 2.0 * acc[p];     // factor 2 = both (j,k) orders of the reference
+    for (int p = 0; p < PER; p++) {
+      const int idx = PER * lane + p;                     // = r * NB + k
+      if (idx < NACC) w.cell[((idx / NB) * 2 + gq) * NB + (idx % NB)] = 2.0 * acc[p];     // factor 2 = both (j,k) orders of the reference
+    }
+  }
   __syncwarp();
   const int base = S->trip_base[e1][e2] + S->nG3;
   for (int row = lane; row < S->nG4; row += 32) {
