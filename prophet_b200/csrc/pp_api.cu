@@ -415,10 +415,14 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
   PP_CUDA(cudaMemcpy(n.d_tf.p, n.tf.data(), n.n_nodes * sizeof(int), cudaMemcpyHostToDevice));
   n.dev.mean = n.d_mean.p; n.dev.scale = n.d_scale.p; n.dev.tf = n.d_tf.p;
   n.dev.tanh_layers = 0;
+  n.dev.spline_layers = 0;
   for (int l = 0; l < n_layers - 1; l++) {
     bool all = true;
     for (int k = 0; k < sizes[l + 1]; k++) all = all && n.tf[n.dev.node_off[l] + k] == 1;
     if (all) n.dev.tanh_layers |= 1u << (l + 1);
+    bool all_spline = true;
+    for (int k = 0; k < sizes[l + 1]; k++) all_spline = all_spline && n.tf[n.dev.node_off[l] + k] == 2;
+    if (all_spline) n.dev.spline_layers |= 1u << (l + 1);
   }
   {
     n.tile_atoms = ppk_mlp_tile_atoms(n.dev);

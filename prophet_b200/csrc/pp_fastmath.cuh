@@ -55,3 +55,33 @@ __device__ __forceinline__ double pp_fast_tanh(double in, double& deriv, const d
   const double t = far ? 1.0 - 2.0 * e * (1.0 - e) : (1.0 - e) * r;
   return copysign(in == 0.0 ? 0.0 : t, in);
 }
+
+// The reference's default transfer function "tanh_spline" (Tables.h:74-128, Tables.cpp:212-221): a C2 cubic spline
+// through tanh on the knots X_i = -17 + 0.034 i, i = 0..1000, saturating outside.  table = X[1001], one pad, then
+// a[1000][4] (cubic, quadratic, linear, constant in x - X_i) at PP_SPLINE_COEF, 16-byte aligned.
+// Branch-free form for the unrolled epilogues: the bin from the uniform spacing with one correction step either way
+// (what the reference's search loops come to; the knots are recomputed instead of loaded -- a bin chosen differently
+// within an ulp of a knot changes nothing at 1e-10, the spline being C2), two 16-byte loads for the coefficients, the
+// saturated ends by selection.
+#define PP_SPLINE_COEF 1002
+__device__ __forceinline__ double pp_fast_tanh_spline(double in, double& deriv, const double* __restrict__ table)
+{
+  int bin = (int)((in + 17.0) * (1000.0 / 34.0));
+  bin = bin < 0 ? 0 : (bin > 999 ? 999 : bin);
+  const double xl = fma(0.034, (double)bin, -17.0);
+  bin = (in < xl && bin > 0) ? bin - 1 : ((in >= xl + 0.034 && bin < 999) ? bin + 1 : bin);
+  const double2* a = reinterpret_cast<const double2*>(table + PP_SPLINE_COEF + 4 * bin);
+  const double2 c01 = __ldg(a), c23 = __ldg(a + 1);
+  const double x = in - fma(0.034, (double)bin, -17.0);
+  double d = (3.0 * c01.x * x + 2.0 * c01.y) * x + c23.x;
+  double v = ((c01.x * x + c01.y) * x + c23.x) * x + c23.y;
+  if (in < -17.0) { v = __ldg(table + PP_SPLINE_COEF + 3); d = 0.0; }
+  if (in >= 17.0) {
+    const double2 e01 = __ldg(reinterpret_cast<const double2*>(table + PP_SPLINE_COEF + 4 * 999));
+    const double2 e23 = __ldg(reinterpret_cast<const double2*>(table + PP_SPLINE_COEF + 4 * 999) + 1);
+    v = e01.x + e01.y + e23.x + e23.y;
+    d = 0.0;
+  }
+  deriv = d;
+  return v;
+}

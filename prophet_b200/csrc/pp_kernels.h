@@ -47,6 +47,7 @@ struct NetDev {
   int node_off[PP_MAX_LAYERS];        // offset of layer l's nodes in the transfer-id list
   int P;
   unsigned tanh_layers;               // bit l set: every node of layer l (1-based, hidden) has the "tanh" transfer (id 1)
+  unsigned spline_layers;             // bit l set: every node of layer l has the "tanh_spline" transfer (id 2)
   const double* params;               // device, this element's parameters
   const int* tf;                      // device, transfer id per node
   const double* mean;                 // device [NG]
@@ -68,7 +69,7 @@ struct MlpArgs {
   double* partial;                    // [n_cta][P_total+3] out (train); this element's slice starts at p_off;
                                       //   fused mode also fills the 3 tail columns (sse, vsse, nval)
   int P_total, p_off;
-  const double* tanh_table;           // [1001 + 4000]
+  const double* tanh_table;           // [1002 + 4000], see pp_fastmath.cuh
   const void* dw_tiles;               // device table of weight-gradient tiles (ppk_mlp_num_dw_tiles)
   const void* dw_tiles2;              // device work table of the two-CTA fused kernel (ppk_mlp2_table), or nullptr
   double* scratch2;                   // two-CTA form: derivative scratch, ppk_mlp2_scratch_doubles(net) doubles

@@ -258,7 +258,7 @@ __device__ __noinline__ double pp_transfer_other(int id, double in, double* deri
     case 0: deriv = 1.0; { res = in; break; }
     case 2: {   // cubic-spline table on [-17,17] (Tables.h:74-128, Tables.cpp:212-221)
       const double* X = table;
-      const double* A = table + 1001;
+      const double* A = table + PP_SPLINE_COEF;
       if (in < X[0]) { deriv = 0.0; { res = A[3]; break; } }
       if (in >= X[1000]) { deriv = 0.0; { res = A[4 * 999] + A[4 * 999 + 1] + A[4 * 999 + 2] + A[4 * 999 + 3]; break; } }
       double m = 1000.0 / (X[1000] - X[0]);
@@ -1020,6 +1020,7 @@ struct Mlp2Plan {
   int w_off[PP_MAX_LAYERS], w_rows[PP_MAX_LAYERS];
   int x_off, h_off[PP_MAX_LAYERS];    // h_off[l]: H_l, l = 1 .. L-1 (later delta_l)
   int mu_off, is_off, exptab_off, cvec_off, erow_off, sttgt_off, red_off, mbar_off;
+  int spline[PP_MAX_LAYERS + 1];      // hidden layer l uses tanh_spline (else tanh)
   int stint_off_bytes, tab_off_bytes;
   size_t smem_bytes;
 };
@@ -1037,7 +1038,7 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
 {
   memset(&p, 0, sizeof(p));
   p.L = net.n_layers;
-  for (int l = 0; l <= p.L; l++) p.n[l] = net.sizes[l];
+  for (int l = 0; l <= p.L; l++) { p.n[l] = net.sizes[l]; p.spline[l] = ((net.tanh_layers >> l) & 1) ? 0 : (int)((net.spline_layers >> l) & 1); }
   size_t off = 0;
   for (int l = 0; l < p.L; l++) {
     p.kp[l] = mlp2_pitch(p.n[l] + 1);
@@ -1111,7 +1112,8 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
 // MODE: PP_MLP_FUSED (single pass over tiles of whole structures), PP_MLP_TRAIN (backward of the two-phase epoch: the
 // error factor of every atom's structure is given, rows may be gathered through a.rows), PP_MLP_FORWARD (energies).
 // NTW: n-tiles (8 columns) of the widest hidden layer; NLW: hidden-layer weight matrices (L - 1)
-template <int MODE, int NTW, int NLW>
+// SPLINE: some hidden layer uses tanh_spline (compiled out otherwise, so the all-tanh kernel keeps its registers)
+template <int MODE, int NTW, int NLW, bool SPLINE>
 __global__ void __launch_bounds__(MLP2_THREADS, 2)
 mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tmap)
 {
@@ -1275,14 +1277,27 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         tile_gemm<false, false, NTW>(acc, l == 0 ? X : sm + p.h_off[l], p.kp[l], sm + p.w_off[l], p.kp[l], warp,
                                      round_up(n_in + 1, 4), 0, NTW, lane);
         double* Hn = sm + p.h_off[l + 1] + (size_t)(rb + g) * p.kp[l + 1];
+        const bool spline_layer = SPLINE && p.spline[l + 1] != 0;      // uniform per layer: tanh_spline (the reference's default) or tanh
         double tv[NTW][2];
+        if (!spline_layer) {
 #pragma unroll
-        for (int nt = 0; nt < NTW; nt++) {
+          for (int nt = 0; nt < NTW; nt++) {
 #pragma unroll
-          for (int h = 0; h < 2; h++) {
-            double dv;
-            tv[nt][h] = pp_fast_tanh(acc[nt][h], dv, exptab);
-            dsc[(size_t)((l * NTW + nt) * 2 + h) * MLP2_THREADS + tid] = dv;      // T' of this activation, see `dsc`
+            for (int h = 0; h < 2; h++) {
+              double dv;
+              tv[nt][h] = pp_fast_tanh(acc[nt][h], dv, exptab);
+              dsc[(size_t)((l * NTW + nt) * 2 + h) * MLP2_THREADS + tid] = dv;      // T' of this activation, see `dsc`
+            }
+          }
+        } else {
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              double dv;
+              tv[nt][h] = pp_fast_tanh_spline(acc[nt][h], dv, a.tanh_table);
+              dsc[(size_t)((l * NTW + nt) * 2 + h) * MLP2_THREADS + tid] = dv;
+            }
           }
         }
         const bool last = (l == L - 2);
@@ -1485,7 +1500,7 @@ static bool mlp2_eligible(const NetDev& net, Mlp2Plan& plan, std::vector<DwTile>
   const int L = net.n_layers;
   if (L < 2 || L > 3) return false;
   for (int l = 1; l < L; l++)
-    if (!((net.tanh_layers >> l) & 1)) return false;
+    if (!(((net.tanh_layers | net.spline_layers) >> l) & 1)) return false;      // per layer: all tanh or all tanh_spline
   if (net.sizes[0] & 1) return false;
   if (net.sizes[L - 1] + 1 > 64) return false;
   const int NTW = mlp2_ntw(net);
@@ -1495,14 +1510,14 @@ static bool mlp2_eligible(const NetDev& net, Mlp2Plan& plan, std::vector<DwTile>
   return plan.smem_bytes <= 113 * 1024;
 }
 // Shared-memory plans of a network shape, computed once (the launchers run every epoch / MD step)
-struct CachedPlans { int n_layers, sizes[PP_MAX_LAYERS + 1]; unsigned tanh_layers; int TM; MlpPlan p1; bool ok2; Mlp2Plan p2; bool used; };
+struct CachedPlans { int n_layers, sizes[PP_MAX_LAYERS + 1]; unsigned tanh_layers, spline_layers; int TM; MlpPlan p1; bool ok2; Mlp2Plan p2; bool used; };
 static const CachedPlans& cached_plans(const NetDev& net)
 {
   static CachedPlans cache[8];
   static int next = 0;
   for (int i = 0; i < 8; i++) {
     const CachedPlans& c = cache[i];
-    if (c.used && c.n_layers == net.n_layers && c.tanh_layers == net.tanh_layers &&
+    if (c.used && c.n_layers == net.n_layers && c.tanh_layers == net.tanh_layers && c.spline_layers == net.spline_layers &&
         memcmp(c.sizes, net.sizes, sizeof(int) * (net.n_layers + 1)) == 0)
       return c;
   }
@@ -1511,6 +1526,7 @@ static const CachedPlans& cached_plans(const NetDev& net)
   c.used = true;
   c.n_layers = net.n_layers;
   c.tanh_layers = net.tanh_layers;
+  c.spline_layers = net.spline_layers;
   memset(c.sizes, 0, sizeof(c.sizes));
   memcpy(c.sizes, net.sizes, sizeof(int) * (net.n_layers + 1));
   c.TM = choose_tm(net, c.p1, nullptr);
@@ -1561,9 +1577,11 @@ int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t
   int grid = 2 * sm_count();
   if (mode == PP_MLP_FORWARD) grid = std::max(1, std::min(grid, n_tiles));     // gradient modes: every CTA writes its partial
   const int NTW = mlp2_ntw(net), NLW = net.n_layers - 1;
+  bool any_spline = false;
+  for (int l = 1; l < net.n_layers; l++) any_spline = any_spline || plan.spline[l] != 0;
 #define PP_LAUNCH2(MODE_, NTW_, NLW_)                                                                           \
   {                                                                                                             \
-    auto k = mlp_fused2_kernel<MODE_, NTW_, NLW_>;                                                              \
+    auto k = any_spline ? mlp_fused2_kernel<MODE_, NTW_, NLW_, true> : mlp_fused2_kernel<MODE_, NTW_, NLW_, false>;  \
     PP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem_bytes));        \
     k<<<grid, MLP2_THREADS, plan.smem_bytes, st>>>(a, plan, tmap);                                              \
   }
@@ -1808,11 +1826,11 @@ int ppk_column_stats(const double* G, int NG, const int* rows, int M, const int*
 // tanh spline table of the reference's Tables("tanh") (Tables.cpp:212-221): C2 cubic spline through tanh at the
 // knots -17 + 0.034 i, i = 0..1000.  The reference ships the coefficients as data; they are regenerated here
 // (natural-spline tridiagonal solve) and agree with the shipped table to ~7e-12 in the cubic coefficient.
-// Layout: X[1001] followed by a[1000][4] (cubic, quadratic, linear, constant in (x - X_i)).
+// Layout: X[1001], one pad, then a[1000][4] at PP_SPLINE_COEF (cubic, quadratic, linear, constant in (x - X_i)).
 void ppk_make_tanh_table(std::vector<double>& t)
 {
   const int N = 1000;
-  t.assign(1001 + 4 * N, 0.0);
+  t.assign(PP_SPLINE_COEF + 4 * N, 0.0);
   std::vector<double> y(N + 1), M2(N + 1, 0.0), cp(N + 1, 0.0), dp(N + 1, 0.0);
   for (int i = 0; i <= N; i++) { t[i] = (double)(-17000 + 34 * i) / 1000.0; y[i] = std::tanh(t[i]); }
   for (int i = 1; i < N; i++) {
@@ -1826,7 +1844,7 @@ void ppk_make_tanh_table(std::vector<double>& t)
   for (int i = N - 1; i >= 1; i--) M2[i] = dp[i] - cp[i] * M2[i + 1];
   for (int i = 0; i < N; i++) {
     double h = t[i + 1] - t[i];
-    double* a = &t[1001 + 4 * i];
+    double* a = &t[PP_SPLINE_COEF + 4 * i];
     a[0] = (M2[i + 1] - M2[i]) / (6.0 * h);
     a[1] = M2[i] / 2.0;
     a[2] = (y[i + 1] - y[i]) / h - h * (2.0 * M2[i] + M2[i + 1]) / 6.0;

@@ -156,9 +156,10 @@ def test_error_returns_are_messages_not_crashes():
         ctx.close()
 
 
-@pytest.mark.parametrize("hidden", [[8, 6], [40], [33, 17], [64, 40], [40, 40]])
+@pytest.mark.parametrize("hidden,transfer", [([8, 6], "tanh"), ([40], "tanh"), ([33, 17], "tanh"), ([64, 40], "tanh"), ([40, 40], "tanh"),
+                                             ([40, 40], "tanh_spline"), ([24], "tanh_spline")])
 @pytest.mark.parametrize("reps", [(2, 2, 2), (1, 1, 2), (1, 2, 3)])
-def test_two_cta_training_kernel_shapes_against_oracle_and_one_cta_form(hidden, reps):
+def test_two_cta_training_kernel_shapes_against_oracle_and_one_cta_form(hidden, transfer, reps):
     """mlp_fused2_kernel over network shapes (one / two hidden layers, 5- and 8-tile widths, ragged widths) and tile
     fillings (64-atom structures = one per tile, 16-atom = four per tile, 48-atom = a tile with 16 padding rows that
     the tensor copy fills with the NEXT structure's atoms): SSE and gradient against the oracle, and against the
@@ -171,6 +172,8 @@ def test_two_cta_training_kernel_shapes_against_oracle_and_one_cta_form(hidden, 
     structs = [synth.make_structure(cfg, 300 + s) for s in range(n)]
     tags = np.array([0, 0, 1, 0, 2, 0, 1], dtype=np.int32)
     net = synth.random_network(cfg, 14, 6)
+    if transfer == "tanh_spline":
+        net["params"][-3] += 30.0          # drive some pre-activations beyond the spline's last knot (|x| > 17: saturated ends)
     mean, scale = 0.2 * synth.normal(14, cfg.NG, 3), 0.5 + np.abs(synth.normal(14, cfg.NG, 4))
     fracs = [capi.cart_to_frac(c, x) for c, x, _, _, _ in structs]
     natoms = [len(z) for _, _, z, _, _ in structs]
@@ -178,7 +181,7 @@ def test_two_cta_training_kernel_shapes_against_oracle_and_one_cta_form(hidden, 
     ctx = capi.Context(0)
     try:
         ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
-        ctx.set_network(0, net["sizes"], net["params"], mean, scale)
+        ctx.set_network(0, net["sizes"], net["params"], mean, scale, transfer=transfer)
         ctx.add_structures(natoms, np.stack([s[0] for s in structs]), np.concatenate(fracs),
                            np.zeros(sum(natoms), dtype=np.int32), targets, tags)
         os.environ.pop("PP_MLP_ONE_CTA", None)
@@ -197,7 +200,7 @@ def test_two_cta_training_kernel_shapes_against_oracle_and_one_cta_form(hidden, 
         # oracle: descriptors from the GPU (checked elsewhere), network + epoch in plain C
         G = np.concatenate([ctx.get_descriptors(s).T for s in range(n)])        # atom-major [atoms][NG]
         off = np.concatenate([[0], np.cumsum(natoms)]).astype(np.int32)
-        onet = oracle.Net(net["sizes"], net["params"], mean, scale)
+        onet = oracle.Net(net["sizes"], net["params"], mean, scale, transfer=transfer)
         ref = oracle.epoch(off, np.zeros(sum(natoms), dtype=np.int32), G, targets, tags, [onet])
         assert abs(r2["SSE"] - ref["SSE"]) <= TOL * abs(ref["SSE"])
         assert rel_err(r2["gradient"], ref["gradient"]) < TOL

@@ -15,12 +15,16 @@ def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "C3"
     n_struct = int(sys.argv[2]) if len(sys.argv) > 2 else 2000
     cfg = synth.CONFIGS[name](n_struct)
+    if len(sys.argv) > 3:
+        cfg.transfer = sys.argv[3]          # e.g. tanh_spline (the reference's default transfer function)
     ctx = capi.Context(0)
     ctx.set_descriptors(len(cfg.elements), cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
     zmap = {z: i for i, z in enumerate(cfg.elements)}
     for e, z in enumerate(cfg.elements):
         net = synth.random_network(cfg, z, 1)
-        ctx.set_network(e, net["sizes"], net["params"], np.zeros(cfg.NG), np.ones(cfg.NG))
+        n_nodes = int(sum(net["sizes"][1:]))
+        ctx.set_network(e, net["sizes"], net["params"], np.zeros(cfg.NG), np.ones(cfg.NG),
+                        node_transfer=[cfg.transfer] * (n_nodes - 1) + ["linear"])
     n = cfg.natoms
     desc_ms = 0.0
     for first in range(0, n_struct, 500):
