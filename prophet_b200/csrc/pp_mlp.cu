@@ -300,6 +300,7 @@ __device__ __forceinline__ double pp_transfer(int id, double in, double& deriv, 
                                               const double* __restrict__ exptab)
 {
   if (id == 1) return pp_fast_tanh(in, deriv, exptab);   // tanh, asymptotic branch beyond |x| > 6 (NN_node.h:193-206)
+  if (id == 2) return pp_fast_tanh_spline(in, deriv, table);      // the reference's default
   return pp_transfer_other(id, in, &deriv, table);
 }
 
