@@ -107,6 +107,7 @@ std::vector<REAL> Optimizer::rprop()
     }
   } else if (N > 1) {
     const std::vector<REAL>& g1 = gradient[N - 2];
+    const std::vector<REAL>& g2 = gradient[N >= 3 ? N - 3 : 0];      // only read when N >= 3
     for (int i = 0; i < P; i++) {
       int sign_change = (int)(search_direction[i] * sign(g[i] * g1[i]));
       if (sign_change < 0) {
@@ -117,7 +118,7 @@ std::vector<REAL> Optimizer::rprop()
         rprop_step[i] = -sign(g[i]) * rprop_weights[i];
         x1[i] = x1[i] + rprop_step[i];
       } else if (sign_change == 0 && N >= 3) {
-        REAL D2 = (g[i] - gradient[N - 3][i]) / rprop_step[i];
+        REAL D2 = (g[i] - g2[i]) / rprop_step[i];
         if (D2 > 0) rprop_weights[i] = std::fabs(g[i]) / D2;
         if (rprop_weights[i] < rprop_weights_min) rprop_weights[i] = rprop_weights_min;
         if (rprop_weights[i] > rprop_weights_max && i != P - 1) rprop_weights[i] = rprop_weights_max;
