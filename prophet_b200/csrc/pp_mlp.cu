@@ -1008,8 +1008,10 @@ int ppk_mlp_dw_tile_bytes(void) { return (int)sizeof(DwTile); }
 // delta passes need no inter-warp synchronisation at all; CTA barriers only surround the weight-gradient products,
 // whose K dimension runs over all atoms of the tile.
 //
-// Eligibility (checked on the host, anything else runs the first form): single element, rows = consecutive atoms
-// with an even descriptor count (tensor copy), 1 or 2 hidden layers of tanh nodes no wider than 8*NTW, 64-atom tiles.
+// Eligibility (checked on the host, anything else runs the first form): an even descriptor count (16-byte rows for
+// the copy engine), 1 or 2 hidden layers, each all tanh or all tanh_spline, no wider than 8*NTW, a shared-memory plan of
+// at most 113 KB, 64-atom tiles.  FUSED additionally needs a single-element system (tiles of whole structures);
+// multi-element systems run FORWARD and TRAIN through it with their rows gathered one bulk copy per atom.
 #define MLP2_WARPS 8
 #define MLP2_THREADS (MLP2_WARPS * 32)
 #define MLP2_TM 64
