@@ -15,6 +15,10 @@
 //       Potential::train (Potential.cpp:607-672) so every per-iteration quantity can be dumped.
 //   ref_driver md <md_case.txt> <out.bin>
 //       Follows PairNN::settings/coeff/compute (pair_nn.cpp:499-526, 223-259, 112-188) without LAMMPS.
+//   ref_driver optq <spec.txt> <out.bin>
+//       spec.txt: P ncalls algorithm lambda_max ncycles threshold seed.  Drives the reference's Optimizer (through
+//       dummy network nodes) on the quadratic f(x) = sum_i a_i (x_i - b_i)^2 and dumps x every 500 calls, the call at
+//       which it converged and the next libc rand() value (the perturbation scheme draws random numbers).
 //   ref_driver ks <samples.txt> <out.bin>
 //       samples.txt: n1 v... n2 v...; calls Analysis::KS (Analysis.cpp:149-202) and dumps D and p.
 
@@ -329,6 +333,47 @@ static int run_md(const string& case_file)
   return 0;
 }
 
+static int run_optq(const string& file)
+{
+  ifstream in(file.c_str());
+  if (!in.is_open()) { fprintf(stderr, "cannot open %s\n", file.c_str()); return 2; }
+  int P = 0, ncalls = 0, ncycles = 1, seed = 1;
+  string algorithm;
+  double lambda_max = 0, threshold = 0;
+  in >> P >> ncalls >> algorithm >> lambda_max >> ncycles >> threshold >> seed;
+  srand(seed);
+  Functional_params F;
+  F.my_training_algorithm = algorithm;
+  F.my_lambda_max = lambda_max;
+  F.my_Ncycles = ncycles;
+  F.my_threshold = threshold;
+  F.my_Niterations = 1 << 30;
+  F.my_Nprint = 1 << 30;
+  Parallel* mpi = new Parallel();
+  // one dummy node with P-1 inputs holds the P parameters
+  vector<Network_node*> nodes(1, new Neural_network_node(P - 1, "linear"));
+  Optimizer* opt = new Optimizer(mpi, F, 1);
+  opt->init(nodes);
+  opt->internal_init();
+  vector<REAL> a(P), b(P);
+  for (int i = 0; i < P; i++) { a[i] = 0.5 + 0.37 * ((i * 7) % 5); b[i] = 0.25 * ((i * 3) % 7) - 0.6; }
+  put_d("x0", opt->get_parameters());
+  int converged_at = -1;
+  for (int call = 0; call < ncalls; call++) {
+    vector<REAL> x = opt->get_parameters();
+    REAL f = 0;
+    vector<REAL> g(P);
+    for (int i = 0; i < P; i++) { const REAL d = x[i] - b[i]; f += a[i] * d * d; g[i] = 2 * a[i] * d; }
+    opt->update_network(f, g);
+    if ((call + 1) % 500 == 0) put_d(idx("x", call + 1), opt->get_parameters());
+    if (opt->is_converged()) { converged_at = call + 1; break; }
+  }
+  put_d("x_final", opt->get_parameters());
+  put_scalar("converged_at", converged_at);
+  put_scalar("next_rand", (double)rand());
+  return 0;
+}
+
 static int run_ks(const string& file)
 {
   ifstream in(file.c_str());
@@ -360,6 +405,7 @@ int main(int argc, char** argv)
   if (mode == "train") rc = run_train(argv[2], argc > 4 ? atoi(argv[4]) : 0);
   else if (mode == "md") rc = run_md(argv[2]);
   else if (mode == "ks") rc = run_ks(argv[2]);
+  else if (mode == "optq") rc = run_optq(argv[2]);
   fclose(g_out);
   return rc;
 }

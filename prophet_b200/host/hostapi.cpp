@@ -13,7 +13,7 @@ using namespace pph;
 extern "C" {
 
 // ---- Rprop driven step by step with caller-supplied gradients -------------------------------------------------
-struct pph_opt { Parallel mpi; FunctionalParams F; Optimizer* opt; };
+struct pph_opt { Parallel mpi; FunctionalParams F; Optimizer* opt; int nsys; };
 
 // line_min_epsilon / debug / sd_momentum as the input_file keys of those names would set them
 void* pph_optimizer_create2(int P, const double* x0, const char* algorithm, int Nsystems, double line_min_epsilon,
@@ -32,11 +32,28 @@ void* pph_optimizer_create2(int P, const double* x0, const char* algorithm, int 
   h->F.debug = debug;
   h->F.sd_momentum = sd_momentum;
   h->F.Niterations = 1 << 30;
+  h->nsys = Nsystems;
   h->opt = new Optimizer(&h->mpi, h->F, Nsystems);
   h->opt->do_print = false;
   h->opt->init(std::vector<REAL>(x0, x0 + P));
   return h;
 }
+// options of a test optimizer: lambda_max / Ncycles / threshold as the input_file keys, printing on (the perturbation
+// scheme only runs while the optimizer prints, as in the reference); call before the first step
+void pph_optimizer_configure(void* hv, double lambda_max, int ncycles, double threshold, int do_print, int P, const double* x0)
+{
+  pph_opt* h = (pph_opt*)hv;
+  const int nsys = h->nsys;
+  delete h->opt;
+  h->F.lambda_max = lambda_max;
+  h->F.Ncycles = ncycles;
+  h->F.threshold = threshold;
+  h->opt = new Optimizer(&h->mpi, h->F, nsys);
+  h->opt->do_print = do_print != 0;
+  h->opt->init(std::vector<REAL>(x0, x0 + P));
+}
+int pph_optimizer_converged(void* hv) { return ((pph_opt*)hv)->opt->is_converged() ? 1 : 0; }
+double pph_optimizer_alpha(void* hv) { return ((pph_opt*)hv)->opt->alpha(); }
 void pph_optimizer_step(void* hv, int P, double sse, const double* grad, double* x_out)
 {
   pph_opt* h = (pph_opt*)hv;

@@ -150,6 +150,8 @@ class Optimizer {
   int iteration() const { return iteration_counter; }
   REAL get_error() const { return Errors.back(); }
   const std::vector<REAL>& parameters() const { return x.back(); }
+  REAL alpha() const { return my_alpha; }          // perturbation amplitude (Optimizer.h:130-137); unused by Potential::train
+  REAL dphi_dt() const { return my_dphi_dt; }
   bool do_print;
   // the algorithms, exposed for tests
   std::vector<REAL> rprop();
@@ -175,6 +177,11 @@ class Optimizer {
   std::deque<std::vector<REAL> > x, gradient;
   std::deque<REAL> Errors;
   std::vector<REAL> search_direction, rprop_weights, rprop_step;
+  // perturbation ("global optimizer") scheme, lambda_max != 0 (Optimizer.cpp:915-938, 1008-1043)
+  bool global_optimizer;
+  REAL my_alpha, my_dphi_dt, alpha_max, current_alpha_max, phase_shift, dalpha_dt, E_best, g_best, E_min;
+  int cycles, t0;
+  std::vector<REAL> x_best;
   // L-BFGS / Brent line minimisation state (Optimizer.h:215-234)
   int BFGS_Nmax;
   REAL convergence, line_last_E, line_last_alpha, line_last_g, brent_c, brent_g_c, brent_d;

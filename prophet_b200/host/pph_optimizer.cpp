@@ -4,6 +4,7 @@
 // identical step and the reference's Bcast of the new parameters (Optimizer.cpp:957) is not needed.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <limits>
 
 #include "pph.h"
@@ -12,6 +13,14 @@ namespace pph {
 
 template <typename T>
 static inline int sign(T v) { return (T(0) < v) - (v < T(0)); }
+
+// RAND::Normal (Common.h:72-75): libc rand(), first draw under the logarithm, second in the cosine
+static REAL rand_normal_opt(REAL mean, REAL sd)
+{
+  const REAL u1 = (REAL)rand() / RAND_MAX;
+  const REAL u2 = (REAL)rand() / RAND_MAX;
+  return mean + sd * std::sqrt(-2.0 * std::log(u1)) * std::cos(2.0 * 3.141592653589793 * u2);
+}
 
 static REAL dot(const std::vector<REAL>& a, const std::vector<REAL>& b)
 {
@@ -50,6 +59,18 @@ Optimizer::Optimizer(Parallel* mpi_in, const FunctionalParams& params, int Nsyst
   alpha1 = lambda0;
   rprop_weights_max = 0.5;
   rprop_weights_min = 1000.0 * std::numeric_limits<REAL>::epsilon();
+  my_alpha = 0.0;
+  my_dphi_dt = 0.0;
+  global_optimizer = true;
+  alpha_max = (int)F.lambda_max;      // the reference's accessor returns int (Functional_params.h:198-201): values below 1 switch the scheme off
+  current_alpha_max = alpha_max;
+  phase_shift = 0.0;
+  dalpha_dt = 0;
+  cycles = 0;
+  t0 = 0;
+  E_best = 9e9;
+  g_best = 0.0;
+  E_min = 0.0;
   BFGS_Nmax = 77;
   convergence = 100 * std::numeric_limits<REAL>::epsilon();
   line_last_E = line_last_alpha = line_last_g = brent_c = brent_g_c = brent_d = 0.0;
@@ -408,8 +429,32 @@ void Optimizer::update_network(REAL Error, const std::vector<REAL>& grad)
     my_is_converged = true;
     line_min = true;
   } else if (norm < my_threshold) {
-    my_is_converged = true;       // lambda_max = 0: no perturbation phase (the "global optimizer" is not in this build)
-    line_min = true;
+    if (alpha_max != 0) {
+      // lambda_max given: instead of stopping, a slow sine of amplitude lambda_max is switched on for half a period
+      // (Optimizer.cpp:915-938).  Potential::train never reads alpha(), so on this path the scheme only decides WHEN
+      // training stops; it is reproduced for that and for the random numbers it draws.
+      if (my_alpha == 0) {
+        if (global_optimizer) {
+          if (SSE < E_best) { E_best = SSE; g_best = norm; x_best = x.back(); }
+          if (mpi->io_node()) std::cout << "----- converged; turning on perturbation -----" << std::endl;
+          E_min = SSE;
+          dalpha_dt = 3.14159265358979e-04;
+          t0 = iteration_counter;
+        } else {
+          my_is_converged = true;
+          line_min = true;
+          if (SSE > E_best) {
+            if (mpi->io_node()) std::cout << "===== resetting to previous best =====" << std::endl;
+            SSE = E_best;
+            norm = g_best;
+            x.push_back(x_best);      // set_parameters(x_best): the caller reads parameters()
+          }
+        }
+      }
+    } else {
+      my_is_converged = true;
+      line_min = true;
+    }
   }
   if (!my_is_converged) x.push_back(next_x());
   if (x.size() > 20) {
@@ -431,6 +476,33 @@ void Optimizer::update_network(REAL Error, const std::vector<REAL>& grad)
     my_is_checkpoint = ((iteration_counter - 1) % my_Ncheckpoint ? false : true);
     if (my_Tbackup) my_is_backup = ((iteration_counter - 1) % my_Nbackup ? false : true);
     if (iteration_counter == 1) { my_is_checkpoint = false; my_is_backup = false; }
+  }
+  if (do_print && dalpha_dt) {      // Optimizer.cpp:1008-1043 (inside the reference's do_print branch)
+    if (SSE < 0.985 * E_min && phase_shift == 0) {
+      if (mpi->io_node()) std::cout << "----- transition detected -----" << std::endl;
+      current_alpha_max = my_alpha;
+      t0 = iteration_counter;
+      cycles = 0;
+      phase_shift = 1.57079632679490;
+      dalpha_dt *= 2;
+    }
+    my_alpha = current_alpha_max * std::sin(dalpha_dt * (iteration_counter - t0) + phase_shift);
+    my_dphi_dt = 0.5 * rand_normal_opt(1, 0.15) * 0.0314159 / 5;
+    if (my_alpha <= 0) {
+      if (current_alpha_max == alpha_max) {
+        if (mpi->io_node()) std::cout << "----- No transition found; completing optimization -----" << std::endl;
+        cycles++;
+        if (cycles == F.Ncycles) global_optimizer = false;
+        my_alpha = 0;
+        dalpha_dt = 0;
+      } else {
+        if (mpi->io_node()) std::cout << "----- continuing optimization -----" << std::endl;
+        phase_shift = 0;
+        my_alpha = 0;
+        current_alpha_max = alpha_max;
+        dalpha_dt = 0;
+      }
+    }
   }
 }
 

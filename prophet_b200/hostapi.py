@@ -46,6 +46,23 @@ class Optimizer:
                                                   line_min_epsilon or 0.0, debug or 0.0,
                                                   sd_momentum or 0.0)
 
+    def configure(self, x0, lambda_max=0.0, ncycles=1, threshold=0.0, do_print=False):
+        """Re-create the optimizer with lambda_max / Ncycles / threshold (input_file keys) and printing on or off."""
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        L = lib()
+        L.pph_optimizer_configure.argtypes = [ctypes.c_void_p, ctypes.c_double, ctypes.c_int, ctypes.c_double, ctypes.c_int,
+                                              ctypes.c_int, _d]
+        L.pph_optimizer_converged.argtypes = [ctypes.c_void_p]
+        L.pph_optimizer_alpha.argtypes = [ctypes.c_void_p]
+        L.pph_optimizer_alpha.restype = ctypes.c_double
+        L.pph_optimizer_configure(self._h, lambda_max, ncycles, threshold, int(do_print), self.P, x0.ctypes.data_as(_d))
+
+    def converged(self):
+        return bool(lib().pph_optimizer_converged(self._h))
+
+    def alpha(self):
+        return lib().pph_optimizer_alpha(self._h)
+
     def step(self, sse, grad):
         grad = np.ascontiguousarray(grad, dtype=np.float64)
         x = np.zeros(self.P)

@@ -387,6 +387,26 @@ def case_ks():
         shutil.rmtree(cwd, ignore_errors=True)
 
 
+def case_opt_perturbation():
+    """The perturbation ("global optimizer") scheme of Optimizer::update_network (Optimizer.cpp:915-938, 1008-1043) on a
+    quadratic objective, P = 9, Rprop, lambda_max = 1.5 (the accessor truncates it to 1), threshold 5e-3, seed 77:
+    the run turns the perturbation on twice, detects a transition, continues, finds none, and stops at call 12560."""
+    cwd = tempfile.mkdtemp(prefix="golden_optq_")
+    try:
+        spec = dict(P=9, ncalls=40000, algorithm="rprop", lambda_max=1.5, ncycles=1, threshold=5e-3, seed=77)
+        with open(os.path.join(cwd, "spec.txt"), "w") as f:
+            f.write("%(P)d %(ncalls)d %(algorithm)s %(lambda_max)r %(ncycles)d %(threshold)r %(seed)d\n" % spec)
+        run_driver(["optq", "spec.txt", "out.bin"], cwd)
+        d = dict(refdump.load(os.path.join(cwd, "out.bin")))
+        for k, v in spec.items():
+            d["spec_" + k] = np.array(v)
+        np.savez_compressed(os.path.join(OUT, "opt_perturbation.npz"), **d)
+        print("wrote opt_perturbation.npz: converged at call %d" % int(d["converged_at"][0]))
+    finally:
+        shutil.rmtree(cwd, ignore_errors=True)
+
+
+CASES["opt_perturbation"] = case_opt_perturbation
 CASES["ks"] = case_ks
 CASES["tio2_md_fe"] = case_tio2_md_fe
 CASES["opt_bfgs"] = case_opt_bfgs

@@ -52,6 +52,41 @@ def test_line_search_algorithms_reproduce_reference_calls_exactly(name, algorith
         assert all(same[:133]) and not same[133]
 
 
+def test_perturbation_scheme_follows_the_reference(capfd):
+    """lambda_max != 0 (Optimizer.cpp:915-938, 1008-1043): reaching the threshold switches a slow sine perturbation on
+    instead of stopping; the scheme decides when training ends and draws random numbers.  On the quadratic objective of
+    the golden run (ref_driver optq) the parameters every 500 calls, the call at which the optimizer stops, the final
+    parameters and the state of libc's rand() stream must all equal the reference's."""
+    import ctypes
+    _ensure_built()
+    d = np.load(os.path.join(GOLDEN_DIR, "opt_perturbation.npz"))
+    P = int(d["spec_P"]); seed = int(d["spec_seed"])
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(seed)
+    for _ in range(2 * P):
+        libc.rand()                       # the reference's node constructor drew P normal deviates for the initial weights
+    a = np.array([0.5 + 0.37 * ((i * 7) % 5) for i in range(P)])
+    b = np.array([0.25 * ((i * 3) % 7) - 0.6 for i in range(P)])
+    opt = hostapi.Optimizer(d["x0"], "rprop", 1)
+    opt.configure(d["x0"], lambda_max=float(d["spec_lambda_max"]), ncycles=int(d["spec_ncycles"]),
+                  threshold=float(d["spec_threshold"]), do_print=True)
+    x = d["x0"].copy()
+    stop = int(d["converged_at"][0])
+    for call in range(1, stop + 1):
+        f = 0.0                            # accumulated in the reference's order
+        for i in range(P):
+            f += a[i] * (x[i] - b[i]) * (x[i] - b[i])
+        x = opt.step(f, 2 * a * (x - b))
+        if call % 500 == 0:
+            assert np.array_equal(x, d["x.%d" % call]), call
+        assert opt.converged() == (call == stop), call
+    assert np.array_equal(x, d["x_final"])
+    assert libc.rand() == int(d["next_rand"][0])
+    out = capfd.readouterr().out
+    for msg in ("converged; turning on perturbation", "transition detected", "continuing optimization", "No transition found"):
+        assert msg in out
+
+
 def test_approximate_ks_statistic_matches_reference():
     """The appendix of `-validate` (Potential.cpp:1107-1117 -> Analysis::KS, Analysis.cpp:149-202)."""
     _ensure_built()
