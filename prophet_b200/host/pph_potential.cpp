@@ -399,6 +399,11 @@ REAL Potential::train()
     long long nval = 0;
     // the loop over systems and atoms, the per-structure error, the gradient assembly and the Reduce of
     // Optimizer::update_network all happen inside this one call
+    // `sgd = true` only shuffles the order in which the reference visits its systems within a full-batch pass
+    // (Potential.cpp:632-634): the sums are the same up to rounding, but std::random_shuffle draws Nlocal - 1 numbers
+    // from libc rand() per epoch, which whatever reads that stream later (-optimize) must see
+    if (params.SGD)
+      for (int k = 1; k < Nlocal; k++) (void)rand();
     PPH_CALL(pp_epoch(ctx, opt.parameters().data(), gradient.data(), &SSE, &vSSE, &nval));
     opt.set_val_sse(vSSE, nval);
     opt.update_network(SSE, gradient);
