@@ -203,7 +203,8 @@ int pph_auto_rows(double Rcut, int Nradial, int Nangular, double* G2_out, int* n
 
 // ---- pair_style nn through the LAMMPS stand-in: settings + coeff + compute on caller arrays ----------------------
 int pph_pair_nn_run(double Rcut, int ntypes, const int* coeff_types, const char** coeff_files, int nlocal, int nghost,
-                    double* x, int* type, const int* numneigh, const int* neigh_flat, double* f, double* eatom, double* eng_vdwl)
+                    double* x, int* type, const int* numneigh, const int* neigh_flat, double* f, double* eatom, double* eng_vdwl,
+                    int* restart_check)
 {
   using namespace LAMMPS_NS;
   const int ntotal = nlocal + nghost;
@@ -212,7 +213,8 @@ int pph_pair_nn_run(double Rcut, int ntypes, const int* coeff_types, const char*
   Atom atom = {xp.data(), fp.data(), type, nlocal, nghost, ntypes};
   Comm comm = {0};
   Error err;
-  LAMMPS lmp = {&atom, &comm, &err};
+  Neighbor neighbor;
+  LAMMPS lmp = {&atom, &comm, &err, &neighbor};
   std::vector<int> ilist(nlocal);
   std::vector<int*> first(nlocal);
   std::vector<int> nn(numneigh, numneigh + nlocal);
@@ -234,10 +236,38 @@ int pph_pair_nn_run(double Rcut, int ntypes, const int* coeff_types, const char*
     char* carg[2] = {tbuf, (char*)coeff_files[i]};
     pair.coeff(2, carg);
   }
+  pair.init_style();
+  if (!(neighbor.skin == 1.0 && neighbor.every == 10 && neighbor.delay == 0 && neighbor.requests[0]->full == 1 &&
+        neighbor.requests[0]->half == 0 && neighbor.requests[0]->id == 1))
+    return 2;
+  double fdummy = 0;
+  if (pair.single(0, 0, 1, 1, 1.0, 0.0, 0.0, fdummy) != 1) return 3;
   pair.init_list(1, &list);
   pair.eatom = eatom;
   pair.compute(3, 0);
   *eng_vdwl = pair.eng_vdwl;
+  if (restart_check) {
+    // write_restart -> a fresh PairNN -> read_restart -> compute: the energies must be the same numbers
+    *restart_check = 1;
+    FILE* rf = tmpfile();
+    if (!rf) return 4;
+    pair.write_restart(rf);
+    rewind(rf);
+    PairNN again(&lmp);
+    again.read_restart(rf);
+    fclose(rf);
+    std::vector<double> f2(3 * (size_t)ntotal, 0.0), e2(nlocal, 0.0);
+    std::vector<double*> fp2(ntotal);
+    for (int i = 0; i < ntotal; i++) fp2[i] = f2.data() + 3 * (size_t)i;
+    atom.f = fp2.data();
+    again.init_list(1, &list);
+    again.eatom = e2.data();
+    again.compute(3, 0);
+    atom.f = fp.data();
+    if (again.eng_vdwl != pair.eng_vdwl) *restart_check = 0;
+    for (int i = 0; i < nlocal; i++)
+      if (e2[i] != eatom[i]) *restart_check = 0;
+  }
   return 0;
 }
 

@@ -25,6 +25,21 @@ struct NeighList {
 
 struct Comm { int me; };
 
+// neighbour-list request as pair_nn.cpp:262-285 fills it in (pre-2020 LAMMPS API)
+struct NeighRequest { int pair, id, half, full, occasional; };
+struct Neighbor {
+  double cutneighmin, cutneighmax, skin;
+  int delay, every;
+  NeighRequest* requests[4];
+  NeighRequest storage[4];
+  int nrequest;
+  Neighbor() : cutneighmin(0), cutneighmax(0), skin(0), delay(0), every(0), nrequest(0)
+  {
+    for (int i = 0; i < 4; i++) requests[i] = &storage[i];
+  }
+  int request(void*, int) { return nrequest < 3 ? nrequest++ : 3; }
+};
+
 struct Error {
   void all(const char* file, int line, const char* msg)
   {
@@ -37,12 +52,14 @@ struct LAMMPS {
   Atom* atom;
   Comm* comm;
   Error* error;
+  Neighbor* neighbor;
 };
 
 class Pair {
  public:
-  explicit Pair(LAMMPS* lmp) : lmp_(lmp), atom(lmp->atom), comm(lmp->comm), error(lmp->error), list(NULL)
+  explicit Pair(LAMMPS* lmp) : lmp_(lmp), atom(lmp->atom), comm(lmp->comm), error(lmp->error), neighbor(lmp->neighbor), list(NULL)
   {
+    instance_me = 0;
     eng_vdwl = 0.0;
     eatom = NULL;
     eflag_global = eflag_atom = vflag_fdotr = evflag = 0;
@@ -74,7 +91,9 @@ class Pair {
   Atom* atom;
   Comm* comm;
   Error* error;
+  Neighbor* neighbor;
   NeighList* list;
+  int instance_me;
   int allocated;
   int** setflag;
   double** cutsq;

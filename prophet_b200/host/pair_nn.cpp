@@ -43,9 +43,76 @@ void PairNN::coeff(int narg, char** arg)
   out_mean = net.params.output_mean;
   if (comm->me == 0) printf("Initializing atom type %d with file %s\n", this_type, arg[1]);
   coeff_types.push_back(this_type);
+  coeff_files.push_back(arg[1]);
   coeff_nets.push_back(net);
   ready = false;
   if (coeff_nets.size() == net.params.atomic_symbols.size()) finish_setup();
+}
+
+void PairNN::init_style()
+{
+  // the reference overrides the user's neighbour settings (pair_nn.cpp:268-281): skin 1.0, list rebuilt every 10
+  // steps without delay, one FULL list with id 1
+  neighbor->cutneighmin = 1.0;
+  neighbor->cutneighmax = Rcut;
+  neighbor->delay = 0;
+  neighbor->every = 10;
+  neighbor->skin = 1.0;
+  const int irequest = neighbor->request(this, instance_me);
+  neighbor->requests[irequest]->pair = 1;
+  neighbor->requests[irequest]->id = 1;
+  neighbor->requests[irequest]->half = 0;
+  neighbor->requests[irequest]->full = 1;
+  neighbor->requests[irequest]->occasional = 0;
+}
+
+void PairNN::write_restart(FILE* fp)
+{
+  write_restart_settings(fp);
+  if (comm->me != 0) return;
+  double rc = Rcut;
+  fwrite(&rc, sizeof(double), 1, fp);
+  for (size_t i = 0; i < coeff_types.size(); i++) {
+    int size = (int)coeff_files[i].size(), type = coeff_types[i];
+    fwrite(&type, sizeof(int), 1, fp);
+    fwrite(&size, sizeof(int), 1, fp);
+    fwrite(coeff_files[i].data(), sizeof(char), (size_t)size, fp);
+  }
+}
+
+void PairNN::read_restart(FILE* fp)
+{
+  read_restart_settings(fp);
+  // Rank 0 reads, everybody replays (the reference broadcasts each item with MPI_Bcast over `world`; with LAMMPS'
+  // MPI that is where the three Bcast calls go -- the stand-in build is single rank)
+  double rc = 0.0;
+  if (comm->me == 0 && fread(&rc, sizeof(double), 1, fp) != 1) error->all(FLERR, "pair_style nn: truncated restart record");
+#ifndef PPH_LAMMPS_STUB
+  MPI_Bcast(&rc, 1, MPI_DOUBLE, 0, world);
+#endif
+  char num[64];
+  snprintf(num, sizeof(num), "%.17g", rc);
+  char* sarg[1] = {num};
+  settings(1, sarg);
+  for (int i = 1; i <= atom->ntypes; i++) {
+    int type = 0, size = 0;
+    if (comm->me == 0 && (fread(&type, sizeof(int), 1, fp) != 1 || fread(&size, sizeof(int), 1, fp) != 1))
+      error->all(FLERR, "pair_style nn: truncated restart record");
+#ifndef PPH_LAMMPS_STUB
+    MPI_Bcast(&type, 1, MPI_INT, 0, world);
+    MPI_Bcast(&size, 1, MPI_INT, 0, world);
+#endif
+    std::string name((size_t)size, '\0');
+    if (comm->me == 0 && size > 0 && fread(&name[0], sizeof(char), (size_t)size, fp) != (size_t)size)
+      error->all(FLERR, "pair_style nn: truncated restart record");
+#ifndef PPH_LAMMPS_STUB
+    MPI_Bcast(&name[0], size, MPI_CHAR, 0, world);
+#endif
+    char tnum[16];
+    snprintf(tnum, sizeof(tnum), "%d", type);
+    char* carg[2] = {tnum, &name[0]};
+    coeff(2, carg);
+  }
 }
 
 void PairNN::finish_setup()

@@ -29,8 +29,18 @@ class PairNN : public Pair {
   virtual void compute(int eflag, int vflag);
   virtual void settings(int narg, char** arg);      // exactly one argument: Rcut (pair_nn.cpp:502-507)
   virtual void coeff(int narg, char** arg);         // type file [cut]       (pair_nn.cpp:226-234)
+  void init_style();                                // full list, skin 1.0, rebuilt every 10 steps (pair_nn.cpp:262-285)
   void init_list(int id, NeighList* ptr) { if (id == 1) list = ptr; }
   double init_one(int, int) { return Rcut; }
+  // restart record (pair_nn.cpp:322-398): Rcut, then per pair_coeff line its type, the length of the checkpoint file
+  // name and the name itself -- reading it replays settings() and coeff()
+  void write_restart(FILE* fp);
+  void read_restart(FILE* fp);
+  void write_restart_settings(FILE*) {}             // nothing, as in the reference (:405-447)
+  void read_restart_settings(FILE*) {}
+  void write_data(FILE*) {}                         // nothing, as in the reference (:455-474)
+  void write_data_all(FILE*) {}
+  double single(int, int, int, int, double, double, double, double&) { return 1; }      // pair_nn.cpp:480-485
   double energy_shift() const { return out_mean; }
 
  private:
@@ -42,6 +52,7 @@ class PairNN : public Pair {
   std::vector<double> type_free_energy, eatom_tmp;
   std::vector<char> type_has_free_energy;
   std::vector<int> coeff_types;
+  std::vector<std::string> coeff_files;       // as given to pair_coeff, for the restart record
   std::vector<pph::HostNet> coeff_nets;
   std::vector<long long> offsets;
   std::vector<int> flat;

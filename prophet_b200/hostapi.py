@@ -144,9 +144,10 @@ def pair_nn_run(rcut, coeff_types, coeff_files, x, types, nlocal, numneigh, neig
     numneigh = np.ascontiguousarray(numneigh, dtype=np.int32); neigh_flat = np.ascontiguousarray(neigh_flat, dtype=np.int32)
     ct = np.ascontiguousarray(coeff_types, dtype=np.int32)
     files = (ctypes.c_char_p * len(coeff_files))(*[f.encode() for f in coeff_files])
-    f = np.zeros_like(x); eatom = np.zeros(nlocal); eng = ctypes.c_double()
+    f = np.zeros_like(x); eatom = np.zeros(nlocal); eng = ctypes.c_double(); restart_ok = ctypes.c_int(0)
     rc = lib().pph_pair_nn_run(ctypes.c_double(rcut), len(ct), ct.ctypes.data_as(_i), files, nlocal, len(x) - nlocal,
                                x.ctypes.data_as(_d), types.ctypes.data_as(_i), numneigh.ctypes.data_as(_i),
-                               neigh_flat.ctypes.data_as(_i), f.ctypes.data_as(_d), eatom.ctypes.data_as(_d), ctypes.byref(eng))
-    assert rc == 0
-    return dict(f=f, eatom=eatom, eng_vdwl=eng.value)
+                               neigh_flat.ctypes.data_as(_i), f.ctypes.data_as(_d), eatom.ctypes.data_as(_d), ctypes.byref(eng),
+                               ctypes.byref(restart_ok))
+    assert rc == 0, rc      # 2: init_style did not request the reference's neighbour settings, 3: single(), 4: no temp file
+    return dict(f=f, eatom=eatom, eng_vdwl=eng.value, restart_ok=bool(restart_ok.value))

@@ -140,6 +140,9 @@ def test_pair_style_nn_through_lammps_stand_in(name, tmp_path):
     assert rel_err(r["eatom"], c.d["eatom"]) < 1e-10
     assert abs(r["eng_vdwl"] - c.d["etotal"][0]) < 1e-10 * abs(c.d["etotal"][0])
     assert rel_err(r["f"], c.d["f"]) < 1e-10
+    # init_style asked for the reference's neighbour settings (checked inside the harness), and a second PairNN built by
+    # read_restart from the first one's write_restart record (pair_nn.cpp:322-398) computes the same energies
+    assert r["restart_ok"]
 
 
 def test_pair_style_nn_free_energy_shift(tmp_path):
