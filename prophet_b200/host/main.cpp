@@ -17,8 +17,8 @@ int main(int argc, char* argv[])
     else if (!strcmp(argv[i], "-train")) run_type = "train";
     else if (!strcmp(argv[i], "-validate")) run_type = "validate";
     else if (!strcmp(argv[i], "-optimize")) run_type = "optimize";
-    else if (!strcmp(argv[i], "-init") || !strcmp(argv[i], "-forces"))
-      PPH_ERROR(std::string("Command line argument \"") + argv[i] + "\" belongs to a workflow outside this build");
+    else if (!strcmp(argv[i], "-init")) run_type = "initialize";      // accepted; for a potential the reference then
+    else if (!strcmp(argv[i], "-forces")) run_type = "forces";        // only sets everything up and exits (main.cpp:32,43,66-77)
     else PPH_ERROR(std::string("Command line argument \"") + argv[i] + "\" not recognized");
   }
   pph::Parallel mpi;
