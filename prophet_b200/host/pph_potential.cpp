@@ -257,6 +257,25 @@ Potential::Potential(const Setup& setup, Parallel* mpi_in) : mpi(mpi_in), params
         }
         PPH_CALL(pp_add_structures(ctx, b1 - b0, nat.data(), cells.data(), frac.data(), elem.data(), tgt.data(), tg.data()));
       }
+      if (params.print_gvectors) {
+        // print_gvector = true (Potential.cpp:114-136): "<rank>.gvector", one line of NG comma-terminated values per
+        // atom, a blank line after every structure, stream default precision
+        std::ostringstream name;
+        name << mpi->rank() << ".gvector";
+        std::ofstream gv(name.str().c_str());
+        const int NG = pp_num_descriptors(ctx);
+        std::vector<double> G;
+        for (int s = 0; s < Nlocal; s++) {
+          const int n = structs[s].natoms();
+          G.assign((size_t)NG * n, 0.0);
+          PPH_CALL(pp_get_descriptors(ctx, s, G.data()));
+          for (int a = 0; a < n; a++) {
+            for (int k = 0; k < NG; k++) gv << G[(size_t)k * n + a] << ",";
+            gv << "\n";
+          }
+          gv << "\n";
+        }
+      }
     }
     params.current_atom_type = atomic_symbol(Z);
     net.params = params;

@@ -249,3 +249,33 @@ def test_cli_optimize_follows_reference_monte_carlo(tmp_path):
     assert len(ga) == len(gb) == 10
     for ra, rb in zip(ga, gb):
         assert len(ra) == len(rb) and np.allclose(ra, rb, rtol=1e-5), (ra, rb)
+
+
+@pytest.mark.skipif(not os.path.exists(REF_CLI), reason="oracle/_ref/PROPhet not built")
+def test_cli_print_gvector_file_matches_reference(tmp_path):
+    """print_gvector = true (Potential.cpp:114-136): both programs dump every atom's descriptors to 0.gvector."""
+    cfg = synth.CONFIGS["C3"](3)
+    ours = tmp_path / "ours"; ref = tmp_path / "ref"
+    for d in (ours, ref):
+        d.mkdir()
+        _write_case(str(d), cfg, 3, [0, 0, 1], [5, 4], seed=16, niter=1, extra=("print_gvector = true",))
+    _run(REF_CLI, ["-in", "input_file", "-train"], str(ref))
+    _run(hostapi.CLI_PATH, ["-in", "input_file", "-train"], str(ours))
+
+    def load(path):
+        blocks, cur = [], []
+        for line in open(path):
+            if line.strip() == "":
+                if cur:
+                    blocks.append(np.array(cur)); cur = []
+            else:
+                cur.append([float(v) for v in line.strip().rstrip(",").split(",")])
+        if cur:
+            blocks.append(np.array(cur))
+        return blocks
+
+    a, b = load(str(ours / "0.gvector")), load(str(ref / "0.gvector"))
+    assert len(a) == len(b) == 3
+    for x, y in zip(a, b):
+        assert x.shape == y.shape == (cfg.natoms, cfg.NG)
+        assert np.allclose(x, y, rtol=2e-5, atol=1e-12)
