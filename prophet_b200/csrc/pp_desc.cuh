@@ -462,17 +462,27 @@ __device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, con
     double acc[NPAD];
 #pragma unroll
     for (int i = 0; i < NPAD; i++) acc[i] = 0.0;
-    for (int a = lane; a < m1; a += 32) {
+    for (int a0 = 0; a0 < m1; a0 += 32) {
+      // Lanes own neighbour a and walk its partners b = a+1, a+2, ... (each unordered pair once).  A pass with at most 16
+      // neighbours left (the tail of a 33..48-neighbour shell) would idle half the warp, so its partner range is split
+      // over up to four lane groups that share the same a.
+      const int na = min(32, m1 - a0);
+      int G = 1, grp = 0, sub = lane;
+      if (same && na <= 16) { G = min(4, 32 / na); grp = lane / na; sub = lane - grp * na; }
+      const bool act = (G == 1) ? (sub < na) : (grp < G);
+      const int a = a0 + (act ? sub : 0);
       const int ja = s1 + a;
       const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
       double Aa[NR_T];
 #pragma unroll
       for (int r = 0; r < NR_T; r++) Aa[r] = (r0 + r < NR) ? Arow[r][ja] : 0.0;
       const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
-      int b = same ? a + 1 : 0;
-      if (same && b >= m1) b -= m1;
+      const int chunk = ((same ? (m1 >> 1) : m2) + G - 1) / G;
+      const int t0 = grp * chunk;
+      const int t1 = act ? min(nt, t0 + chunk) : t0;
       const int sb = same ? s1 : s2, mb = same ? m1 : m2;
-      for (int t = 0; t < nt; t++) {
+      int b = same ? (a + 1 + t0) % m1 : 0;
+      for (int t = t0; t < t1; t++) {
         const int jb = sb + b;
         b++;
         if (b >= mb) b -= mb;
@@ -551,10 +561,16 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
   }
   const int width = same ? 32 : (m2 < 32 ? m2 : 32);
   const int npass = (m1 + width - 1) / width;
-  const int nt_max = same ? (m1 >> 1) : m2;
   for (int pass = 0; pass < npass; pass++) {
-    const int a = pass * width + lane;
-    const bool act = (lane < width) && (a < m1);
+    // Lanes own neighbour a and walk its partners; in one step the lanes' partners are distinct, so the shared-memory
+    // force accumulators need no atomics.  A pass with at most 16 neighbours left (the tail of a 33..48-neighbour shell)
+    // would idle half the warp: its partner range is split over up to four lane groups that share the same a, in chunks
+    // at least `na` long so that the groups' partner windows stay disjoint.
+    const int na = min(width, m1 - pass * width);
+    int G = 1, grp = 0, sub = lane;
+    if (same && na <= 16) { G = min(4, 32 / na); grp = lane / na; sub = lane - grp * na; }
+    const int a = pass * width + sub;
+    const bool act = (G == 1) ? ((lane < width) && (a < m1)) : (grp < G);
     const int ja = s1 + (act ? a : 0);
     const double ax = w.ux[ja], ay = w.uy[ja], az = w.uz[ja], Ra = w.R[ja];
     const double invRa = 1.0 / Ra;
@@ -566,9 +582,15 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
       dAa[r] = ok ? dArow[r][ja] : 0.0;
     }
     double gx = 0.0, gy = 0.0, gz = 0.0;
-    const int nt = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    const int nt_all = same ? (m1 >> 1) : m2;
+    const int chunk = (G == 1) ? nt_all : max((nt_all + G - 1) / G, na);
+    const int nt_max = min(chunk, nt_all);
+    const int t0 = grp * chunk;
+    // this lane's own step count within its chunk
+    const int nt_a = same ? ((m1 - 1) >> 1) + (((m1 & 1) == 0 && a < (m1 >> 1)) ? 1 : 0) : m2;
+    const int nt = min(nt_a - t0, chunk);
     const int sb = same ? s1 : s2, mb = same ? m1 : m2;
-    int b = same ? a + 1 : lane;
+    int b = same ? (a + 1 + t0) % m1 : lane;
     if (b >= mb) b -= mb;
     for (int t = 0; t < nt_max; t++) {
       if (act && t < nt) {
@@ -626,7 +648,13 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
       if (b >= mb) b -= mb;
       __syncwarp();
     }
-    if (act) { w.fx[ja] += gx; w.fy[ja] += gy; w.fz[ja] += gz; }
+    for (int g = 1; g < G; g++) {                     // gather the groups' partial sums for a into group 0
+      const int src = (sub + g * na) & 31;
+      const double ox = __shfl_sync(0xffffffffu, gx, src), oy = __shfl_sync(0xffffffffu, gy, src),
+                   oz = __shfl_sync(0xffffffffu, gz, src);
+      if (grp == 0) { gx += ox; gy += oy; gz += oz; }
+    }
+    if (act && grp == 0) { w.fx[ja] += gx; w.fy[ja] += gy; w.fz[ja] += gz; }
     __syncwarp();
   }
 }
