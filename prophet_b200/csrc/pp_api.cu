@@ -308,6 +308,7 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
   // power-basis fast path: every xi an integer power of two below 2^5 and at most two distinct lambdas
   {
     S.basis_nb = 0;
+    S.basis_used[0] = S.basis_used[1] = 0;
     S.basis_lam[0] = S.basis_lam[1] = 0.0;
     bool ok = nG4 > 0;
     int nlam = 0, maxb = 0;
@@ -332,6 +333,7 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
         while ((1 << b) < e) b++;
         S.g4_bb[r] = b;
         S.g4_bg[r] = (S.basis_lam[0] == S.ang_lam[k]) ? 0 : 1;
+        S.basis_used[S.g4_bg[r]] |= 1 << b;
       }
     }
   }

@@ -58,8 +58,10 @@ struct DescSpec {
   double scan_d2_hi, scan_d2_lo;  // squared-distance thresholds equivalent to d <= Rcut and d > 0.01 on d = sqrt(d2)
   int g4_rad[PP_MAX_G4_ROWS], g4_ang[PP_MAX_G4_ROWS];
   // power-basis fast path (pp_desc.cuh): basis_nb = number of power levels (0 = not applicable), the two lambdas,
+  // which levels each lambda group uses,
   // and each row's (lambda group, level)
   int basis_nb;
+  int basis_used[2];              // per lambda group: bit k set when some row uses power level k
   double basis_lam[2];
   int g4_bg[PP_MAX_G4_ROWS], g4_bb[PP_MAX_G4_ROWS];
   // slot of the first triplet row for element pair (e1,e2): Structure::init_type_G_map (Structure.cpp:1500-1510)

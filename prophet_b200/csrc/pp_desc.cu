@@ -148,7 +148,7 @@ md_force_kernel(MdArgs a)
 
 // ---------------------------------------------------------------------------------------------------------
 // template dispatch on the register tile of the G4 grid.
-//   basis path (power-of-two xi, <= 2 lambdas): NR_T in {1,3,5,8} x NB in {3,5}
+//   basis path (power-of-two xi, <= 2 lambdas): NR_T in {1,3,5,8} x NB in {3,5} (+ 5 levels without xi = 8)
 //   general path (any xi / lambda):             NR_T in {3,8}     x NA_T = 4, chunked over the grid
 template <typename F>
 static int dispatch_tile(const DescSpec& hs, F&& f)
@@ -159,6 +159,8 @@ static int dispatch_tile(const DescSpec& hs, F&& f)
     const int nr = NR <= 1 ? 1 : NR <= 3 ? 3 : NR <= 5 ? 5 : 8;
     if (hs.basis_nb <= 3) {
       if (nr == 1) PP_CASE(1, 3, true) if (nr == 3) PP_CASE(3, 3, true) if (nr == 5) PP_CASE(5, 3, true) PP_CASE(8, 3, true)
+    } else if (((hs.basis_used[0] | hs.basis_used[1]) & 8) == 0) {      // xi = 8 unused, e.g. xi in {1, 2, 4, 16}
+      if (nr == 1) PP_CASE(1, 6, true) if (nr == 3) PP_CASE(3, 6, true) if (nr == 5) PP_CASE(5, 6, true) PP_CASE(8, 6, true)
     } else {
       if (nr == 1) PP_CASE(1, 5, true) if (nr == 3) PP_CASE(3, 5, true) if (nr == 5) PP_CASE(5, 5, true) PP_CASE(8, 5, true)
     }

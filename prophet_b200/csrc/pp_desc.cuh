@@ -439,13 +439,25 @@ __device__ __forceinline__ void pp_reduce_scatter(double (&v)[NPAD], int lane)
   }
 }
 
-template <int NR_T, int NB>
+// NBX = number of power levels NB, or 6 = five levels of which level 3 (xi = 8) is used by no row: the usual
+// xi in {1, 2, 4, 16} set.  That level is still squared through but gets no accumulator and no weight.
+template <int NBX> struct PowerLevels {
+  static constexpr int NB = NBX == 6 ? 5 : NBX;         // levels in the squaring chain (and in the cell layout)
+  static constexpr int NU = NBX == 6 ? 4 : NBX;         // levels that carry rows
+  __host__ __device__ static constexpr bool used(int k) { return !(NBX == 6 && k == 3); }
+  __host__ __device__ static constexpr int slot(int k) { return (NBX == 6 && k == 4) ? 3 : k; }      // level -> compact index
+  __host__ __device__ static constexpr int level(int u) { return (NBX == 6 && u == 3) ? 4 : u; }     // compact index -> level
+};
+
+template <int NR_T, int NBX>
 __device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
                                               int e1, int e2, int r0, bool skip_rjk)
 {
-  // One pass over the pairs per lambda group: NR_T * NB accumulators live instead of twice that many (the pair geometry
+  // One pass over the pairs per lambda group: NR_T * NU accumulators live instead of twice that many (the pair geometry
   // is cheap to redo), which is what lets a fourth block onto the SM.
-  constexpr int NACC = NR_T * NB;
+  using PL = PowerLevels<NBX>;
+  constexpr int NB = PL::NB, NU = PL::NU;
+  constexpr int NACC = NR_T * NU;
   constexpr int NPAD = NACC <= 32 ? 32 : 64;
   const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
   const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
@@ -500,7 +512,7 @@ __device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, con
         for (int r = 0; r < NR_T; r++) {
           const double tr = Aa[r] * Arow[r][jb];
 #pragma unroll
-          for (int k = 0; k < NB; k++) acc[r * NB + k] = fma(pw[k], tr, acc[r * NB + k]);
+          for (int u = 0; u < NU; u++) acc[r * NU + u] = fma(pw[PL::level(u)], tr, acc[r * NU + u]);
         }
       }
     }
@@ -508,8 +520,8 @@ __device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, con
     constexpr int PER = NPAD / 32;
 #pragma unroll
     for (int p = 0; p < PER; p++) {
-      const int idx = PER * lane + p;                     // = r * NB + k
-      if (idx < NACC) w.cell[((idx / NB) * 2 + gq) * NB + (idx % NB)] = 2.0 * acc[p];     // factor 2 = both (j,k) orders of the reference
+      const int idx = PER * lane + p;                     // = r * NU + u
+      if (idx < NACC) w.cell[((idx / NU) * 2 + gq) * NB + PL::level(idx % NU)] = 2.0 * acc[p];     // factor 2 = both (j,k) orders of the reference
     }
   }
   __syncwarp();
@@ -523,10 +535,12 @@ __device__ inline void pp_g4_block_desc_basis(WarpNbr& w, int cap, int lane, con
 
 // Force chain rule on the power basis.  W[r][g][b] = 2 * 2^(1-xi) * dE/dG(row) at the row's slot (0 elsewhere).
 //   d/dc pw_g[b] = 2^b lam_g x^(2^b - 1) = 2^b lam_g * prod_{k<b} pw_g[k]        (no division)
-template <int NR_T, int NB>
+template <int NR_T, int NBX>
 __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S,
                                                int e1, int e2, int r0, bool skip_rjk)
 {
+  using PL = PowerLevels<NBX>;
+  constexpr int NB = PL::NB;
   constexpr int NW = NR_T * 2 * NB;
   const int s1 = w.start[e1], m1 = w.start[e1 + 1] - s1;
   const int s2 = w.start[e2], m2 = w.start[e2 + 1] - s2;
@@ -614,11 +628,13 @@ __device__ inline void pp_g4_block_force_basis(WarpNbr& w, int cap, int lane, co
             double dk = pp;                                   // d/dc p^(2^k) = 2^k * pp
 #pragma unroll
             for (int k = 0; k < NB; k++) {
+              if (PL::used(k)) {                              // compile-time: an unused level has zero weights
 #pragma unroll
-              for (int r = 0; r < NR_T; r++) {
-                const double wv = Wld(k, r, gq);
-                Ss[r] = fma(wv, pk, Ss[r]);
-                Ts[r] = fma(wv, dk, Ts[r]);
+                for (int r = 0; r < NR_T; r++) {
+                  const double wv = Wld(k, r, gq);
+                  Ss[r] = fma(wv, pk, Ss[r]);
+                  Ts[r] = fma(wv, dk, Ts[r]);
+                }
               }
               if (k + 1 < NB) {
                 pp *= pk;
@@ -796,7 +812,7 @@ __device__ __noinline__ void pp_g3_block_force(WarpNbr w, int cap, int lane, con
   }
 }
 
-// NX is the angular register tile NA_T on the general path and the number of power levels NB on the basis path.
+// NX is the angular register tile NA_T on the general path and the power-level code NBX (PowerLevels) on the basis path.
 template <int NR_T, int NX, bool BASIS>
 __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
 {

@@ -282,3 +282,44 @@ def test_general_angular_path_descriptors_and_forces_vs_oracle():
         assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("xis", [(1, 2, 4, 8, 16), (1, 2, 4, 16), (8, 16), (1, 4), (2,)])
+def test_power_basis_level_sets_vs_oracle(xis):
+    """Every variant of the power-basis fast path: five squaring levels with and without xi = 8 among the rows, the
+    three-level tile, and lambda groups that use different levels (Structure.h:369-414 angular_term with integer xi)."""
+    cfg = synth.config_c3(2)
+    cfg.lattice = synth.lattice_tio2((2, 2, 3))
+    cfg.G1, cfg.G3 = [], []
+    cfg.G2 = [[6.0, 0.0, 0.3, 0.0]]
+    cfg.G4 = []
+    for n, xi in enumerate(xis):
+        cfg.G4.append([6.0, 0.0, 0.02, float(xi), 1.0])
+        if n % 2 == 0:
+            cfg.G4.append([6.0, 0.0, 0.2, float(xi), -1.0])
+    zmap = {z: i for i, z in enumerate(cfg.elements)}
+    cell, cart, Z, _, _ = synth.make_structure(cfg, 901)
+    frac = capi.cart_to_frac(cell, cart)
+    elem = np.array([zmap[int(z)] for z in Z], dtype=np.int32)
+    ne = len(cfg.elements)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        ctx.add_structures([len(Z)], cell[None], frac, elem, [0.0], [0])
+        G = ctx.get_descriptors(0)
+        Gref = oracle.descriptors_periodic(cell, frac, elem, ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        assert rel_err(G, Gref) < TOL, rel_err(G, Gref)
+        x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + 1.0)
+        numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+        elem_all = np.array([zmap[int(z)] for z in Zall], dtype=np.int32)
+        for e, z in enumerate(cfg.elements):
+            net = synth.random_network(cfg, z, 17)
+            ctx.set_network(e, net["sizes"], net["params"], 0.1 * synth.normal(z, cfg.NG, 3), 0.5 + np.abs(synth.normal(z, cfg.NG, 4)))
+        ctx.md_set_types([0] + list(range(ne)))
+        r = ctx.md_compute(x, elem_all + 1, nlocal, offsets, flat, want_G=True, want_dEdG=True)
+        Gmd = oracle.descriptors_md(x, elem_all, nlocal, offsets, flat, ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        assert rel_err(r["G"], Gmd) < TOL
+        fo = oracle.forces_md(x, elem_all, nlocal, offsets, flat, ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut, r["dEdG"])
+        assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
+    finally:
+        ctx.close()
