@@ -322,15 +322,22 @@ __device__ inline void pp_pair_rows_desc(WarpNbr& w, int cap, int lane, const De
   const int npair = S->npair;
   for (int e = 0; e < S->n_elem; e++) {
     const int s = w.start[e], m = w.start[e + 1] - s;
+    // the cutoff factor depends on (Rc, fc type) only, usually shared by all rows: evaluated when that key changes and
+    // kept in the staging array (free after pp_finalize_entries; each lane reads back only what it wrote)
+    double key_rc = -1.0;
+    int key_fs = -1;
     for (int r = 0; r < npair; r++) {
       double rc = S->pair_rc[r], eta = S->pair_eta[r], rs = S->pair_rs[r];
       int fs = S->pair_fc[r];
       bool g1 = r < S->nG1;
+      if (rc != key_rc || fs != key_fs) {
+        key_rc = rc; key_fs = fs;
+        for (int a = lane; a < m; a += 32) w.sx[s + a] = pp_fc(w.R[s + a] / rc, fs);
+      }
       double acc = 0.0;
       for (int a = lane; a < m; a += 32) {
-        double R = w.R[s + a];
-        double f = pp_fc(R / rc, fs);
-        if (!g1) { double d = R - rs; f *= exp(-eta * (d * d)); }
+        double f = w.sx[s + a];
+        if (!g1) { double d = w.R[s + a] - rs; f *= exp(-eta * (d * d)); }
         acc += f;
       }
       acc = pp_warp_sum(acc);
@@ -844,16 +851,24 @@ __device__ inline void pp_pair_rows_force(WarpNbr& w, int cap, int lane, const D
     double R = w.R[p];
     int e = w.elem[p];
     double dEdR = 0.0;
+    // cutoff factor and slope depend on (Rc, fc type) only, usually shared by all rows: evaluated when that key changes
+    double key_rc = -1.0, f = 0.0, df = 0.0;
+    int key_fs = -1;
     for (int r = 0; r < npair; r++) {
       double rc = S->pair_rc[r];
-      if (R >= rc) continue;
       int fs = S->pair_fc[r];
+      if (rc != key_rc || fs != key_fs) {
+        key_rc = rc; key_fs = fs;
+        f = pp_fc(R / rc, fs);
+        df = pp_dfc(rc, R, fs);
+      }
+      if (R >= rc) continue;
       double wt = w.buf[npair * e + r];
       if (r < S->nG1) {
-        dEdR += wt * pp_dfc(rc, R, fs);
+        dEdR += wt * df;
       } else {
         double eta = S->pair_eta[r], d = R - S->pair_rs[r];
-        dEdR += wt * exp(-eta * d * d) * (pp_dfc(rc, R, fs) - 2.0 * eta * d * pp_fc(R / rc, fs));
+        dEdR += wt * exp(-eta * d * d) * (df - 2.0 * eta * d * f);
       }
     }
     w.fx[p] += dEdR * w.ux[p]; w.fy[p] += dEdR * w.uy[p]; w.fz[p] += dEdR * w.uz[p];
