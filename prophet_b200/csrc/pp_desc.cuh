@@ -197,13 +197,19 @@ __device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const 
   const int NR = S->NR;
   for (int p = lane; p < n; p += 32) {
     double R = w.R[p];
+    double key_rc = -1.0, f = 0.0, df = 0.0;      // cutoff factor and slope: once per (Rc, fc type), usually one key
+    int key_fs = -1;
     for (int r = 0; r < NR; r++) {
       double rc = S->rad_rc[r], eta = S->rad_eta[r];
       int fs = S->rad_fc[r];
       double ex = exp(-eta * (R * R));
-      double f = pp_fc(R / rc, fs);
+      if (rc != key_rc || fs != key_fs) {
+        key_rc = rc; key_fs = fs;
+        f = pp_fc(R / rc, fs);
+        if (FORCE) df = pp_dfc(rc, R, fs);
+      }
       w.A[(size_t)r * cap + p] = ex * f;
-      if (FORCE) w.dA[(size_t)r * cap + p] = ex * (pp_dfc(rc, R, fs) - 2.0 * R * eta * f);
+      if (FORCE) w.dA[(size_t)r * cap + p] = ex * (df - 2.0 * R * eta * f);
     }
     if (FORCE) { w.fx[p] = 0.0; w.fy[p] = 0.0; w.fz[p] = 0.0; w.sR[p] = 1.0 / R; }   // staging is free now: keep 1/R there
   }
