@@ -323,3 +323,46 @@ def test_power_basis_level_sets_vs_oracle(xis):
         assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("rcut", [5.55, 5.9, 6.0])
+def test_neighbour_counts_across_the_tail_pass_split(rcut):
+    """The pair loops split the partner range of a short last pass over 2-4 lane groups (pp_desc.cuh).  Rcut 5.55 gives
+    34 neighbours (2 left over: four groups), 5.9 cuts through the perturbed fifth shell (34..46 neighbours: every group
+    count), 6.0 is C2's 46.  Descriptors (periodic and MD branch) and forces against the oracle."""
+    cfg = synth.config_c2(1)
+    cfg.sigma = 0.12
+    cfg.rcut = rcut
+    cfg.G2 = [[rcut] + list(r[1:]) for r in cfg.G2][:4]
+    cfg.G4 = [[rcut] + list(r[1:]) for r in cfg.G4]
+    cell, cart, Z, _, _ = synth.make_structure(cfg, 31)
+    frac = capi.cart_to_frac(cell, cart)
+    elem = np.zeros(len(Z), dtype=np.int32)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        ctx.add_structures([len(Z)], cell[None], frac, elem, [0.0], [0])
+        G = ctx.get_descriptors(0)
+        Gref = oracle.descriptors_periodic(cell, frac, elem, 1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        assert rel_err(G, Gref) < TOL, rel_err(G, Gref)
+        x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + 1.0)
+        numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+        within = []
+        for i in range(nlocal):
+            js = flat[offsets[i]:offsets[i + 1]]
+            d = np.linalg.norm(x[js] - x[i], axis=1)
+            within.append(int(np.sum(d <= cfg.rcut)))
+        if rcut == 5.9:
+            assert len(set(within)) >= 5, sorted(set(within))          # the split is exercised at several widths
+        net = synth.random_network(cfg, 14, 5)
+        ctx.set_network(0, net["sizes"], net["params"], 0.1 * synth.normal(9, cfg.NG, 3), 0.5 + np.abs(synth.normal(9, cfg.NG, 4)))
+        ctx.md_set_types([0, 0])
+        types = np.ones(len(x), dtype=np.int32)
+        r = ctx.md_compute(x, types, nlocal, offsets, flat, want_G=True, want_dEdG=True)
+        zeros = np.zeros(len(x), dtype=np.int32)
+        Gmd = oracle.descriptors_md(x, zeros, nlocal, offsets, flat, 1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        assert rel_err(r["G"], Gmd) < TOL, rel_err(r["G"], Gmd)
+        fo = oracle.forces_md(x, zeros, nlocal, offsets, flat, 1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut, r["dEdG"])
+        assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
+    finally:
+        ctx.close()
