@@ -107,10 +107,13 @@ int pp_epoch(pp_context* ctx, const double* params_in, double* grad_out, double*
  * result layout on device = [grad(P), sse, vsse, nval] doubles. */
 int pp_epoch_device(pp_context* ctx);
 int pp_epoch_result_dev(pp_context* ctx, double** result_dev, int* n);
-/* Diagnostic: which kernel form the last epoch ran.  0 = two launches per element (forward, then backward: any
- * system), 1 = single-pass fused kernel, one CTA per SM, 2 = single-pass fused kernel with in-place deltas, two
- * CTAs per SM (single element, tanh hidden nodes; same arithmetic, different summation order).  -1 before the first epoch.  The environment variable
- * PP_MLP_ONE_CTA=1 keeps form 2 from being chosen.  No reference counterpart. */
+/* Diagnostic: which kernel form the last epoch ran.  0 = two launches per element (forward, then backward with the
+ * forward pass recomputed: any system), 1 = single-pass fused kernel, one CTA per SM, 2 = single-pass fused kernel with
+ * in-place deltas, two CTAs per SM (single element, tanh / tanh_spline hidden nodes), 3 = two launches per element with
+ * the activations kept in HBM between them (several elements, or networks too large for the single-pass kernels; even
+ * layer widths up to 64, at most four hidden layers).  Same arithmetic in every form, different summation order.
+ * -1 before the first epoch.  Environment: PP_MLP_ONE_CTA=1 keeps form 2 from being chosen, PP_MLP_NO_STORE=1 form 3.
+ * No reference counterpart. */
 int pp_epoch_form(pp_context* ctx);
 /* Potential::evaluate (Potential.cpp:515-551): E_out[n_struct] = sum_atoms E_i + out_mean (every tag) */
 int pp_evaluate(pp_context* ctx, double* E_out);

@@ -55,8 +55,9 @@ struct NetHost {
   std::vector<double> params, mean, scale;
   DevBuf<double> d_mean, d_scale;
   DevBuf<int> d_tf;
-  DevBuf<unsigned char> d_dw_tiles, d_dw_tiles2;
+  DevBuf<unsigned char> d_dw_tiles, d_dw_tiles2, d_dw_tiles3;
   bool has_tiles2 = false;
+  bool has_tiles3 = false;             // eligible for the two-phase kernels with stored activations (pp_mlpw.cu)
   int tile_atoms = 0;
   NetDev dev;
 };
@@ -97,6 +98,7 @@ struct pp_context {
   int epoch_form = -1;                 // kernel form of the last epoch (pp_epoch_form)
   DevBuf<double> d_err_scratch;        // struct_errors_kernel: per-block loss terms
   DevBuf<double> d_scratch2;           // mlp_fused2_kernel: derivative scratch (stays in L2)
+  DevBuf<double> d_hstore[PP_MAX_ELEM], d_tstore[PP_MAX_ELEM];   // stored two-phase epoch: H_l and T'_l of every atom of an element
   DevBuf<unsigned> d_err_ticket;
   DevBuf<long long> d_count;
   double* h_result = nullptr;          // pinned mirror of d_result ([P_total + 3]) and of the parameters ([P_total]) behind it
@@ -185,8 +187,8 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_cell_of.release(); c->d_cell_count.release(); c->d_sorted.release(); c->d_counts.release();
   c->d_cell_start.release(); c->d_scan_sums.release(); c->d_scan_total.release(); c->d_sum_partial.release(); c->d_etotal.release();
   for (int e = 0; e < PP_MAX_ELEM; e++) {
-    c->d_rows[e].release(); c->d_md_rows[e].release();
-    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release(); c->nets[e].d_dw_tiles2.release();
+    c->d_rows[e].release(); c->d_md_rows[e].release(); c->d_hstore[e].release(); c->d_tstore[e].release();
+    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release(); c->nets[e].d_dw_tiles2.release(); c->nets[e].d_dw_tiles3.release();
   }
   c->d_tile_struct0.release();
   if (c->d_spec) cudaFree(c->d_spec);
@@ -443,6 +445,15 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
       if (n.d_dw_tiles2.ensure(t2.size(), 0, c->stream)) return 1;
       PP_CUDA(cudaMemcpy(n.d_dw_tiles2.p, t2.data(), t2.size(), cudaMemcpyHostToDevice));
       n.has_tiles2 = true;
+    }
+    int n3 = 0;
+    n.has_tiles3 = false;
+    if (ppk_mlpw_table(n.dev, nullptr, &n3) && n3 > 0) {
+      std::vector<unsigned char> t3((size_t)n3 * ppk_mlp_dw_tile_bytes());
+      ppk_mlpw_table(n.dev, t3.data(), &n3);
+      if (n.d_dw_tiles3.ensure(t3.size(), 0, c->stream)) return 1;
+      PP_CUDA(cudaMemcpy(n.d_dw_tiles3.p, t3.data(), t3.size(), cudaMemcpyHostToDevice));
+      n.has_tiles3 = true;
     }
   }
   c->tiles_dirty = true;
@@ -849,14 +860,32 @@ static bool all_two_cta(pp_context* c)
   return true;
 }
 
-static int forward_all(pp_context* c)
+// every element's network can run the two-phase kernels that keep the activations in HBM between the phases
+static bool all_stored(pp_context* c)
 {
-  const bool two = all_two_cta(c);
-  for (int e = 0; e < c->spec.n_elem; e++) {
-    MlpArgs a = mlp_args_train(c, e);
-    int n_cta = 0;
-    if (ppk_mlp_launch2(PP_MLP_FORWARD, two, a, c->stream, &c->launches, &n_cta)) return 1;
+  for (int e = 0; e < c->spec.n_elem; e++)
+    if (!c->nets[e].has_tiles3 || !ppk_mlpw_ok(c->nets[e].dev)) return false;
+  return true;
+}
+
+static MlpwStore store_of(pp_context* c, int e, bool with_store)
+{
+  MlpwStore st;
+  memset(&st, 0, sizeof(st));
+  if (!with_store) return st;
+  const NetHost& n = c->nets[e];
+  const size_t M = c->h_rows[e].size();
+  size_t off = 0;
+  for (int l = 1; l < n.n_layers; l++) {
+    st.H[l] = c->d_hstore[e].p + off;
+    st.T[l] = c->d_tstore[e].p + off;
+    off += M * (size_t)n.sizes[l];
   }
+  return st;
+}
+
+static int struct_errors_all(pp_context* c)
+{
   StructArgs sa;
   sa.n_struct = c->n_struct;
   sa.struct_atom0 = c->d_struct_atom0.p;
@@ -871,6 +900,23 @@ static int forward_all(pp_context* c)
   sa.scratch = c->d_err_scratch.p;
   sa.ticket = c->d_err_ticket.p;
   return ppk_struct_errors(sa, c->stream, &c->launches);
+}
+
+// forward pass of every element + per-structure energies and errors.  stored: the kernels of pp_mlpw.cu, which also
+// keep H_l / T'_l for the backward pass when with_store is set.
+static int forward_all(pp_context* c, bool stored, bool with_store)
+{
+  const bool two = !stored && all_two_cta(c);
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    MlpArgs a = mlp_args_train(c, e);
+    if (stored) {
+      if (ppk_mlpw_forward(a, store_of(c, e, with_store), c->stream, &c->launches)) return 1;
+    } else {
+      int n_cta = 0;
+      if (ppk_mlp_launch2(PP_MLP_FORWARD, two, a, c->stream, &c->launches, &n_cta)) return 1;
+    }
+  }
+  return struct_errors_all(c);
 }
 
 static int epoch_buffers(pp_context* c)
@@ -890,33 +936,80 @@ static int epoch_buffers(pp_context* c)
   return 0;
 }
 
+// Which form the epoch takes: 1 / 2 = single pass (single-element system whose structures fit a tile), 3 = two phases
+// with the activations kept in HBM in between (several elements, or a network too large for 64-atom tiles in the
+// single-pass kernels), 0 = two phases with the forward pass recomputed (anything else).
+static int choose_epoch_form(pp_context* c)
+{
+  // networks of up to five n-tiles and two hidden layers are quicker through the two-CTA kernels' FORWARD / TRAIN modes
+  // (measured on C3); PP_MLP_FORCE_STORE=1 sends every eligible system through the stored form
+  const bool stored = all_stored(c) && (!all_two_cta(c) || getenv("PP_MLP_FORCE_STORE") != nullptr);
+  if (c->fused_ok) {
+    const NetHost& n = c->nets[0];
+    const bool two = n.has_tiles2 && ppk_mlp_two_cta_ok(n.dev);
+    if (two) return 2;
+    if (stored && n.tile_atoms < 64) return 3;
+    return 1;
+  }
+  return stored ? 3 : 0;
+}
+
 extern "C" int pp_epoch_device(pp_context* c)
 {
   if (nets_ready(c)) return 1;
-  PP_REQUIRE(c->n_struct > 0, "pp_epoch: no structures");
+  // a single rank without structures has nothing to train on; one rank of several (more ranks than systems, which
+  // the reference tolerates, Setup.cpp:582) contributes zeros and still joins the reduction
+  PP_REQUIRE(c->n_struct > 0 || c->comm.nranks > 1, "pp_epoch: no structures");
   PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
   if (prepare_fused_tiles(c)) return 1;
   if (tick(c, 0)) return 1;
-  if (c->fused_ok) {
-    // one pass: forward, per-structure error and backward in the same kernel; loss terms ride in the partials' tail
+  const int stride = c->P_total + 3;
+  if (c->n_struct == 0) {
     if (tick(c, 1)) return 1;
-    MlpArgs a = mlp_args_train(c, 0);
-    int n_cta = 0;
-    if (ppk_mlp_launch_fused(a, c->stream, &c->launches, &n_cta)) return 1;
-    c->epoch_form = (n_cta > ppk_mlp_single_ctas()) ? 2 : 1;
-    if (ppk_reduce_partials(c->d_partial.p, n_cta, c->P_total + 3, c->P_total + 3, c->d_result.p, c->stream, &c->launches)) return 1;
+    PP_CUDA(cudaMemsetAsync(c->d_result.p, 0, (size_t)stride * sizeof(double), c->stream));
+    c->epoch_form = -1;
   } else {
-    c->epoch_form = 0;
-    if (forward_all(c)) return 1;
-    if (tick(c, 1)) return 1;
-    const bool two = all_two_cta(c);
-    int n_cta = ppk_mlp_single_ctas();
-    for (int e = 0; e < c->spec.n_elem; e++) {
-      MlpArgs a = mlp_args_train(c, e);
-      if (ppk_mlp_launch2(PP_MLP_TRAIN, two, a, c->stream, &c->launches, &n_cta)) return 1;
+    const int form = choose_epoch_form(c);
+    c->epoch_form = form;
+    if (form == 1 || form == 2) {
+      // one pass: forward, per-structure error and backward in the same kernel; loss terms ride in the partials' tail
+      if (tick(c, 1)) return 1;
+      MlpArgs a = mlp_args_train(c, 0);
+      int n_cta = 0;
+      if (ppk_mlp_launch_fused(a, c->stream, &c->launches, &n_cta)) return 1;
+      c->epoch_form = (n_cta > ppk_mlp_single_ctas()) ? 2 : 1;
+      if (ppk_reduce_partials(c->d_partial.p, n_cta, stride, stride, c->d_result.p, c->stream, &c->launches)) return 1;
+    } else {
+      const bool stored = (form == 3);
+      if (stored) {
+        for (int e = 0; e < c->spec.n_elem; e++) {
+          const size_t need = c->h_rows[e].size() * (size_t)ppk_mlpw_store_width(c->nets[e].dev);
+          if (c->d_hstore[e].ensure(std::max<size_t>(need, 2), 0, c->stream) || c->d_tstore[e].ensure(std::max<size_t>(need, 2), 0, c->stream)) return 1;
+        }
+      }
+      if (forward_all(c, stored, true)) return 1;
+      if (tick(c, 1)) return 1;
+      const bool two = !stored && all_two_cta(c);
+      int rows_e[PP_MAX_ELEM] = {0, 0, 0, 0}, n_max = 0;
+      for (int e = 0; e < c->spec.n_elem; e++) {
+        MlpArgs a = mlp_args_train(c, e);
+        if (a.M == 0) continue;                 // this rank holds no atom of the element: its columns are zeroed below
+        if (stored) {
+          a.dw_tiles2 = c->nets[e].d_dw_tiles3.p;
+          if (ppk_mlpw_backward(a, store_of(c, e, true), c->stream, &c->launches, &rows_e[e])) return 1;
+        } else if (ppk_mlp_launch2(PP_MLP_TRAIN, two, a, c->stream, &c->launches, &rows_e[e])) return 1;
+        n_max = std::max(n_max, rows_e[e]);
+      }
+      if (n_max == 0) n_max = 1;
+      // every element's column block must hold n_max rows: zero the rows its launch did not write
+      for (int e = 0; e < c->spec.n_elem; e++) {
+        if (rows_e[e] >= n_max || c->nets[e].P == 0) continue;
+        PP_CUDA(cudaMemset2DAsync(c->d_partial.p + (size_t)rows_e[e] * stride + c->nets[e].p_off, (size_t)stride * sizeof(double), 0,
+                                  (size_t)c->nets[e].P * sizeof(double), (size_t)(n_max - rows_e[e]), c->stream));
+      }
+      if (ppk_reduce_partials(c->d_partial.p, n_max, stride, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
     }
-    if (ppk_reduce_partials(c->d_partial.p, n_cta, c->P_total + 3, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
   }
   if (tick(c, 2)) return 1;
   if (c->comm.allreduce_device(c->d_result.p, c->P_total + 3, c->stream)) return 1;
@@ -992,7 +1085,7 @@ extern "C" int pp_evaluate(pp_context* c, double* E_out)
   PP_REQUIRE(c->n_struct > 0, "pp_evaluate: no structures");
   PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
-  if (forward_all(c)) return 1;
+  if (forward_all(c, all_stored(c) && !all_two_cta(c), false)) return 1;
   PP_CUDA(cudaMemcpyAsync(E_out, c->d_E_struct.p, c->n_struct * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   PP_CUDA(cudaStreamSynchronize(c->stream));
   return 0;

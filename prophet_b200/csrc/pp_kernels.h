@@ -98,6 +98,23 @@ bool ppk_mlp_two_cta_ok(const NetDev& net);
 int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta);
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
 
+// tensor map of a row-major [rows][cols] FP64 array with box (box_cols x box_rows); out_map is a CUtensorMap (cached)
+bool ppk_tiled_map(const double* base, int cols, long long rows, int box_cols, int box_rows, void* out_map);
+int ppk_sm_count(void);
+
+// ---- two-phase epoch with stored activations (pp_mlpw.cu): systems of several elements, wide / deep networks ----
+// H[l] / T[l], l = 1 .. n_layers-1: activations and exact transfer-function derivatives of hidden layer l for the
+// atoms of ONE element, row-major [M][sizes[l]], rows in the order of MlpArgs::rows.  H[1] == nullptr: nothing stored.
+struct MlpwStore {
+  double* H[5];
+  double* T[5];
+};
+bool ppk_mlpw_ok(const NetDev& net);                                   // network shape eligible for these kernels
+int ppk_mlpw_table(const NetDev& net, void* host_out, int* n_entries); // weight-gradient work table (MlpArgs::dw_tiles2)
+int ppk_mlpw_store_width(const NetDev& net);                           // doubles of H (and of T') per atom
+int ppk_mlpw_forward(const MlpArgs& a, const MlpwStore& st, cudaStream_t stream, long long* launches);
+int ppk_mlpw_backward(const MlpArgs& a, const MlpwStore& st, cudaStream_t stream, long long* launches, int* n_cta);
+
 // per-structure energies / errors (Potential.cpp:641-668)
 struct StructArgs {
   int n_struct;

@@ -194,8 +194,7 @@ def case_tio2_train():
 
 
 def case_abo4_train():
-    cfg = synth.config_c4(2)
-    cfg.hidden = [12, 10, 8]      # full 120 descriptors, small nets: keeps the fixture small
+    cfg = synth.config_c4(2)      # BASELINE config 4 as named: 120 descriptors, three nets 120-60-60-60-1 (P = 43 923)
     st = retag([synth.make_structure(cfg, s) for s in range(2)], [0, 0])
     train_case("abo4_train", cfg, st, 2, seed=41)
 
