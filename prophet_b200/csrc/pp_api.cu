@@ -871,16 +871,8 @@ static bool all_stored(pp_context* c)
 static MlpwStore store_of(pp_context* c, int e, bool with_store)
 {
   MlpwStore st;
-  memset(&st, 0, sizeof(st));
-  if (!with_store) return st;
-  const NetHost& n = c->nets[e];
-  const size_t M = c->h_rows[e].size();
-  size_t off = 0;
-  for (int l = 1; l < n.n_layers; l++) {
-    st.H[l] = c->d_hstore[e].p + off;
-    st.T[l] = c->d_tstore[e].p + off;
-    off += M * (size_t)n.sizes[l];
-  }
+  st.H = with_store ? c->d_hstore[e].p : nullptr;
+  st.T = with_store ? c->d_tstore[e].p : nullptr;
   return st;
 }
 

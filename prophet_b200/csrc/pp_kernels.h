@@ -103,11 +103,12 @@ bool ppk_tiled_map(const double* base, int cols, long long rows, int box_cols, i
 int ppk_sm_count(void);
 
 // ---- two-phase epoch with stored activations (pp_mlpw.cu): systems of several elements, wide / deep networks ----
-// H[l] / T[l], l = 1 .. n_layers-1: activations and exact transfer-function derivatives of hidden layer l for the
-// atoms of ONE element, row-major [M][sizes[l]], rows in the order of MlpArgs::rows.  H[1] == nullptr: nothing stored.
+// H / T: activations and exact transfer-function derivatives of the hidden layers for the atoms of ONE element, layer
+// after layer: layer l (1 .. n_layers-1) is a row-major [M][sizes[l]] block at offset M * (sizes[1] + .. + sizes[l-1]),
+// rows in the order of MlpArgs::rows.  H == nullptr: nothing is stored (forward pass only).
 struct MlpwStore {
-  double* H[5];
-  double* T[5];
+  double* H;
+  double* T;
 };
 bool ppk_mlpw_ok(const NetDev& net);                                   // network shape eligible for these kernels
 int ppk_mlpw_table(const NetDev& net, void* host_out, int* n_entries); // weight-gradient work table (MlpArgs::dw_tiles2)
