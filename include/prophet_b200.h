@@ -72,6 +72,9 @@ int pp_set_input_scaling(pp_context* ctx, int elem, const double* in_mean, const
 /* Cartesian -> fractional + single wrap: Structure::Set_Convert + Normalize (Structure.cpp:1159-1279).
  * cell = rows a,b,c.  Bit-identical to the reference (host arithmetic, no FMA contraction). */
 int pp_cart_to_frac(const double* cell, const double* cart, int n, double* frac_out);
+/* The same for n_struct structures in one call (the loop over systems of the Potential constructor,
+ * Potential.cpp:113-150): natoms[n_struct], cells[n_struct][9], cart / frac_out[sum natoms][3]. */
+int pp_cart_to_frac_batch(int n_struct, const int* natoms, const double* cells, const double* cart, double* frac_out);
 /* Append n_struct periodic structures and compute their descriptors on the GPU
  * (Set_Neighbor :1287-1353 + Calc_G periodic branch :985-1071, fused; never materialised on the host).
  *   natoms[n_struct]; cells[n_struct][9] rows a,b,c; frac[sum natoms][3] fractional coordinates as

@@ -28,7 +28,7 @@ _vp = ctypes.c_void_p
 SYMBOLS = [
     "pp_last_error", "pp_version", "pp_create", "pp_destroy", "pp_set_descriptors", "pp_num_descriptors",
     "pp_set_network", "pp_set_output_scaling", "pp_num_parameters", "pp_set_parameters", "pp_get_parameters",
-    "pp_set_input_scaling", "pp_cart_to_frac", "pp_add_structures", "pp_clear_structures", "pp_recompute_descriptors",
+    "pp_set_input_scaling", "pp_cart_to_frac", "pp_cart_to_frac_batch", "pp_add_structures", "pp_clear_structures", "pp_recompute_descriptors",
     "pp_num_structures",
     "pp_num_atoms", "pp_get_descriptors", "pp_get_neighbors", "pp_precondition", "pp_get_input_scaling", "pp_epoch",
     "pp_epoch_device", "pp_epoch_result_dev", "pp_epoch_form", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
@@ -80,6 +80,13 @@ def cart_to_frac(cell, cart):
     cell = _c(cell, np.float64); cart = _c(cart, np.float64)
     out = np.empty_like(cart)
     _check(lib().pp_cart_to_frac(_p(cell, _d), _p(cart, _d), ctypes.c_int(len(cart)), _p(out, _d)))
+    return out
+
+
+def cart_to_frac_batch(natoms, cells, cart):
+    natoms = _c(natoms, np.int32); cells = _c(cells, np.float64); cart = _c(cart, np.float64)
+    out = np.empty_like(cart)
+    _check(lib().pp_cart_to_frac_batch(ctypes.c_int(len(natoms)), _p(natoms, _i), _p(cells, _d), _p(cart, _d), _p(out, _d)))
     return out
 
 
@@ -222,7 +229,8 @@ class Context:
         _check(lib().pp_epoch_device(self._h))
 
     def epoch_form(self):
-        """0 two-phase, 1 fused (one CTA per SM), 2 fused with in-place deltas (two CTAs per SM)."""
+        """0 two-phase with recompute, 1 fused (one CTA per SM), 2 fused with in-place deltas (two CTAs per SM), 3 two-phase
+        with the activations stored in HBM between the phases."""
         return lib().pp_epoch_form(self._h)
 
     def epoch_result_dev(self):

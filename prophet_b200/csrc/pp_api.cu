@@ -554,6 +554,20 @@ extern "C" int pp_cart_to_frac(const double* cell, const double* cart, int n, do
   return 0;
 }
 
+// The same for a batch of structures in one call (the Potential constructor's loop over systems, Potential.cpp:113-150):
+// structure s has natoms[s] atoms, cell cells[9 s ..], positions concatenated.
+extern "C" int pp_cart_to_frac_batch(int n_struct, const int* natoms, const double* cells, const double* cart, double* frac)
+{
+  PP_REQUIRE(n_struct >= 0 && (n_struct == 0 || (natoms && cells && cart && frac)), "pp_cart_to_frac_batch: bad arguments");
+  size_t a0 = 0;
+  for (int s = 0; s < n_struct; s++) {
+    PP_REQUIRE(natoms[s] >= 0, "pp_cart_to_frac_batch: structure %d has %d atoms", s, natoms[s]);
+    if (pp_cart_to_frac(cells + 9 * (size_t)s, cart + 3 * a0, natoms[s], frac + 3 * a0)) return 1;
+    a0 += (size_t)natoms[s];
+  }
+  return 0;
+}
+
 static PeriodicArgs periodic_args(pp_context* c)
 {
   PeriodicArgs a;
