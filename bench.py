@@ -218,6 +218,10 @@ def train_bench(torch, dist, capi, synth, name, ids, rank, world, local_rank, st
         x_pin.copy_(torch.from_numpy(x0))
         ctx.set_parameters(x0)
         n_sus = max(int(sustain_s * 1e3 / max(dev_ms / steps, 1e-3)), steps)
+        if dist is not None:                    # every rank must run the SAME number of epochs (each one holds a collective)
+            nt = torch.tensor([n_sus], dtype=torch.int64, device="cuda")
+            dist.broadcast(nt, 0)
+            n_sus = int(nt.item())
         sus_sampler = ClockSampler(local_rank) if rank == 0 else None
         barrier()
         if sus_sampler:
