@@ -201,6 +201,7 @@ def train_bench(torch, dist, capi, synth, name, ids, rank, world, local_rank, st
         ctx.epoch_into(x_pin.data_ptr(), g_pin.data_ptr())
         fwd_ms.append(ctx.phase_ms(1)); bwd_ms.append(ctx.phase_ms(2)); coll_ms.append(ctx.phase_ms(3))
     form = ctx.epoch_form()
+    comm_path = ctx.comm_path()
     e2e_ms = float("nan")
     if e2e:
         # the loop itself is the host layer's C++ training loop (what `PROPhet_b200 -train` runs): pp_epoch with HOST
@@ -252,7 +253,7 @@ def train_bench(torch, dist, capi, synth, name, ids, rank, world, local_rank, st
                e2e_value=(total_struct / (e2e_ms / steps * 1e-3)) if e2e else None, total_struct=int(total_struct),
                total_atoms=int(total_atoms), atoms_local=atoms_local, n_local=len(ids), launches=int(launches_timed),
                flops_atom=flops_atom, kernel_ms=kern_ms, fwd_ms=fwd, bwd_ms=bwd, coll_ms=float(np.median(coll_ms)),
-               desc_ms=desc_ms, gen_s=gen_s, lib_s=lib_s, setup_wall=setup_wall, sustained=sustained, sizes=sizes)
+               desc_ms=desc_ms, gen_s=gen_s, lib_s=lib_s, setup_wall=setup_wall, sustained=sustained, sizes=sizes, comm_path=comm_path)
     ctx.close()
     return res
 
@@ -339,7 +340,8 @@ def run_ours(args):
             "gpu_launches": head["launches"],
             "clocks": clocks,
             "roofline": roofline_of(head, peaks),
-            "phases_ms": {"forward": head["fwd_ms"], "backward_reduce": head["bwd_ms"], "collective": head["coll_ms"]},
+            "phases_ms": {"forward": head["fwd_ms"], "backward": head["bwd_ms"], "reduce_and_collective": head["coll_ms"]},
+            "collective_path": head["comm_path"],
             "setup": {"descriptor_kernel_ms_total": head["desc_ms"], "structures_per_s_kernel": n_local / (head["desc_ms"] * 1e-3),
                       "wall_s": head["setup_wall"], "host_generation_s": head["gen_s"], "library_calls_s": head["lib_s"],
                       "structures_per_s_load": n_local / max(head["lib_s"], 1e-9),
@@ -365,7 +367,7 @@ def run_ours(args):
                                  "unit": UNIT, "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 8 * r["P"],
                                                        "d2h_bytes_per_step": 8 * (r["P"] + 3)},
                                  "epoch_form": r["form"], "parameters": r["P"], "gpu_launches": r["launches"],
-                                 "phases_ms": {"forward": r["fwd_ms"], "backward_reduce": r["bwd_ms"], "collective": r["coll_ms"]},
+                                 "phases_ms": {"forward": r["fwd_ms"], "backward": r["bwd_ms"], "reduce_and_collective": r["coll_ms"]},
                                  "roofline": roofline_of(r, peaks),
                                  "setup": {"descriptor_kernel_ms_total": r["desc_ms"], "host_generation_s": r["gen_s"], "library_calls_s": r["lib_s"],
                                            "structures_per_s_load": r["n_local"] / max(r["lib_s"], 1e-9)}}

@@ -149,6 +149,11 @@ int pp_md_step_device(pp_context* ctx, const double* x_dev, double* f_dev, doubl
 int pp_comm_unique_id(void* unique_id_128);
 int pp_comm_init(pp_context* ctx, int nranks, int rank, const void* unique_id_128);
 int pp_comm_rank(pp_context* ctx);
+/* Diagnostic: how the per-epoch sum over ranks travels -- "peer memory" (every rank's reduction kernel stores its sums
+ * into receive slots in each peer's memory over NVLink and every rank adds the slots in rank order: one-shot, latency
+ * bound), "nccl" (ncclAllReduce; also chosen by PP_COMM_NCCL_ONLY=1, when peers cannot be mapped, or beyond 8 ranks) or
+ * "single rank".  Decided at the first epoch.  No reference counterpart. */
+const char* pp_comm_path(pp_context* ctx);
 int pp_comm_size(pp_context* ctx);
 /* in-place sum over ranks of n host doubles, result on every rank: Parallel::Reduce(..., MPI_SUM) followed by
  * Parallel::Bcast (Parallel.h:93-150), the pattern of every small collective in Potential / Setup; identity for one rank */
@@ -175,7 +180,8 @@ int pp_column_sums_static(int device, const double* matrix_dev, long long n_rows
 /* number of kernels this library launched since the context was created */
 long long pp_kernel_launches(pp_context* ctx);
 /* device-side time (ms, CUDA events on the context's stream) of the last call's phases:
- * which: 0 = descriptors (pp_add_structures), 1 = epoch forward, 2 = epoch backward+reduce, 3 = collective,
+ * which: 0 = descriptors (pp_add_structures), 1 = epoch forward, 2 = epoch backward, 3 = reduction of the per-CTA
+ *        partial gradients + sum over ranks,
  *        4 = md descriptors, 5 = md network, 6 = md forces */
 double pp_last_phase_ms(pp_context* ctx, int which);
 void* pp_stream(pp_context* ctx);

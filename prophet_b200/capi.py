@@ -33,7 +33,7 @@ SYMBOLS = [
     "pp_num_atoms", "pp_get_descriptors", "pp_get_neighbors", "pp_precondition", "pp_get_input_scaling", "pp_epoch",
     "pp_epoch_device", "pp_epoch_result_dev", "pp_epoch_form", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
     "pp_md_compute", "pp_md_build_neighbors", "pp_md_get_neighbors", "pp_md_step", "pp_md_step_device",
-    "pp_comm_unique_id", "pp_comm_init", "pp_comm_rank", "pp_comm_size", "pp_kernel_launches", "pp_last_phase_ms",
+    "pp_comm_unique_id", "pp_comm_init", "pp_comm_rank", "pp_comm_size", "pp_comm_path", "pp_kernel_launches", "pp_last_phase_ms",
     "pp_stream", "pp_column_sums_static", "pp_comm_allreduce_host",
 ]
 
@@ -307,6 +307,10 @@ class Context:
     def comm_init(self, nranks, rank, unique_id: bytes):
         buf = ctypes.create_string_buffer(unique_id, 128)
         _check(lib().pp_comm_init(self._h, ctypes.c_int(nranks), ctypes.c_int(rank), buf))
+
+    def comm_path(self) -> str:
+        lib().pp_comm_path.restype = ctypes.c_char_p
+        return lib().pp_comm_path(self._h).decode()
 
     @property
     def kernel_launches(self):

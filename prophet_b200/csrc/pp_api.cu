@@ -971,6 +971,8 @@ extern "C" int pp_epoch_device(pp_context* c)
   if (prepare_fused_tiles(c)) return 1;
   if (tick(c, 0)) return 1;
   const int stride = c->P_total + 3;
+  // what the reduction at the end sums: the partial rows' columns [0, red_cols), then d_result's own [red_cols, stride)
+  int red_rows = 0, red_cols = 0;
   if (c->n_struct == 0) {
     if (tick(c, 1)) return 1;
     PP_CUDA(cudaMemsetAsync(c->d_result.p, 0, (size_t)stride * sizeof(double), c->stream));
@@ -985,7 +987,7 @@ extern "C" int pp_epoch_device(pp_context* c)
       int n_cta = 0;
       if (ppk_mlp_launch_fused(a, c->stream, &c->launches, &n_cta)) return 1;
       c->epoch_form = (n_cta > ppk_mlp_single_ctas()) ? 2 : 1;
-      if (ppk_reduce_partials(c->d_partial.p, n_cta, stride, stride, c->d_result.p, c->stream, &c->launches)) return 1;
+      red_rows = n_cta; red_cols = stride;
     } else {
       const bool stored = (form == 3);
       if (stored) {
@@ -1014,11 +1016,12 @@ extern "C" int pp_epoch_device(pp_context* c)
         PP_CUDA(cudaMemset2DAsync(c->d_partial.p + (size_t)rows_e[e] * stride + c->nets[e].p_off, (size_t)stride * sizeof(double), 0,
                                   (size_t)c->nets[e].P * sizeof(double), (size_t)(n_max - rows_e[e]), c->stream));
       }
-      if (ppk_reduce_partials(c->d_partial.p, n_max, stride, c->P_total, c->d_result.p, c->stream, &c->launches)) return 1;
+      red_rows = n_max; red_cols = c->P_total;     // the loss terms are in d_result's tail already (struct_errors_kernel)
     }
   }
   if (tick(c, 2)) return 1;
-  if (c->comm.allreduce_device(c->d_result.p, c->P_total + 3, c->stream)) return 1;
+  // fixed-order sum of the partial rows and, with several ranks, the sum over ranks (Optimizer.cpp:887-888, 969-970)
+  if (c->comm.reduce_sum(c->d_partial.p, red_rows, stride, red_cols, stride, c->d_result.p, c->stream, &c->launches)) return 1;
   if (tick(c, 3)) return 1;
   return 0;
 }
@@ -1344,5 +1347,6 @@ extern "C" int pp_comm_allreduce_host(pp_context* c, double* buf, int n)
   PP_CUDA(cudaSetDevice(c->device));
   return c->comm.allreduce_host(buf, n, c->stream);
 }
+extern "C" const char* pp_comm_path(pp_context* c) { return c ? c->comm.path() : ""; }
 extern "C" int pp_comm_rank(pp_context* c) { return c ? c->comm.rank : 0; }
 extern "C" int pp_comm_size(pp_context* c) { return c ? c->comm.nranks : 1; }

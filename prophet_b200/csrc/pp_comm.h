@@ -6,15 +6,38 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#define PP_PEER_MAX 8
+// Receive slots of the one-shot sum over peer memory (pp_comm.cu): every rank's region holds, per epoch parity, one
+// slot of `cap` doubles per source rank, and one arrival flag per source rank.
+struct PPPeerTable {
+  double* slots[PP_PEER_MAX];                 // base of rank r's slot area, as mapped into THIS process
+  unsigned long long* flags[PP_PEER_MAX];     // base of rank r's flag array
+};
+
 struct PPComm {
   int nranks = 1, rank = 0;
   void* comm = nullptr;
   double* d_stage = nullptr;
   size_t stage_cap = 0;
+  // one-shot sum over peer memory (NVLink): state
+  int peer_state = 0;                         // 0 not tried, 1 ready, -1 unavailable (NCCL is used)
+  size_t peer_cap = 0;                        // doubles per slot
+  void* peer_region = nullptr;                // this rank's region (flags, then slots)
+  void* peer_mapped[PP_PEER_MAX] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  PPPeerTable peers;
+  unsigned long long peer_epoch = 0;
+  unsigned* d_ticket = nullptr;
+  int* d_peer_err = nullptr;
 
   static int unique_id(void* out128);
   int init(int nranks_, int rank_, const void* id128);
   int allreduce_device(double* buf_dev, int n, cudaStream_t st);   // in place, sum; no-op for one rank
   int allreduce_host(double* buf_host, int n, cudaStream_t st);    // in place, sum; no-op for one rank
+  // out[0..ncols) = sum over ranks of (column sums of this rank's partial rows, then tail[ncols_partial..ncols) taken
+  // from out itself), identical on every rank.  One rank: the local reduction only.
+  int reduce_sum(const double* partial, int n_cta, int stride, int ncols_partial, int ncols, double* out, cudaStream_t st,
+                 long long* launches);
+  int peer_setup(size_t need, cudaStream_t st);
+  const char* path() const { return nranks == 1 ? "single rank" : (peer_state == 1 ? "peer memory" : "nccl"); }
   void destroy();
 };

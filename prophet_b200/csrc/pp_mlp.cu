@@ -1529,33 +1529,32 @@ int ppk_struct_errors(const StructArgs& a, cudaStream_t st, long long* launches)
   return 0;
 }
 
-// Sum of the per-CTA partial rows, in a FIXED order (the result is bit-reproducible run to run): 32 columns x 8 row
-// groups per block; group j adds rows j, j+8, j+16, ... (four independent chains to cover the load latency), then the
-// eight group sums are added in order.
-__global__ void __launch_bounds__(256)
+// Sum of the per-CTA partial rows, in a FIXED order (the result is bit-reproducible run to run): 32 columns x 32 row
+// groups per block; group g adds rows g, g+32, g+64, ... (two independent chains to cover the load latency), then the
+// 32 group sums are added in order.  reduce_push_kernel (pp_comm.cu) uses the same order.
+#define PP_RED_GROUPS 32
+__global__ void __launch_bounds__(32 * PP_RED_GROUPS)
 reduce_partials_kernel(const double* __restrict__ partial, int n_cta, int stride, int ncols, double* __restrict__ out)
 {
-  __shared__ double part[8][33];
+  __shared__ double part[PP_RED_GROUPS][33];
   const int col = threadIdx.x & 31, grp = threadIdx.x >> 5;
   const int p = blockIdx.x * 32 + col;
-  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  double s0 = 0.0, s1 = 0.0;
   if (p < ncols) {
     const double* src = partial + p;
     int c = grp;
-    for (; c + 24 < n_cta; c += 32) {
+    for (; c + PP_RED_GROUPS < n_cta; c += 2 * PP_RED_GROUPS) {
       s0 += src[(size_t)c * stride];
-      s1 += src[(size_t)(c + 8) * stride];
-      s2 += src[(size_t)(c + 16) * stride];
-      s3 += src[(size_t)(c + 24) * stride];
+      s1 += src[(size_t)(c + PP_RED_GROUPS) * stride];
     }
-    for (; c < n_cta; c += 8) s0 += src[(size_t)c * stride];
+    if (c < n_cta) s0 += src[(size_t)c * stride];
   }
-  part[grp][col] = (s0 + s1) + (s2 + s3);
+  part[grp][col] = s0 + s1;
   __syncthreads();
   if (grp == 0 && p < ncols) {
     double s = part[0][col];
 #pragma unroll
-    for (int j = 1; j < 8; j++) s += part[j][col];
+    for (int j = 1; j < PP_RED_GROUPS; j++) s += part[j][col];
     out[p] = s;
   }
 }
@@ -1563,7 +1562,7 @@ reduce_partials_kernel(const double* __restrict__ partial, int n_cta, int stride
 int ppk_reduce_partials(const double* partial, int n_cta, int stride, int ncols, double* out, cudaStream_t st, long long* launches)
 {
   if (ncols == 0) return 0;
-  reduce_partials_kernel<<<(ncols + 31) / 32, 256, 0, st>>>(partial, n_cta, stride, ncols, out);
+  reduce_partials_kernel<<<(ncols + 31) / 32, 32 * PP_RED_GROUPS, 0, st>>>(partial, n_cta, stride, ncols, out);
   (*launches)++;
   PP_CUDA(cudaGetLastError());
   return 0;
