@@ -379,18 +379,15 @@ def run_ours(args):
             out["multi_rank_parity"] = par
             assert par["ok"], "multi-rank epoch differs from the single-rank epoch: %r" % (par,)
     if not args.no_md:
-        # pair_nn (second metric of BASELINE.json); at N > 1 every rank runs an independent replica of the box
+        # pair_nn (second metric of BASELINE.json): one box cut over the GPUs, exchange owned by the library
         md = run_md_bench(torch, capi, synth, local_rank, args.md_cells, args.md_steps, 2, dist=dist, rank=rank, world=world)
-        if dist is not None:
-            t = torch.tensor([md["ms_per_step"], md["e2e"]["ms_per_step"]], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            md["ms_per_step"], md["e2e"]["ms_per_step"] = [float(v) for v in t.cpu()]
-            md["value"] = world * md["atoms_local"] / (md["ms_per_step"] * 1e-3)
-            md["e2e"]["value"] = world * md["atoms_local"] / (md["e2e"]["ms_per_step"] * 1e-3)
-            md["n_gpus"] = world
-            md["partition"] = "%d sub-boxes along x (weak scaling), ghost forces of the x faces exchanged with ring neighbours " \
-                              "(NCCL send/recv), y/z images folded locally, energy all-reduced; e2e leg: per-rank host round trip " \
-                              "without the exchange" % world
+        if world > 1:
+            t = torch.tensor(list(capi.Context.comm_unique_id()) if rank == 0 else [0] * 128, dtype=torch.uint8, device="cuda")
+            dist.broadcast(t, 0)
+            chk = md_partition_check(torch, capi, synth, dist, local_rank, rank, world, bytes(t.cpu().tolist()))
+            if rank == 0:
+                md["partition_parity"] = chk
+                assert chk["ok"], "partitioned forces differ from the single-rank forces: %r" % (chk,)
         if rank == 0:
             if world == 1 and not args.no_cpu_baseline:
                 md["cpu_baseline"] = reference_md_rate()
@@ -413,16 +410,13 @@ def md_system(synth, cells, seed=5, skin=1.0, with_owner=False):
     return cfg, np.ascontiguousarray(x), nlocal
 
 
-def run_md_bench(torch, capi, synth, device, cells, steps, warmup, dist=None, rank=0, world=1):
-    """pp_md_build_neighbors once (LAMMPS rebuilds every 10 steps, pair_nn.cpp:276), then `steps` calls of the
-    PairNN::compute equivalent: device-resident (value) and through host buffers (e2e).
-
-    N > 1 (weak scaling): the global box is N sub-boxes side by side along x, one per GPU, periodic.  Each rank
-    computes forces on its locals AND ghosts exactly as the reference does (pair_nn.cpp:182 writes ghost forces and
-    relies on LAMMPS' reverse communication); the harness then plays LAMMPS' part: ghost forces of y/z images are
-    folded onto their owners locally, those of the two x faces travel to the neighbouring ranks (NCCL send/recv,
-    ring) and are added there, and the energy is all-reduced.  That exchange is inside the timed region."""
-    cfg, x, nlocal, owner, shift = md_system(synth, cells, with_owner=True)
+def md_partition(torch, capi, synth, dist, device, cells, rank, world, comm_uid=None, seed=5, skin=1.0):
+    """This rank's slab of the global diamond-Si box (cells^3 unit cells, periodic), set up in a context: atoms uploaded,
+    full neighbour list built on the GPU, ghost-force exchange lists installed.  Returns (ctx, cfg, partition dict)."""
+    cfg = synth.config_c5(cells)
+    cell, cart, Z, _, _ = synth.make_structure(cfg, seed)          # the same global box on every rank (seeded)
+    part = synth.slab_partition(cell, cart, rank, world, cfg.rcut + skin)
+    x, nlocal = part["x"], part["nlocal"]
     ntotal = len(x)
     ctx = capi.Context(device)
     ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
@@ -430,110 +424,193 @@ def run_md_bench(torch, capi, synth, device, cells, steps, warmup, dist=None, ra
     mean = 0.1 * synth.normal(9, cfg.NG, 3); scale = 0.5 + np.abs(synth.normal(9, cfg.NG, 4))
     ctx.set_network(0, net["sizes"], net["params"], mean, scale)
     ctx.md_set_types([0, 0])
-    types = np.ones(ntotal, dtype=np.int32)
     t0 = time.perf_counter()
-    ctx.md_build_neighbors(x, types, nlocal, cfg.rcut + 1.0)
-    build_s = time.perf_counter() - t0
+    ctx.md_build_neighbors(x, np.ones(ntotal, dtype=np.int32), nlocal, cfg.rcut + skin)
+    part["build_s"] = time.perf_counter() - t0
+    if world > 1:
+        ctx.comm_init(world, rank, comm_uid)
+    # exchange lists: ghosts owned by this rank fold locally; the others go to their owners, who need to know which of
+    # THEIR atoms each value belongs to (set-up time exchange of index lists, as LAMMPS' Comm::borders does)
+    gidx = np.arange(nlocal, ntotal, dtype=np.int32)
+    mine = part["ghost_rank"] == rank
+    wanted = {}
+    for o in np.unique(part["ghost_rank"]):
+        if int(o) != rank:
+            sel = part["ghost_rank"] == o
+            wanted[int(o)] = (gidx[sel], part["ghost_local"][sel])
+    peers = []
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, {o: v[1] for o, v in wanted.items()})
+        for o in sorted(set(wanted) | {r for r in range(world) if r != rank and rank in gathered[r]}):
+            send_idx = wanted[o][0] if o in wanted else np.zeros(0, dtype=np.int32)
+            recv_dst = gathered[o].get(rank, np.zeros(0, dtype=np.int32))
+            peers.append((o, send_idx, recv_dst))
+    ctx.md_exchange_setup(gidx[mine], part["ghost_local"][mine], peers)
+    part["exchange"] = {"own_ghosts": int(mine.sum()), "peers": [(o, int(len(a)), int(len(b))) for o, a, b in peers]}
+    return ctx, cfg, part
+
+
+def md_partition_check(torch, capi, synth, dist, device, rank, world, uid, cells=12):
+    """Outside every timed region: a small box cut over the ranks must give, after the exchange, the forces and the
+    energy of the same box on ONE rank (north_star: forces within 1e-10)."""
+    ctx, cfg, part = md_partition(torch, capi, synth, dist, device, cells, rank, world, comm_uid=uid)
+    x, nlocal = part["x"], part["nlocal"]
+    f = np.zeros((nlocal, 3)); ea = np.zeros(max(nlocal, 1))
+    xp = torch.from_numpy(x).pin_memory(); fp = torch.from_numpy(f).pin_memory(); ep = torch.from_numpy(ea).pin_memory()
+    et = ctx.md_step_exchange_ptr(xp.data_ptr(), fp.data_ptr(), ep.data_ptr())
+    ctx.close()
+    res = [None] * world
+    if world > 1:
+        dist.all_gather_object(res, (part["owned_ids"], fp.numpy().copy(), et))
+    else:
+        res[0] = (part["owned_ids"], fp.numpy().copy(), et)
+    out = None
+    if rank == 0:
+        one, cfg1, p1 = md_partition(torch, capi, synth, None, device, cells, 0, 1)
+        f1 = torch.zeros(p1["nlocal"], 3, dtype=torch.float64).pin_memory()
+        x1 = torch.from_numpy(p1["x"]).pin_memory()
+        et1 = one.md_step_exchange_ptr(x1.data_ptr(), f1.data_ptr(), None)
+        one.close()
+        fall = np.zeros_like(f1.numpy())
+        for ids, fr, _ in res:
+            fall[ids] = fr
+        fmax = float(np.max(np.abs(f1.numpy())))
+        out = {"workload": "diamond Si %d^3 cells (%d atoms) cut into %d slabs vs one rank" % (cells, len(fall), world),
+               "force_rel_err": float(np.max(np.abs(fall - f1.numpy())) / fmax), "energy_rel_err": abs(res[0][2] - et1) / abs(et1),
+               "energies_equal_on_all_ranks": bool(all(abs(r[2] - res[0][2]) == 0.0 for r in res)), "tolerance": 1e-10}
+        out["ok"] = bool(out["force_rel_err"] <= 1e-10 and out["energy_rel_err"] <= 1e-12 and out["energies_equal_on_all_ranks"])
+    return out
+
+
+def run_md_bench(torch, capi, synth, device, cells, steps, warmup, dist=None, rank=0, world=1):
+    """pair_nn as BASELINE.json names it: ONE box (cells^3 diamond cells; C5 = 50 -> 1 M atoms) cut into `world` slabs
+    along x, one per GPU (strong scaling).  pp_md_build_neighbors once (LAMMPS rebuilds every 10 steps, pair_nn.cpp:276),
+    then `steps` calls of the PairNN::compute equivalent followed by the reverse communication of the ghost forces and the
+    energy sum -- both owned by the library (pp_md_exchange_device: pack kernel, NCCL send/recv, ordered add) and both
+    inside the timed regions: device-resident (value) and through host buffers (e2e)."""
+    uid = None
+    if world > 1:
+        t = torch.tensor(list(capi.Context.comm_unique_id()) if rank == 0 else [0] * 128, dtype=torch.uint8, device="cuda")
+        dist.broadcast(t, 0)
+        uid = bytes(t.cpu().tolist())
+    ctx, cfg, part = md_partition(torch, capi, synth, dist, device, cells, rank, world, comm_uid=uid)
+    x, nlocal = part["x"], part["nlocal"]
+    ntotal = len(x)
     stream = torch.cuda.ExternalStream(ctx.stream)
     dev = torch.device("cuda", device)
     xd = torch.from_numpy(x).to(dev)
     fd = torch.zeros_like(xd)
     ed = torch.zeros(1, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
-    exchange = None
-    if world > 1:
-        own = torch.from_numpy(owner).to(dev)
-        gidx = torch.arange(nlocal, ntotal, device=dev)
-        sx = torch.from_numpy(shift[:, 0].copy()).to(dev)
-        sel_self, sel_left, sel_right = (sx == 0), (sx < 0), (sx > 0)
-        g_self, o_self = gidx[sel_self], own[sel_self]
-        g_left, o_left = gidx[sel_left], own[sel_left]
-        g_right, o_right = gidx[sel_right], own[sel_right]
-        left, right = (rank - 1) % world, (rank + 1) % world
-        recv_r = torch.empty((len(g_left), 3), dtype=torch.float64, device=dev)    # from the right neighbour: its left ghosts = my atoms
-        recv_l = torch.empty((len(g_right), 3), dtype=torch.float64, device=dev)
-
-        def exchange():
-            with torch.cuda.stream(stream):
-                fd.index_add_(0, o_self, fd[g_self])                      # local fold (y/z periodic images)
-                send_l, send_r = fd[g_left].contiguous(), fd[g_right].contiguous()
-                ops = [dist.P2POp(dist.isend, send_l, left), dist.P2POp(dist.isend, send_r, right),
-                       dist.P2POp(dist.irecv, recv_r, right), dist.P2POp(dist.irecv, recv_l, left)]
-                for w_ in dist.batch_isend_irecv(ops):
-                    w_.wait()
-                fd.index_add_(0, o_left, recv_r)
-                fd.index_add_(0, o_right, recv_l)
-                dist.all_reduce(ed)
 
     def one_step():
         with torch.cuda.stream(stream):
             fd.zero_()                                                    # LAMMPS clears forces before Pair::compute
         ctx.md_step_device(xd.data_ptr(), fd.data_ptr(), ed.data_ptr())
-        if exchange is not None:
-            exchange()
+        ctx.md_exchange_device(fd.data_ptr(), ed.data_ptr())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
 
     for _ in range(warmup):
         one_step()
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-        torch.cuda.synchronize()
+    barrier()
     ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
     l0 = ctx.kernel_launches
     ev0.record(stream)
     for _ in range(steps):
         one_step()
     ev1.record(stream)
-    ev1.synchronize()
-    torch.cuda.synchronize()
+    barrier()
     dev_ms = ev0.elapsed_time(ev1) / steps
     launches = ctx.kernel_launches - l0
-    # property check (outside the timed region): once every ghost force is back on its owner the forces on the local
-    # atoms are those of the periodic system, whose total force vanishes
+    exch_ms = ctx.phase_ms(7)
+    # property check (outside the timed region): with every ghost force back on its owner the forces on the atoms of the
+    # periodic box must add up to zero
     one_step()
     with torch.cuda.stream(stream):
-        f_loc = fd[:nlocal].clone()
-        if world == 1:
-            f_loc.index_add_(0, torch.from_numpy(owner).to(dev), fd[nlocal:])
-        fsum = float(f_loc.sum(dim=0).abs().max() / f_loc.abs().max())
+        fsum_v = fd[:nlocal].sum(dim=0)
+        fmax_v = fd[:nlocal].abs().max().reshape(1)
     torch.cuda.synchronize()
-    # e2e: pinned host positions in, forces / energies out, every step
+    if dist is not None:
+        dist.all_reduce(fsum_v)
+        dist.all_reduce(fmax_v, op=dist.ReduceOp.MAX)
+    fsum = float(fsum_v.abs().max() / fmax_v[0])
+    # e2e: pinned host positions in, forces of the local atoms / energies out, exchange included, every step
     x_pin = torch.from_numpy(x).pin_memory()
-    f_pin = torch.zeros(ntotal, 3, dtype=torch.float64).pin_memory()
+    f_pin = torch.zeros(max(nlocal, 1), 3, dtype=torch.float64).pin_memory()
     ea_pin = torch.zeros(max(nlocal, 1), dtype=torch.float64).pin_memory()
     for _ in range(max(1, warmup - 1)):
-        ctx.md_step_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
+        ctx.md_step_exchange_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
+    barrier()
     phases = []
     t0 = time.perf_counter()
     for _ in range(steps):
-        ctx.md_step_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
-        phases.append((ctx.phase_ms(4), ctx.phase_ms(5), ctx.phase_ms(6)))
+        ctx.md_step_exchange_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
+        phases.append((ctx.phase_ms(4), ctx.phase_ms(5), ctx.phase_ms(6), ctx.phase_ms(7)))
     e2e_ms = (time.perf_counter() - t0) * 1e3 / steps
     ph = np.median(np.array(phases), axis=0)
-    # algorithmic flops per atom-step (measured mean neighbour count n)
-    off, _nb = None, None
-    nneigh = None
-    out = {"metric": "pair_nn atom-steps/sec", "value": nlocal / (dev_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": dev_ms,
-           "atoms_local": int(nlocal), "atoms_ghost": int(ntotal - nlocal), "steps": steps, "warmup": warmup,
-           "workload": "C5: diamond Si %dx%dx%d cells, Rcut 6 + skin 1, 50 descriptors, net 50-40-40-1" % (cells, cells, cells),
-           "e2e": {"value": nlocal / (e2e_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": e2e_ms,
-                   "h2d_bytes_per_step": 2 * 24 * ntotal, "d2h_bytes_per_step": 24 * ntotal + 8 * nlocal + 8},
-           "phases_ms": {"descriptors": float(ph[0]), "network": float(ph[1]), "forces": float(ph[2])},
-           "neighbor_build_s": build_s, "gpu_launches": int(launches), "total_force_over_max_force": fsum}
+    tt = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([float(nlocal), float(ntotal - nlocal)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt)
+    dev_ms, e2e_ms = [float(v) for v in tt.cpu()]
+    atoms_total, ghosts_total = [int(v) for v in cnt.cpu()]
+    out = {"metric": "pair_nn atom-steps/sec", "value": atoms_total / (dev_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": dev_ms,
+           "n_gpus": world, "scaling": "strong", "atoms_total": atoms_total, "atoms_local": int(nlocal), "atoms_ghost": int(ntotal - nlocal),
+           "ghosts_total": ghosts_total, "steps": steps, "warmup": warmup,
+           "workload": "C5: ONE diamond-Si box of %dx%dx%d cells (%d atoms) cut into %d slab(s) along x, Rcut 6 + skin 1, 50 descriptors, "
+                       "net 50-40-40-1" % (cells, cells, cells, atoms_total, world),
+           "partition": "rank r owns x in [r L/N, (r+1) L/N); ghosts = periodic images within Rcut + skin; forces are computed on locals "
+                        "and ghosts (pair_nn.cpp:182) and the ghost forces return to their owners through pp_md_exchange_device (pack "
+                        "kernel, NCCL send/recv, ordered add; own periodic images folded locally), energy all-reduced -- inside both timings",
+           "exchange": dict(part["exchange"], ms=exch_ms),
+           "e2e": {"value": atoms_total / (e2e_ms * 1e-3), "unit": "atom-steps/s", "ms_per_step": e2e_ms,
+                   "h2d_bytes_per_step": 24 * ntotal, "d2h_bytes_per_step": 24 * nlocal + 8 * nlocal + 8},
+           "phases_ms": {"descriptors": float(ph[0]), "network": float(ph[1]), "forces": float(ph[2]), "exchange": float(ph[3])},
+           "neighbor_build_s": part["build_s"], "gpu_launches": int(launches), "total_force_over_max_force": fsum}
     peaks = _fp64_peaks()
-    flops_desc, flops_force = 0.41e6, 1.21e6      # per atom at n = 45; the dominant kernel is the force kernel
-    out["roofline"] = {"bound": "fp64-fma", "kernel": "md_force_kernel", "achieved": flops_force * nlocal / (ph[2] * 1e-3) / 1e12,
+    # Analytic FP64 operation count of the factorised evaluation the kernels actually perform (DESIGN.md section 4.1):
+    # per neighbour and per unordered pair of neighbours, at C2's rows; SURVEY's row-by-row count is kept for reference.
+    fl = md_flops_model(cfg, part.get("mean_neighbours", 45.2))
+    out["roofline"] = {"bound": "fp64-fma", "kernel": "md_force_kernel", "achieved": fl["force"] * nlocal / (ph[2] * 1e-3) / 1e12,
                        "peak": peaks["fp64_fma_tflops"], "unit": "TFLOP/s",
-                       "frac": flops_force * nlocal / (ph[2] * 1e-3) / 1e12 / peaks["fp64_fma_tflops"],
-                       "algorithmic_flops_per_atom": flops_force, "peak_source": peaks["source"],
-                       # SURVEY 8(d) counts every G4 row per pair (12 + 30 x 40 flops); the factorised power-basis evaluation
-                       # EXECUTES far fewer, so the fraction above can exceed 1.  What the kernel really issues (ncu,
-                       # profiles/r01_ncu_md_final.txt capture: dfma x 2 + dmul + dadd = 0.284 MFLOP per atom at C5's rows):
-                       "executed": {"flops_per_atom": 0.284e6, "achieved": 0.284e6 * nlocal / (ph[2] * 1e-3) / 1e12,
-                                    "frac": 0.284e6 * nlocal / (ph[2] * 1e-3) / 1e12 / peaks["fp64_fma_tflops"],
-                                    "source": "ncu sm__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on of md_force_kernel"}}
+                       "frac": fl["force"] * nlocal / (ph[2] * 1e-3) / 1e12 / peaks["fp64_fma_tflops"],
+                       "algorithmic_flops_per_atom": fl["force"], "peak_source": peaks["source"], "flops_model": fl,
+                       "descriptor_kernel": {"kernel": "md_desc_kernel", "algorithmic_flops_per_atom": fl["desc"],
+                                             "achieved": fl["desc"] * nlocal / (ph[0] * 1e-3) / 1e12,
+                                             "frac": fl["desc"] * nlocal / (ph[0] * 1e-3) / 1e12 / peaks["fp64_fma_tflops"]},
+                       "naive_flops_per_atom": {"descriptors": 0.41e6, "forces": 1.21e6,
+                                                "note": "SURVEY 8(d): every G4 row evaluated per ordered pair; not what runs"}}
     ctx.close()
     return out
+
+
+def md_flops_model(cfg, n):
+    """FP64 operations per central atom of the factorised power-basis evaluation (pp_desc.cuh), counting an FMA as two:
+    n neighbours inside Rcut, n(n-1)/2 unordered pairs, NR radial keys (distinct eta), NB power levels x 2 lambdas."""
+    NR = len({(r[0], r[1], r[2]) for r in cfg.G4})
+    xis = sorted({int(r[3]) for r in cfg.G4})
+    levels = len(xis)                                   # accumulated power levels (1, 2, 4, 16 -> 4)
+    chain = int(np.log2(max(xis))) if xis else 0        # squarings from (1 + lam c) to the highest power
+    nG2 = len(cfg.G2)
+    pairs = n * (n - 1) / 2.0
+    # per neighbour: distance, unit vector, cutoff spline + slope (~40), one exp + product per radial key and per G2 row
+    per_nb_desc = 40 + 22 * NR + 24 * nG2
+    # per unordered pair and lambda: cos (5), chain of squarings (chain), per level and radial key one FMA (2)
+    per_pair_desc = 2 * (5 + 1 + chain + 2 * levels * NR) + 2 * NR
+    # forces: the same products plus the derivative chain: per level and key two FMAs, three Cartesian components for each
+    # of the two neighbours (prefix products of the powers give d/dc)
+    per_nb_force = 60 + 30 * NR + 40 * nG2
+    per_pair_force = 2 * (5 + 1 + 2 * chain + 4 * levels * NR) + 8 * NR + 36
+    return {"neighbours": n, "radial_keys": NR, "power_levels": levels, "desc": n * per_nb_desc + pairs * per_pair_desc,
+            "force": n * per_nb_force + pairs * per_pair_force,
+            "note": "model of the factorised evaluation, FMA = 2; see DESIGN.md section 4.1"}
 
 
 def reference_md_rate(cells=2, cores=1):

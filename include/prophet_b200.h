@@ -144,6 +144,28 @@ int pp_md_step(pp_context* ctx, const double* x, double* f_inout, double* eatom_
 /* the same with x / f already on the device (x_dev[ntotal][3], f_dev[ntotal][3] accumulated into) */
 int pp_md_step_device(pp_context* ctx, const double* x_dev, double* f_dev, double* etotal_dev);
 
+/* ---- partitioned box: the host engine's reverse communication ------------------------------------------------------ */
+/* PairNN::compute leaves forces on ghost atoms (Structure::Get_Forces writes f[j] for every neighbour, pair_nn.cpp:182)
+ * and counts on LAMMPS' Comm::reverse_comm to return them to the atoms that own them.  When a caller drives a box cut
+ * over the ranks of a communicator itself (pp_comm_init), these calls play that part on the GPU: ghost forces are packed
+ * by a kernel, travel by NCCL send/recv on the context's stream and are added in a fixed order (reproducible forces).
+ *   own ghosts : n_self pairs (ghost index self_src[k] >= nlocal, local index self_dst[k]): periodic images of this
+ *                rank's own atoms;
+ *   peers      : for peer i (rank peer_rank[i]) send_count[i] ghost indices in send_idx_flat (concatenated over peers),
+ *                sent in that order, and recv_count[i] local indices in recv_dst_flat: where the values that peer sends
+ *                (in ITS order) are added.  The lists are whatever the caller's decomposition dictates.
+ * Call after pp_md_build_neighbors (which fixes nlocal / nghost). */
+int pp_md_exchange_setup(pp_context* ctx, int n_self, const int* self_src, const int* self_dst, int n_peers, const int* peer_rank,
+                         const int* send_count, const int* send_idx_flat, const int* recv_count, const int* recv_dst_flat);
+/* f_dev[ntotal][3] (device): ghost forces added onto their owners here and on the peers; etotal_dev (device, may be NULL):
+ * this rank's total as pp_md_step_device leaves it -> the sum over ranks (the output shift counted once, as
+ * pair_nn.cpp:175-179 adds it on rank 0 only). */
+int pp_md_exchange_device(pp_context* ctx, double* f_dev, double* etotal_dev);
+/* pp_md_step for a partitioned box: x[ntotal][3] uploaded, forces on locals and ghosts, exchange, then the forces of
+ * the nlocal LOCAL atoms written to f_local_out[nlocal][3] (overwritten, LAMMPS having cleared them), per-atom energies
+ * and the total over all ranks. */
+int pp_md_step_exchange(pp_context* ctx, const double* x, double* f_local_out, double* eatom_out, double* etotal_out);
+
 /* ---- Parallel (Parallel.h:93-214): NCCL replaces MPI_Reduce/MPI_Bcast of Optimizer::update_network ---------- */
 /* unique_id: 128-byte ncclUniqueId made by pp_comm_unique_id on rank 0 and distributed by the launcher */
 int pp_comm_unique_id(void* unique_id_128);
@@ -182,7 +204,7 @@ long long pp_kernel_launches(pp_context* ctx);
 /* device-side time (ms, CUDA events on the context's stream) of the last call's phases:
  * which: 0 = descriptors (pp_add_structures), 1 = epoch forward, 2 = epoch backward, 3 = reduction of the per-CTA
  *        partial gradients + sum over ranks,
- *        4 = md descriptors, 5 = md network, 6 = md forces */
+ *        4 = md descriptors, 5 = md network, 6 = md forces, 7 = ghost-force exchange (pp_md_exchange_device) */
 double pp_last_phase_ms(pp_context* ctx, int which);
 void* pp_stream(pp_context* ctx);
 

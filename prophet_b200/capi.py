@@ -33,6 +33,7 @@ SYMBOLS = [
     "pp_num_atoms", "pp_get_descriptors", "pp_get_neighbors", "pp_precondition", "pp_get_input_scaling", "pp_epoch",
     "pp_epoch_device", "pp_epoch_result_dev", "pp_epoch_form", "pp_evaluate", "pp_get_atom_energies", "pp_md_set_types",
     "pp_md_compute", "pp_md_build_neighbors", "pp_md_get_neighbors", "pp_md_step", "pp_md_step_device",
+    "pp_md_exchange_setup", "pp_md_exchange_device", "pp_md_step_exchange",
     "pp_comm_unique_id", "pp_comm_init", "pp_comm_rank", "pp_comm_size", "pp_comm_path", "pp_kernel_launches", "pp_last_phase_ms",
     "pp_stream", "pp_column_sums_static", "pp_comm_allreduce_host",
 ]
@@ -296,6 +297,24 @@ class Context:
 
     def md_step_device(self, x_dev: int, f_dev: int, etotal_dev: int):
         _check(lib().pp_md_step_device(self._h, _vp(x_dev), _vp(f_dev), _vp(etotal_dev)))
+
+    def md_exchange_setup(self, self_src, self_dst, peers):
+        """peers: list of (rank, send_idx array, recv_dst array)."""
+        self_src = _c(self_src, np.int32); self_dst = _c(self_dst, np.int32)
+        ranks = _c([p[0] for p in peers], np.int32)
+        sc = _c([len(p[1]) for p in peers], np.int32); rc = _c([len(p[2]) for p in peers], np.int32)
+        sflat = _c(np.concatenate([np.asarray(p[1], dtype=np.int32) for p in peers]) if peers else np.zeros(0), np.int32)
+        rflat = _c(np.concatenate([np.asarray(p[2], dtype=np.int32) for p in peers]) if peers else np.zeros(0), np.int32)
+        _check(lib().pp_md_exchange_setup(self._h, ctypes.c_int(len(self_src)), _p(self_src, _i), _p(self_dst, _i), ctypes.c_int(len(peers)),
+                                          _p(ranks, _i), _p(sc, _i), _p(sflat, _i), _p(rc, _i), _p(rflat, _i)))
+
+    def md_exchange_device(self, f_dev: int, etotal_dev: int = 0):
+        _check(lib().pp_md_exchange_device(self._h, _vp(f_dev), _vp(etotal_dev) if etotal_dev else None))
+
+    def md_step_exchange_ptr(self, x_ptr: int, f_ptr: int, eatom_ptr: Optional[int] = None):
+        et = ctypes.c_double()
+        _check(lib().pp_md_step_exchange(self._h, _vp(x_ptr), _vp(f_ptr), _vp(eatom_ptr) if eatom_ptr else None, ctypes.byref(et)))
+        return et.value
 
     # ---- comm / instrumentation ----
     @staticmethod

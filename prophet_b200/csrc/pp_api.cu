@@ -68,7 +68,7 @@ struct pp_context {
   long long launches = 0;
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   bool epoch_phases_pending = false;   // pp_epoch finished: events 0..3 hold its phases, read out on demand (pp_last_phase_ms)
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   bool spec_set = false;
   DescSpec spec;
@@ -124,6 +124,12 @@ struct pp_context {
   DevBuf<long long> d_cell_start, d_scan_sums, d_scan_total;
   DevBuf<double> d_sum_partial, d_etotal;
   bool md_list_resident = false;
+  // reverse communication of ghost forces (pp_md_exchange_*)
+  struct SegList { int n_seg = 0; DevBuf<int> seg_off, seg_dst, idx; };
+  struct MdPeer { int rank = 0; int n_send = 0, n_recv = 0; DevBuf<int> send_idx; DevBuf<double> sendbuf, recvbuf; SegList add; };
+  SegList md_self;
+  std::vector<MdPeer> md_peers;
+  bool md_exchange_set = false;
 
   PPComm comm;
 };
@@ -157,7 +163,7 @@ extern "C" int pp_create(int device, int fp_mode, pp_context** out)
   pp_context* c = new pp_context();
   c->device = device;
   PP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  for (int i = 0; i < 4; i++) PP_CUDA(cudaEventCreate(&c->ev[i]));
+  for (int i = 0; i < 6; i++) PP_CUDA(cudaEventCreate(&c->ev[i]));
   PP_CUDA(cudaMalloc(&c->d_spec, sizeof(DescSpec)));
   if (c->d_overflow.ensure(1, 0, c->stream)) return 1;
   std::vector<double> table;
@@ -191,8 +197,13 @@ extern "C" void pp_destroy(pp_context* c)
     c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release(); c->nets[e].d_dw_tiles2.release(); c->nets[e].d_dw_tiles3.release();
   }
   c->d_tile_struct0.release();
+  c->md_self.seg_off.release(); c->md_self.seg_dst.release(); c->md_self.idx.release();
+  for (auto& p : c->md_peers) {
+    p.send_idx.release(); p.sendbuf.release(); p.recvbuf.release();
+    p.add.seg_off.release(); p.add.seg_dst.release(); p.add.idx.release();
+  }
   if (c->d_spec) cudaFree(c->d_spec);
-  for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  for (int i = 0; i < 6; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -201,6 +212,7 @@ extern "C" long long pp_kernel_launches(pp_context* c) { return c ? c->launches 
 extern "C" double pp_last_phase_ms(pp_context* c, int which)
 {
   if (!c || which < 0 || which >= 8) return 0.0;
+  if (which == 7 && c->md_exchange_set) tock(c, 4, 5, 7);      // the exchange's own pair of events (synchronises on them)
   if (c->epoch_phases_pending) {       // the epoch's events are only turned into times when somebody asks
     c->epoch_phases_pending = false;
     tock(c, 0, 1, 1); tock(c, 1, 2, 2); tock(c, 2, 3, 3);
@@ -1329,6 +1341,132 @@ extern "C" int pp_md_step(pp_context* c, const double* x, double* f_inout, doubl
   PP_CUDA(cudaMemcpyAsync(&et, c->d_etotal.p, sizeof(double), cudaMemcpyDeviceToHost, st));
   PP_CUDA(cudaStreamSynchronize(st));
   tock(c, 0, 1, 4); tock(c, 1, 2, 5); tock(c, 2, 3, 6);
+  if (etotal_out) *etotal_out = et;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Reverse communication of ghost forces for a box partitioned over the ranks (what LAMMPS' Comm::reverse_comm does for
+// pair_nn, which leaves forces on ghost atoms, pair_nn.cpp:182).
+static int build_seglist(pp_context* c, pp_context::SegList& L, int n, const int* src, const int* dst, int n_dst_max, const char* what)
+{
+  // stable sort of the values by destination atom -> one segment per destination, values in list order inside it
+  std::vector<int> order(n);
+  for (int k = 0; k < n; k++) {
+    PP_REQUIRE(dst[k] >= 0 && dst[k] < n_dst_max, "pp_md_exchange_setup: %s destination %d out of range", what, dst[k]);
+    order[k] = k;
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return dst[a] < dst[b]; });
+  std::vector<int> seg_off, seg_dst, idx(n);
+  for (int k = 0; k < n; k++) {
+    const int o = order[k];
+    if (k == 0 || dst[o] != dst[order[k - 1]]) { seg_off.push_back(k); seg_dst.push_back(dst[o]); }
+    idx[k] = src ? src[o] : o;
+  }
+  seg_off.push_back(n);
+  L.n_seg = (int)seg_dst.size();
+  cudaStream_t st = c->stream;
+  if (L.seg_off.ensure(seg_off.size(), 0, st) || L.seg_dst.ensure(std::max<size_t>(seg_dst.size(), 1), 0, st) || L.idx.ensure(std::max(n, 1), 0, st)) return 1;
+  PP_CUDA(cudaMemcpyAsync(L.seg_off.p, seg_off.data(), seg_off.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  if (L.n_seg) PP_CUDA(cudaMemcpyAsync(L.seg_dst.p, seg_dst.data(), seg_dst.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  if (n) PP_CUDA(cudaMemcpyAsync(L.idx.p, idx.data(), n * sizeof(int), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaStreamSynchronize(st));      // the host vectors are locals
+  return 0;
+}
+
+extern "C" int pp_md_exchange_setup(pp_context* c, int n_self, const int* self_src, const int* self_dst, int n_peers, const int* peer_rank,
+                                    const int* send_count, const int* send_idx_flat, const int* recv_count, const int* recv_dst_flat)
+{
+  PP_REQUIRE(c && c->md_ntotal > 0, "pp_md_exchange_setup: upload the atoms first (pp_md_build_neighbors)");
+  PP_REQUIRE(n_self >= 0 && n_peers >= 0, "pp_md_exchange_setup: negative count");
+  PP_REQUIRE(n_peers == 0 || c->comm.nranks > 1, "pp_md_exchange_setup: peers given but no communicator (pp_comm_init)");
+  PP_CUDA(cudaSetDevice(c->device));
+  const int nlocal = c->md_nlocal, ntotal = c->md_ntotal;
+  for (int k = 0; k < n_self; k++)
+    PP_REQUIRE(self_src[k] >= nlocal && self_src[k] < ntotal, "pp_md_exchange_setup: own ghost index %d is not a ghost", self_src[k]);
+  if (build_seglist(c, c->md_self, n_self, self_src, self_dst, nlocal, "own-ghost")) return 1;
+  for (auto& p : c->md_peers) {
+    p.send_idx.release(); p.sendbuf.release(); p.recvbuf.release();
+    p.add.seg_off.release(); p.add.seg_dst.release(); p.add.idx.release();
+  }
+  c->md_peers.clear();
+  c->md_peers.resize(n_peers);
+  size_t so = 0, ro = 0;
+  for (int i = 0; i < n_peers; i++) {
+    pp_context::MdPeer& p = c->md_peers[i];
+    PP_REQUIRE(peer_rank[i] >= 0 && peer_rank[i] < c->comm.nranks && peer_rank[i] != c->comm.rank, "pp_md_exchange_setup: bad peer rank %d", peer_rank[i]);
+    p.rank = peer_rank[i];
+    p.n_send = send_count[i];
+    p.n_recv = recv_count[i];
+    for (int k = 0; k < p.n_send; k++)
+      PP_REQUIRE(send_idx_flat[so + k] >= nlocal && send_idx_flat[so + k] < ntotal, "pp_md_exchange_setup: send index %d is not a ghost", send_idx_flat[so + k]);
+    if (p.send_idx.ensure(std::max(p.n_send, 1), 0, c->stream) || p.sendbuf.ensure(3 * (size_t)std::max(p.n_send, 1), 0, c->stream) ||
+        p.recvbuf.ensure(3 * (size_t)std::max(p.n_recv, 1), 0, c->stream))
+      return 1;
+    if (p.n_send) PP_CUDA(cudaMemcpy(p.send_idx.p, send_idx_flat + so, p.n_send * sizeof(int), cudaMemcpyHostToDevice));
+    if (build_seglist(c, p.add, p.n_recv, nullptr, recv_dst_flat + ro, nlocal, "received")) return 1;
+    so += p.n_send;
+    ro += p.n_recv;
+  }
+  c->md_exchange_set = true;
+  return 0;
+}
+
+// forces of ghosts back to their owners (f_dev[ntotal][3], accumulated in place), energy summed over the ranks
+extern "C" int pp_md_exchange_device(pp_context* c, double* f_dev, double* etotal_dev)
+{
+  PP_REQUIRE(c && c->md_exchange_set, "pp_md_exchange_device: call pp_md_exchange_setup first");
+  PP_REQUIRE(f_dev, "pp_md_exchange_device: NULL force array");
+  PP_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  PP_CUDA(cudaEventRecord(c->ev[4], st));
+  const int np = (int)c->md_peers.size();
+  std::vector<int> ranks(np);
+  std::vector<double*> sb(np), rb(np);
+  std::vector<size_t> sn(np), rn(np);
+  for (int i = 0; i < np; i++) {
+    pp_context::MdPeer& p = c->md_peers[i];
+    if (ppk_pack_forces(f_dev, p.send_idx.p, p.n_send, p.sendbuf.p, st, &c->launches)) return 1;
+    ranks[i] = p.rank; sb[i] = p.sendbuf.p; rb[i] = p.recvbuf.p; sn[i] = 3 * (size_t)p.n_send; rn[i] = 3 * (size_t)p.n_recv;
+  }
+  if (c->comm.sendrecv(np, ranks.data(), sb.data(), sn.data(), rb.data(), rn.data(), st)) return 1;
+  // own ghosts first, then the peers in the order given: a fixed order, so the forces are reproducible
+  if (ppk_segment_add(f_dev, c->md_self.seg_off.p, c->md_self.seg_dst.p, c->md_self.n_seg, f_dev, c->md_self.idx.p, st, &c->launches)) return 1;
+  for (int i = 0; i < np; i++) {
+    pp_context::MdPeer& p = c->md_peers[i];
+    if (ppk_segment_add(f_dev, p.add.seg_off.p, p.add.seg_dst.p, p.add.n_seg, p.recvbuf.p, p.add.idx.p, st, &c->launches)) return 1;
+  }
+  if (etotal_dev && c->comm.nranks > 1) {
+    // each rank's total carries the output shift (pair_nn.cpp:175-179 adds it on rank 0 only): keep it once
+    if (c->comm.rank != 0 && c->out_mean != 0.0 && ppk_add_scalar(etotal_dev, -c->out_mean, st, &c->launches)) return 1;
+    if (c->comm.allreduce_device(etotal_dev, 1, st)) return 1;
+  }
+  PP_CUDA(cudaEventRecord(c->ev[5], st));
+  return 0;
+}
+
+// One MD step of a partitioned box through host buffers: x[ntotal][3] uploaded, forces computed on locals and ghosts,
+// ghost forces returned to their owners (on this rank and on the peers), the forces of the nlocal LOCAL atoms
+// downloaded (overwritten, not added), energies downloaded; *etotal_out is the sum over all ranks.
+extern "C" int pp_md_step_exchange(pp_context* c, const double* x, double* f_local_out, double* eatom_out, double* etotal_out)
+{
+  PP_REQUIRE(c && c->md_list_resident && c->md_exchange_set, "pp_md_step_exchange: needs pp_md_build_neighbors and pp_md_exchange_setup");
+  PP_REQUIRE(x, "pp_md_step_exchange: NULL positions");
+  PP_CUDA(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int ntotal = c->md_ntotal, nlocal = c->md_nlocal;
+  if (c->d_etotal.ensure(1, 0, st)) return 1;
+  PP_CUDA(cudaMemcpyAsync(c->d_x.p, x, 3 * (size_t)ntotal * sizeof(double), cudaMemcpyHostToDevice, st));
+  PP_CUDA(cudaMemsetAsync(c->d_f.p, 0, 3 * (size_t)ntotal * sizeof(double), st));
+  if (md_run(c, c->d_x.p, c->d_f.p)) return 1;
+  if (md_energy_total(c, c->d_etotal.p)) return 1;
+  if (pp_md_exchange_device(c, c->d_f.p, c->d_etotal.p)) return 1;
+  if (f_local_out) PP_CUDA(cudaMemcpyAsync(f_local_out, c->d_f.p, 3 * (size_t)nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (eatom_out) PP_CUDA(cudaMemcpyAsync(eatom_out, c->d_eatom.p, nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));
+  double et = 0.0;
+  PP_CUDA(cudaMemcpyAsync(&et, c->d_etotal.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+  PP_CUDA(cudaStreamSynchronize(st));
+  tock(c, 0, 1, 4); tock(c, 1, 2, 5); tock(c, 2, 3, 6); tock(c, 4, 5, 7);
   if (etotal_out) *etotal_out = et;
   return 0;
 }

@@ -11,6 +11,9 @@ typedef int (*fn_get_id)(NcclId*);
 typedef int (*fn_init_rank)(void**, int, NcclId, int);
 typedef int (*fn_allreduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 typedef int (*fn_allgather)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef int (*fn_send)(const void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_recv)(void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_group)(void);
 typedef int (*fn_destroy)(void*);
 typedef const char* (*fn_errstr)(int);
 
@@ -20,6 +23,9 @@ struct NcclApi {
   fn_init_rank init_rank = nullptr;
   fn_allreduce allreduce = nullptr;
   fn_allgather allgather = nullptr;
+  fn_send send = nullptr;
+  fn_recv recv = nullptr;
+  fn_group group_start = nullptr, group_end = nullptr;
   fn_destroy destroy = nullptr;
   fn_errstr errstr = nullptr;
 } g_nccl;
@@ -39,6 +45,10 @@ int load_nccl()
   g_nccl.init_rank = (fn_init_rank)dlsym(h, "ncclCommInitRank");
   g_nccl.allreduce = (fn_allreduce)dlsym(h, "ncclAllReduce");
   g_nccl.allgather = (fn_allgather)dlsym(h, "ncclAllGather");
+  g_nccl.send = (fn_send)dlsym(h, "ncclSend");
+  g_nccl.recv = (fn_recv)dlsym(h, "ncclRecv");
+  g_nccl.group_start = (fn_group)dlsym(h, "ncclGroupStart");
+  g_nccl.group_end = (fn_group)dlsym(h, "ncclGroupEnd");
   g_nccl.destroy = (fn_destroy)dlsym(h, "ncclCommDestroy");
   g_nccl.errstr = (fn_errstr)dlsym(h, "ncclGetErrorString");
   PP_REQUIRE(g_nccl.get_id && g_nccl.init_rank && g_nccl.allreduce && g_nccl.destroy, "NCCL library lacks required symbols");
@@ -237,6 +247,22 @@ int PPComm::reduce_sum(const double* partial, int n_cta, int stride, int ncols_p
                                                        d_peer_err);
   *launches += 2;
   PP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int PPComm::sendrecv(int n_peers, const int* peer, double* const* sendbuf, const size_t* send_n, double* const* recvbuf, const size_t* recv_n,
+                     cudaStream_t st)
+{
+  if (n_peers == 0) return 0;
+  PP_REQUIRE(comm && g_nccl.send && g_nccl.recv && g_nccl.group_start && g_nccl.group_end, "point-to-point exchange needs an initialised communicator");
+  int rc = g_nccl.group_start();
+  PP_REQUIRE(rc == 0, "ncclGroupStart failed: %s", nccl_err(rc));
+  for (int i = 0; i < n_peers; i++) {
+    if (send_n[i]) { rc = g_nccl.send(sendbuf[i], send_n[i], /*ncclDouble*/ 8, peer[i], comm, st); PP_REQUIRE(rc == 0, "ncclSend failed: %s", nccl_err(rc)); }
+    if (recv_n[i]) { rc = g_nccl.recv(recvbuf[i], recv_n[i], /*ncclDouble*/ 8, peer[i], comm, st); PP_REQUIRE(rc == 0, "ncclRecv failed: %s", nccl_err(rc)); }
+  }
+  rc = g_nccl.group_end();
+  PP_REQUIRE(rc == 0, "ncclGroupEnd failed: %s", nccl_err(rc));
   return 0;
 }
 

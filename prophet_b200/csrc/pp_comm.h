@@ -38,6 +38,9 @@ struct PPComm {
   int reduce_sum(const double* partial, int n_cta, int stride, int ncols_partial, int ncols, double* out, cudaStream_t st,
                  long long* launches);
   int peer_setup(size_t need, cudaStream_t st);
+  // grouped point-to-point exchange of doubles with n_peers ranks (ncclGroupStart / ncclSend / ncclRecv / ncclGroupEnd)
+  int sendrecv(int n_peers, const int* peer, double* const* sendbuf, const size_t* send_n, double* const* recvbuf, const size_t* recv_n,
+               cudaStream_t st);
   const char* path() const { return nranks == 1 ? "single rank" : (peer_state == 1 ? "peer memory" : "nccl"); }
   void destroy();
 };

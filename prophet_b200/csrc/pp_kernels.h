@@ -162,3 +162,9 @@ int ppk_scan_counts(const int* counts, long long n, long long* offsets, CellWork
 int ppk_fill_cell_neighbors(const double* x_dev, int nlocal, const CellGrid& g, double cutneigh, CellWork& w, const long long* offsets,
                             int* neigh_out, cudaStream_t st, long long* launches);
 int ppk_sum(const double* v, long long n, double add, double* partial, double* out, cudaStream_t st, long long* launches);
+
+// ---- reverse communication of ghost forces (pp_exchange.cu) -----------------------------------------------------
+int ppk_pack_forces(const double* f, const int* idx, int n, double* out, cudaStream_t st, long long* launches);
+int ppk_add_scalar(double* v, double a, cudaStream_t st, long long* launches);
+int ppk_segment_add(double* f, const int* seg_off, const int* seg_dst, int n_seg, const double* base, const int* idx, cudaStream_t st,
+                    long long* launches);

@@ -333,6 +333,44 @@ def expand_ghosts(cell: np.ndarray, cart: np.ndarray, Z: np.ndarray, halo: float
     return np.concatenate(xs), np.concatenate(zs), len(cart)
 
 
+def slab_partition(cell: np.ndarray, cart: np.ndarray, rank: int, world: int, halo: float):
+    """Rank ``rank``'s share of an orthorhombic periodic box cut into ``world`` slabs along x (what LAMMPS' spatial
+    decomposition hands one MPI rank): the atoms it owns, followed by the ghosts -- every periodic image of any atom that
+    lies within ``halo`` of the slab (and of the box faces in y and z).
+
+    Returns dict(x [nlocal+nghost,3], nlocal, owned_ids [nlocal] global ids (ascending), ghost_rank [nghost] owning rank
+    of each ghost, ghost_local [nghost] its index among the owner's local atoms)."""
+    L = np.diag(cell)
+    assert np.allclose(cell, np.diag(L)), "slab partition implemented for orthorhombic boxes"
+    n = len(cart)
+    width = L[0] / world
+    owner = np.minimum((cart[:, 0] / width).astype(np.int64), world - 1)
+    owner = np.maximum(owner, 0)
+    local_of = np.empty(n, dtype=np.int64)
+    for r in range(world):
+        ids = np.nonzero(owner == r)[0]
+        local_of[ids] = np.arange(len(ids))
+    owned = np.nonzero(owner == rank)[0]
+    xlo, xhi = rank * width, (rank + 1) * width
+    nrep = np.ceil(halo / L).astype(int)
+    gx, gid = [], []
+    idx = np.arange(n)
+    for i in range(-nrep[0], nrep[0] + 1):
+        for j in range(-nrep[1], nrep[1] + 1):
+            for k in range(-nrep[2], nrep[2] + 1):
+                sh = cart + np.array([i, j, k], dtype=np.float64) * L
+                keep = ((sh[:, 0] > xlo - halo) & (sh[:, 0] < xhi + halo) & (sh[:, 1] > -halo) & (sh[:, 1] < L[1] + halo) &
+                        (sh[:, 2] > -halo) & (sh[:, 2] < L[2] + halo))
+                if i == 0 and j == 0 and k == 0:
+                    keep &= owner != rank
+                gx.append(sh[keep])
+                gid.append(idx[keep])
+    gid = np.concatenate(gid)
+    x = np.concatenate([cart[owned]] + gx)
+    return dict(x=np.ascontiguousarray(x), nlocal=len(owned), owned_ids=owned, ghost_rank=owner[gid].astype(np.int32),
+                ghost_local=local_of[gid].astype(np.int32))
+
+
 def brute_full_neighbor_list(x: np.ndarray, nlocal: int, cutneigh: float):
     """Full list (locals -> locals+ghosts) with LAMMPS' test rsq < cutneigh^2, ascending j."""
     numneigh = np.zeros(nlocal, dtype=np.int32)
