@@ -40,8 +40,15 @@ const char* pp_last_error(void);
 int pp_version(void);
 
 /* ---- context --------------------------------------------------------------------------------------------- */
-/* Create a context on CUDA device `device`.  fp_mode: 64 (only mode implemented).  Replaces nothing in the
- * reference (it has no device); plays the role of the Potential constructor's resource set-up. */
+/* Create a context on CUDA device `device`.  Replaces nothing in the reference (it has no device); plays the role of
+ * the Potential constructor's resource set-up.
+ * fp_mode 64: every kernel in IEEE double, the reference's REAL (Common.h:59); results within relative 1e-10.
+ * fp_mode 32: the reference's USE_FLOAT switch (Common.h:53-61; its own float build does not compile, so the FP64
+ *   reference at relative 1e-5 is the yardstick).  Training epochs of single-element systems with tanh hidden layers
+ *   (one or two, up to 64 wide, structures of up to 256 atoms) run in single precision: the descriptors are kept as
+ *   normalised FP32 and the layer products are 3xTF32 tensor-core products accumulated in FP32; structure energies,
+ *   errors, loss terms and the final gradient sum stay FP64 (pp_epoch_form == 4).  Descriptors, neighbour lists,
+ *   evaluation, MD and every other system keep the FP64 kernels in this mode. */
 int pp_create(int device, int fp_mode, pp_context** out);
 void pp_destroy(pp_context* ctx);
 
@@ -114,7 +121,8 @@ int pp_epoch_result_dev(pp_context* ctx, double** result_dev, int* n);
  * forward pass recomputed: any system), 1 = single-pass fused kernel, one CTA per SM, 2 = single-pass fused kernel with
  * in-place deltas, two CTAs per SM (single element, tanh / tanh_spline hidden nodes), 3 = two launches per element with
  * the activations kept in HBM between them (several elements, or networks too large for the single-pass kernels; even
- * layer widths up to 64, at most four hidden layers).  Same arithmetic in every form, different summation order.
+ * layer widths up to 64, at most four hidden layers), 4 = the single-precision single-pass kernel of fp_mode 32.
+ * Same arithmetic in forms 0 - 3, different summation order.
  * -1 before the first epoch.  Environment: PP_MLP_ONE_CTA=1 keeps form 2 from being chosen, PP_MLP_NO_STORE=1 form 3.
  * No reference counterpart. */
 int pp_epoch_form(pp_context* ctx);

@@ -55,7 +55,8 @@ struct NetHost {
   std::vector<double> params, mean, scale;
   DevBuf<double> d_mean, d_scale;
   DevBuf<int> d_tf;
-  DevBuf<unsigned char> d_dw_tiles, d_dw_tiles2, d_dw_tiles3;
+  DevBuf<unsigned char> d_dw_tiles, d_dw_tiles2, d_dw_tiles3, d_dw_tiles32;
+  bool has_tiles32 = false;            // eligible for the FP32-mode training kernel (pp_mlp32.cu)
   bool has_tiles2 = false;
   bool has_tiles3 = false;             // eligible for the two-phase kernels with stored activations (pp_mlpw.cu)
   int tile_atoms = 0;
@@ -64,6 +65,10 @@ struct NetHost {
 
 struct pp_context {
   int device = 0;
+  int fp_mode = 64;                    // 32: training epochs of eligible systems run in single precision (pp_mlp32.cu)
+  DevBuf<float> d_G32;                 // FP32 mode: normalised descriptors [atoms][NGp]
+  DevBuf<double> d_ms32;               // FP32 mode: mean and scale of every element, [2][n_elem][NG]
+  bool g32_dirty = true;
   cudaStream_t stream = nullptr;
   long long launches = 0;
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -105,6 +110,7 @@ struct pp_context {
   size_t h_result_cap = 0;
   // fused single-pass epoch: tiles of whole structures
   bool tiles_dirty = true, fused_ok = false;
+  int tiles_tm = 0;                    // tile size the list was packed for
   int n_fused_tiles = 0;
   DevBuf<int> d_tile_struct0;
 
@@ -153,7 +159,7 @@ static int tock(pp_context* c, int i0, int i1, int which)
 extern "C" int pp_create(int device, int fp_mode, pp_context** out)
 {
   PP_REQUIRE(out != nullptr, "pp_create: out is NULL");
-  PP_REQUIRE(fp_mode == 64, "pp_create: fp_mode %d not implemented (only 64)", fp_mode);
+  PP_REQUIRE(fp_mode == 64 || fp_mode == 32, "pp_create: fp_mode %d not implemented (64 or 32)", fp_mode);
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   PP_REQUIRE(e == cudaSuccess && ndev > 0, "pp_create: no CUDA device available (%s); this library has no CPU fallback",
@@ -162,6 +168,7 @@ extern "C" int pp_create(int device, int fp_mode, pp_context** out)
   PP_CUDA(cudaSetDevice(device));
   pp_context* c = new pp_context();
   c->device = device;
+  c->fp_mode = fp_mode;
   PP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   for (int i = 0; i < 6; i++) PP_CUDA(cudaEventCreate(&c->ev[i]));
   PP_CUDA(cudaMalloc(&c->d_spec, sizeof(DescSpec)));
@@ -194,9 +201,9 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_cell_start.release(); c->d_scan_sums.release(); c->d_scan_total.release(); c->d_sum_partial.release(); c->d_etotal.release();
   for (int e = 0; e < PP_MAX_ELEM; e++) {
     c->d_rows[e].release(); c->d_md_rows[e].release(); c->d_hstore[e].release(); c->d_tstore[e].release();
-    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release(); c->nets[e].d_dw_tiles2.release(); c->nets[e].d_dw_tiles3.release();
+    c->nets[e].d_mean.release(); c->nets[e].d_scale.release(); c->nets[e].d_tf.release(); c->nets[e].d_dw_tiles.release(); c->nets[e].d_dw_tiles2.release(); c->nets[e].d_dw_tiles3.release(); c->nets[e].d_dw_tiles32.release();
   }
-  c->d_tile_struct0.release();
+  c->d_tile_struct0.release(); c->d_G32.release(); c->d_ms32.release();
   c->md_self.seg_off.release(); c->md_self.seg_dst.release(); c->md_self.idx.release();
   for (auto& p : c->md_peers) {
     p.send_idx.release(); p.sendbuf.release(); p.recvbuf.release();
@@ -458,6 +465,16 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
       PP_CUDA(cudaMemcpy(n.d_dw_tiles2.p, t2.data(), t2.size(), cudaMemcpyHostToDevice));
       n.has_tiles2 = true;
     }
+    int n32 = 0;
+    n.has_tiles32 = false;
+    const int esz = ppk_mlp32_table(n.dev, nullptr, &n32);
+    if (esz > 0 && n32 > 0) {
+      std::vector<unsigned char> t32((size_t)n32 * esz);
+      ppk_mlp32_table(n.dev, t32.data(), &n32);
+      if (n.d_dw_tiles32.ensure(t32.size(), 0, c->stream)) return 1;
+      PP_CUDA(cudaMemcpy(n.d_dw_tiles32.p, t32.data(), t32.size(), cudaMemcpyHostToDevice));
+      n.has_tiles32 = true;
+    }
     int n3 = 0;
     n.has_tiles3 = false;
     if (ppk_mlpw_table(n.dev, nullptr, &n3) && n3 > 0) {
@@ -469,6 +486,7 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
     }
   }
   c->tiles_dirty = true;
+  c->g32_dirty = true;
   n.set = true;
   return rebuild_param_layout(c);
 }
@@ -517,6 +535,7 @@ extern "C" int pp_set_input_scaling(pp_context* c, int elem, const double* in_me
   int NG = n.sizes[0];
   n.mean.assign(in_mean, in_mean + NG);
   n.scale.assign(in_scale, in_scale + NG);
+  c->g32_dirty = true;
   PP_CUDA(cudaMemcpy(n.d_mean.p, n.mean.data(), NG * sizeof(double), cudaMemcpyHostToDevice));
   PP_CUDA(cudaMemcpy(n.d_scale.p, n.scale.data(), NG * sizeof(double), cudaMemcpyHostToDevice));
   return 0;
@@ -650,6 +669,7 @@ extern "C" int pp_add_structures(pp_context* c, int n_struct, const int* natoms,
   c->n_struct = ns;
   c->n_atoms = na;
   c->tiles_dirty = true;
+  c->g32_dirty = true;
   // per-element row lists (structure-major)
   for (int e = 0; e < S.n_elem; e++) {
     size_t before = c->h_rows[e].size();
@@ -680,6 +700,7 @@ extern "C" int pp_recompute_descriptors(pp_context* c)
   PeriodicArgs a = periodic_args(c);
   a.n_atoms = c->n_atoms;
   a.atom_begin = 0;
+  c->g32_dirty = true;
   if (tick(c, 0)) return 1;
   if (ppk_desc_periodic(c->spec, a, &c->desc_cap, c->stream, &c->launches)) return 1;
   if (tick(c, 1)) return 1;
@@ -852,14 +873,20 @@ static MlpArgs mlp_args_train(pp_context* c, int e)
 
 // Single-element systems whose structures each fit one MLP tile take the fused single-pass epoch: tiles are
 // runs of whole consecutive structures, packed greedily up to the tile size.
+static bool fp32_epoch(pp_context* c)
+{
+  return c->fp_mode == 32 && c->spec.n_elem == 1 && c->nets[0].set && c->nets[0].has_tiles32 && getenv("PP_FP32_OFF") == nullptr;
+}
+
 static int prepare_fused_tiles(pp_context* c)
 {
-  if (!c->tiles_dirty) return 0;
+  const int TM = (c->spec.n_elem == 1 && c->nets[0].set) ? (fp32_epoch(c) ? ppk_mlp32_tile_atoms() : c->nets[0].tile_atoms) : 0;
+  if (!c->tiles_dirty && c->tiles_tm == TM) return 0;
   c->tiles_dirty = false;
+  c->tiles_tm = TM;
   c->fused_ok = false;
   c->n_fused_tiles = 0;
   if (c->spec.n_elem != 1 || !c->nets[0].set || c->n_struct == 0) return 0;
-  const int TM = c->nets[0].tile_atoms;
   std::vector<int> t0;
   t0.push_back(0);
   int used = 0;
@@ -990,9 +1017,26 @@ extern "C" int pp_epoch_device(pp_context* c)
     PP_CUDA(cudaMemsetAsync(c->d_result.p, 0, (size_t)stride * sizeof(double), c->stream));
     c->epoch_form = -1;
   } else {
-    const int form = choose_epoch_form(c);
+    const int form = (fp32_epoch(c) && c->fused_ok) ? 4 : choose_epoch_form(c);
     c->epoch_form = form;
-    if (form == 1 || form == 2) {
+    if (form == 4) {
+      // FP32 mode: one pass on 3xTF32 products over the normalised FP32 copy of the descriptors (refreshed when the
+      // descriptors or the input scaling changed)
+      const int NG = c->spec.NG, NGp = ppk_mlp32_pitch(c->nets[0].dev);
+      if (c->g32_dirty) {
+        if (c->d_G32.ensure((size_t)c->n_atoms * NGp, 0, c->stream) || c->d_ms32.ensure(2 * (size_t)NG, 0, c->stream)) return 1;
+        PP_CUDA(cudaMemcpyAsync(c->d_ms32.p, c->nets[0].mean.data(), NG * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        PP_CUDA(cudaMemcpyAsync(c->d_ms32.p + NG, c->nets[0].scale.data(), NG * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        if (ppk_g_to_f32(c->d_G.p, NG, NGp, c->n_atoms, nullptr, c->d_ms32.p, c->d_ms32.p + NG, c->d_G32.p, c->stream, &c->launches)) return 1;
+        c->g32_dirty = false;
+      }
+      if (tick(c, 1)) return 1;
+      MlpArgs a = mlp_args_train(c, 0);
+      a.dw_tiles2 = c->nets[0].d_dw_tiles32.p;
+      int n_cta = 0;
+      if (ppk_mlp32_launch_fused(a, c->d_G32.p, c->n_atoms, c->stream, &c->launches, &n_cta)) return 1;
+      red_rows = n_cta; red_cols = stride;
+    } else if (form == 1 || form == 2) {
       // one pass: forward, per-structure error and backward in the same kernel; loss terms ride in the partials' tail
       if (tick(c, 1)) return 1;
       MlpArgs a = mlp_args_train(c, 0);

@@ -116,6 +116,16 @@ int ppk_mlpw_store_width(const NetDev& net);                           // double
 int ppk_mlpw_forward(const MlpArgs& a, const MlpwStore& st, cudaStream_t stream, long long* launches);
 int ppk_mlpw_backward(const MlpArgs& a, const MlpwStore& st, cudaStream_t stream, long long* launches, int* n_cta);
 
+// ---- FP32 mode (pp_mlp32.cu): descriptors kept as FP32, single-pass training epoch on 3xTF32 tensor-core products ----
+bool ppk_tiled_map_f32(const float* base, int cols, int pitch_floats, long long rows, int box_cols, int box_rows, void* out_map);
+bool ppk_mlp32_ok(const NetDev& net);
+int ppk_mlp32_pitch(const NetDev& net);                 // row pitch (floats) of the FP32 descriptor array
+int ppk_mlp32_tile_atoms(void);
+int ppk_mlp32_table(const NetDev& net, void* host_out, int* n_entries);      // returns the entry size in bytes (0: not eligible)
+int ppk_g_to_f32(const double* G, int NG, int NGp, long long n_atoms, const int* elem, const double* mean, const double* scale, float* out,
+                 cudaStream_t st, long long* launches);
+int ppk_mlp32_launch_fused(const MlpArgs& a, const float* G32, long long n_atoms, cudaStream_t st, long long* launches, int* n_cta);
+
 // per-structure energies / errors (Potential.cpp:641-668)
 struct StructArgs {
   int n_struct;

@@ -757,6 +757,19 @@ bool ppk_tiled_map(const double* G, int NG, long long atoms, int box_cols, int b
   return true;
 }
 
+// the same for an FP32 array whose rows are `pitch_floats` apart (FP32 mode); not cached: one per epoch launch
+bool ppk_tiled_map_f32(const float* base, int cols, int pitch_floats, long long rows, int box_cols, int box_rows, void* out_map)
+{
+  if (encode_tiled() == nullptr) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t gstride[1] = {(cuuint64_t)pitch_floats * sizeof(float)};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return encode_tiled()(reinterpret_cast<CUtensorMap*>(out_map), CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box,
+                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static int g_sm_count = 0;
 int ppk_sm_count(void)
 {

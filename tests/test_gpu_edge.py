@@ -141,7 +141,7 @@ def test_error_returns_are_messages_not_crashes():
         with pytest.raises(capi.PPError, match="no structures"):
             ctx.epoch()
         with pytest.raises(capi.PPError, match="fp_mode"):
-            capi.Context(0, fp_mode=32)
+            capi.Context(0, fp_mode=16)
         # clear and re-add
         cell, cart, Z, _, _ = synth.make_structure(cfg, 1)
         frac = capi.cart_to_frac(cell, cart)
