@@ -13,7 +13,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libprophet_b200.so")
+LIB_PATH = os.environ.get("PP_LIB_PATH") or os.path.join(_HERE, "libprophet_b200.so")      # PP_LIB_PATH: tuning builds (tools/)
 _LIB = None
 
 TRANSFER_IDS = {"linear": 0, "tanh": 1, "tanh_spline": 2, "tanh_crazy": 3, "cubic": 4, "pulse": 5, "sin": 6,

@@ -11,8 +11,8 @@
 #define PP_MAX_PAIR_ROWS 32    // G1 + G2 rows
 #define PP_MAX_G4_ROWS 64
 #define PP_MAX_G3_ROWS 16
-#define PP_MAX_RAD 16          // distinct (Rc, fc, eta) among G4 rows
-#define PP_MAX_ANG 16          // distinct (xi, lambda) among G4 rows
+#define PP_MAX_RAD 64          // distinct (Rc, fc, eta) among G4 rows: up to every row its own (the -optimize search perturbs them all)
+#define PP_MAX_ANG 64          // distinct (xi, lambda) among G4 rows
 #define PP_MAX_LAYERS 8        // weight layers per net (hidden + output)
 #define PP_WARP 32
 

@@ -4,7 +4,9 @@
 
 #define DESC_WARPS 4
 #ifndef DESC_BLOCKS_PER_SM
+#ifndef DESC_BLOCKS_PER_SM
 #define DESC_BLOCKS_PER_SM 4      // 16 warps per SM (<= 128 registers)
+#endif
 #endif
 
 // ---------------------------------------------------------------------------------------------------------
@@ -105,7 +107,7 @@ md_desc_kernel(MdArgs a)
 
 // MD forces: Structure::Get_Forces non-periodic branch (Structure.cpp:429-713) with dE/dG given.
 template <int NR_T, int NX, bool BASIS>
-__global__ void __launch_bounds__(DESC_WARPS * 32, 4)
+__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
 md_force_kernel(MdArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -174,6 +176,9 @@ static int max_cap_for(int NR, int NG, bool force)
 {
   int cap = 32;
   while (pp_warp_smem_bytes(cap * 2, NR, NG, force) * DESC_WARPS <= 110 * 1024) cap *= 2;      // two blocks per SM at least
+  // many distinct radial keys (every row its own after the -optimize search perturbed them): one block per SM rather
+  // than refusing shells of more than 32 neighbours
+  while (cap < 128 && pp_warp_smem_bytes(cap * 2, NR, NG, force) * DESC_WARPS <= 220 * 1024) cap *= 2;
   return cap;
 }
 

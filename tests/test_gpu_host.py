@@ -122,6 +122,39 @@ def test_cli_line_search_training_matches_reference_cli(algorithm, tmp_path):
     assert rel_err(a["params"], b["params"]) < 1e-7
 
 
+@pytest.mark.skipif(not os.path.exists(REF_CLI), reason="oracle/_ref/PROPhet not built")
+@pytest.mark.parametrize("extra", [("precondition_output = true",), ("sgd = true", "seed = 7"), ("regularization = 1e-3",),
+                                   ("precondition_output = true", "regularization = 5e-4", "sgd = true", "seed = 3")])
+def test_cli_training_options_match_reference_cli(extra, tmp_path):
+    """The training options that change the arithmetic around the GPU epoch: output preconditioning
+    (Potential.cpp:461-495), the shuffled visiting order of `sgd` (Potential.cpp:632-634: a full-batch pass in a different
+    order, same libc rand() stream) and the L2 term of the optimizer (Optimizer.cpp:897-905).  Same input_file,
+    PROPhet.xml and checkpoint_in for both programs; the training table and the saved potentials must agree."""
+    assert os.path.exists(hostapi.CLI_PATH), "PROPhet_b200 not built"
+    # `sgd` is compared on a single-element system: with several elements the reference's shuffled order trips over its
+    # own accumulator reset (NN.cpp:629-646 resets a net's dOutput/dParameters when i_sys changes or when ITS cursor
+    # wraps; a system visited last in one epoch and first in the next leaves the other elements' nets un-reset), which
+    # corrupts the printed gradient norm of those epochs.  That stale sum is not reproduced (DESIGN.md, quirks).
+    cfg = synth.CONFIGS["C2" if any(e.startswith("sgd") for e in extra) else "C3"](6)
+    ours = tmp_path / "ours"; ref = tmp_path / "ref"
+    for d in (ours, ref):
+        d.mkdir()
+        _write_case(str(d), cfg, 6, [0, 0, 1, 0, 0, 2], [7, 5], seed=15, niter=6, extra=extra)
+    out_ref = _run(REF_CLI, ["-in", "input_file", "-train"], str(ref))
+    out_ours = _run(hostapi.CLI_PATH, ["-in", "input_file", "-train"], str(ours))
+    t_ref, t_ours = _iteration_table(out_ref), _iteration_table(out_ours)
+    assert len(t_ref) == 6 and len(t_ours) == 6, (out_ref[-1500:], out_ours[-1500:])
+    assert np.allclose(np.array(t_ours), np.array(t_ref), rtol=2e-6, atol=0), (t_ours, t_ref)
+    for z in cfg.elements:
+        sym = synth.Z_TO_SYMBOL[z]
+        a = ckpt.read_checkpoint(str(ours / ("trained_" + sym)))
+        b = ckpt.read_checkpoint(str(ref / ("trained_" + sym)))
+        assert rel_err(a["params"], b["params"]) < 1e-9
+        for k in ("out_mean", "out_scale"):
+            if k in a and k in b:
+                assert abs(a[k] - b[k]) <= 1e-11 * max(abs(b[k]), 1e-300)
+
+
 @pytest.mark.parametrize("name", ["si_md", "tio2_md"])
 def test_pair_style_nn_through_lammps_stand_in(name, tmp_path):
     """pair_style nn <Rcut> / pair_coeff <type> <file> / compute(), with checkpoint files in the reference's format."""

@@ -366,3 +366,77 @@ def test_neighbour_counts_across_the_tail_pass_split(rcut):
         assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
     finally:
         ctx.close()
+
+
+def test_default_auto_generated_rows_descriptors_and_forces_vs_oracle():
+    """What a user who writes no G rows gets (Structure::init_G, Structure.cpp:816-850, `Nradial 8`, `Nangular 8`): G2
+    rows with one eta and eight Rs, G4 rows with xi = 1, 6, 11, 16 and lambda = +-1 -- odd exponents that the power
+    basis does not cover, so the general angular path runs.  Periodic descriptors and neighbour lists, then the MD
+    branch and the force chain rule on the ghost-expanded cell, against the oracle."""
+    from prophet_b200 import hostapi
+    g2, g4 = hostapi.auto_rows(6.0, 8, 8)
+    assert sorted({float(r[3]) for r in g4}) == [1.0, 6.0, 11.0, 16.0]
+    cfg = synth.config_c3(2)
+    cfg.lattice = synth.lattice_tio2((2, 2, 3))
+    cfg.G1, cfg.G3 = [], []
+    cfg.G2, cfg.G4 = [list(r) for r in g2], [list(r) for r in g4]
+    zmap = {z: i for i, z in enumerate(cfg.elements)}
+    cell, cart, Z, _, _ = synth.make_structure(cfg, 910)
+    frac = capi.cart_to_frac(cell, cart)
+    elem = np.array([zmap[int(z)] for z in Z], dtype=np.int32)
+    ne = len(cfg.elements)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        ctx.add_structures([len(Z)], cell[None], frac, elem, [0.0], [0])
+        G = ctx.get_descriptors(0)
+        Gref = oracle.descriptors_periodic(cell, frac, elem, ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        assert rel_err(G, Gref) < TOL, rel_err(G, Gref)
+        x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + 1.0)
+        numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+        elem_all = np.array([zmap[int(z)] for z in Zall], dtype=np.int32)
+        for e, z in enumerate(cfg.elements):
+            net = synth.random_network(cfg, z, 19)
+            ctx.set_network(e, net["sizes"], net["params"], 0.1 * synth.normal(z, cfg.NG, 3), 0.5 + np.abs(synth.normal(z, cfg.NG, 4)))
+        ctx.md_set_types([0] + list(range(ne)))
+        r = ctx.md_compute(x, elem_all + 1, nlocal, offsets, flat, want_G=True, want_dEdG=True)
+        Gmd = oracle.descriptors_md(x, elem_all, nlocal, offsets, flat, ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
+        assert rel_err(r["G"], Gmd) < TOL
+        fo = oracle.forces_md(x, elem_all, nlocal, offsets, flat, ne, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut, r["dEdG"])
+        assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
+    finally:
+        ctx.close()
+
+
+def test_forty_distinct_g4_keys_the_optimize_search_on_c2_rows():
+    """Potential::optimize_Gs (Potential.cpp:709-877) perturbs eta, xi of EVERY row, so C2's 40 G4 rows become 40
+    distinct (Rc, fc, eta) keys and 40 distinct non-integer (xi, lambda) keys: the general angular path walks the
+    whole 40 x 40 key grid in chunks.  pp_set_descriptors with new row parameters + pp_recompute_descriptors against
+    the oracle, descriptors and forces."""
+    cfg = synth.config_c2(1)
+    rng = np.random.RandomState(3)
+    g2 = [[r[0], r[1], r[2] * (1.0 + 0.1 * rng.rand()), r[3]] for r in cfg.G2]
+    g4 = [[r[0], r[1], r[2] * (1.0 + 0.1 * rng.rand()), r[3] * (1.0 + 0.1 * rng.rand()), r[4]] for r in cfg.G4]
+    assert len({(r[0], r[1], r[2]) for r in g4}) == 40 and len({(r[3], r[4]) for r in g4}) == 40
+    cell, cart, Z, _, _ = synth.make_structure(cfg, 920)
+    frac = capi.cart_to_frac(cell, cart)
+    elem = np.zeros(len(Z), dtype=np.int32)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(1, cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)          # the power-basis rows first
+        ctx.add_structures([len(Z)], cell[None], frac, elem, [0.0], [0])
+        ctx.set_descriptors(1, cfg.G1, g2, cfg.G3, g4, cfg.rcut)                  # then the perturbed parameters, in place
+        ctx.recompute_descriptors()
+        G = ctx.get_descriptors(0)
+        Gref = oracle.descriptors_periodic(cell, frac, elem, 1, cfg.G1, g2, cfg.G3, g4, cfg.rcut)
+        assert rel_err(G, Gref) < TOL, rel_err(G, Gref)
+        x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + 1.0)
+        numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+        net = synth.random_network(cfg, 14, 21)
+        ctx.set_network(0, net["sizes"], net["params"], 0.1 * synth.normal(14, cfg.NG, 3), 0.5 + np.abs(synth.normal(14, cfg.NG, 4)))
+        ctx.md_set_types([0, 0])
+        r = ctx.md_compute(x, np.ones(len(x), dtype=np.int32), nlocal, offsets, flat, want_G=True, want_dEdG=True)
+        fo = oracle.forces_md(x, np.zeros(len(x), dtype=np.int32), nlocal, offsets, flat, 1, cfg.G1, g2, cfg.G3, g4, cfg.rcut, r["dEdG"])
+        assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
+    finally:
+        ctx.close()
