@@ -201,7 +201,9 @@ int pp_comm_allreduce_host(pp_context* ctx, double* buf, int n);
  *   - n_cols <= 512, otherwise the call fails with an error (use pp_precondition, which allocates);
  *   - the array is held by every GPU that loads the library until the process exits;
  *   - one array per GPU, shared by all calls: calls that could overlap on the same GPU must be serialised by the caller;
- *   - the first call on a GPU resolves the array's address (a set-up step): make it before any stream capture.
+ *   - the first call on a GPU resolves the array's address (a set-up step): make it before any stream capture, and
+ *     do not let two first calls for the same GPU run at the same time on different threads;
+ *   - the caller's current device is the same after the call as before it.
  * All pointers are DEVICE pointers; `stream` is a cudaStream_t (NULL = default stream); the call does not synchronise. */
 int pp_column_sums_static(int device, const double* matrix_dev, long long n_rows, int n_cols,
                           const double* shift_dev, int squared, double* sums_out_dev, void* stream);

@@ -247,7 +247,11 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
                    c->spec.nG4 == nG4 && c->spec.Rcut == Rcut,
                "pp_set_descriptors: structures already added; only row parameters may change (same counts and Rcut), "
                "otherwise call pp_clear_structures first");
-  DescSpec& S = c->spec;
+  PP_CUDA(cudaSetDevice(c->device));
+  // the new specification is assembled in a local and committed (host copy, device copy, flags) only after every check
+  // passed: a rejected call leaves the context as it was
+  DescSpec S_new;
+  DescSpec& S = S_new;
   memset(&S, 0, sizeof(S));
   S.n_elem = n_elem; S.nG1 = nG1; S.nG2 = nG2; S.nG3 = nG3; S.nG4 = nG4;
   S.npair = nG1 + nG2; S.ntrip = nG3 + nG4;
@@ -376,7 +380,11 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
       index += S.ntrip;
     }
   PP_CUDA(cudaMemcpy(c->d_spec, &S, sizeof(S), cudaMemcpyHostToDevice));
+  if (c->spec_set && c->spec.NG != S.NG)
+    for (int e = 0; e < PP_MAX_ELEM; e++) c->nets[e].set = false;      // networks of the old input width no longer apply
+  c->spec = S;
   c->spec_set = true;
+  c->g32_dirty = true;
   return 0;
 }
 
@@ -407,6 +415,7 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
                               const double* params, const double* in_mean, const double* in_scale)
 {
   PP_REQUIRE(c && c->spec_set, "pp_set_network: call pp_set_descriptors first");
+  PP_CUDA(cudaSetDevice(c->device));
   PP_REQUIRE(elem >= 0 && elem < c->spec.n_elem, "pp_set_network: element index %d out of range", elem);
   PP_REQUIRE(n_layers >= 1 && n_layers <= PP_MAX_LAYERS, "pp_set_network: %d weight layers (max %d)", n_layers, PP_MAX_LAYERS);
   PP_REQUIRE(sizes[0] == c->spec.NG, "pp_set_network: input width %d != number of descriptors %d", sizes[0], c->spec.NG);
@@ -511,6 +520,7 @@ static int nets_ready(pp_context* c)
 extern "C" int pp_set_parameters(pp_context* c, const double* params)
 {
   if (nets_ready(c)) return 1;
+  PP_CUDA(cudaSetDevice(c->device));
   for (int e = 0; e < c->spec.n_elem; e++) {
     NetHost& n = c->nets[e];
     std::copy(params + n.p_off, params + n.p_off + n.P, n.params.begin());
@@ -523,6 +533,7 @@ extern "C" int pp_set_parameters(pp_context* c, const double* params)
 extern "C" int pp_get_parameters(pp_context* c, double* params)
 {
   if (nets_ready(c)) return 1;
+  PP_CUDA(cudaSetDevice(c->device));
   PP_CUDA(cudaMemcpyAsync(params, c->d_params.p, c->P_total * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   PP_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
@@ -531,6 +542,7 @@ extern "C" int pp_get_parameters(pp_context* c, double* params)
 extern "C" int pp_set_input_scaling(pp_context* c, int elem, const double* in_mean, const double* in_scale)
 {
   PP_REQUIRE(c && elem >= 0 && elem < PP_MAX_ELEM && c->nets[elem].set, "pp_set_input_scaling: no network for element %d", elem);
+  PP_CUDA(cudaSetDevice(c->device));
   NetHost& n = c->nets[elem];
   int NG = n.sizes[0];
   n.mean.assign(in_mean, in_mean + NG);
@@ -727,6 +739,7 @@ extern "C" long long pp_num_atoms(pp_context* c) { return c ? c->n_atoms : -1; }
 extern "C" int pp_get_descriptors(pp_context* c, int s, double* G_out)
 {
   PP_REQUIRE(c && s >= 0 && s < c->n_struct, "pp_get_descriptors: structure %d out of range", s);
+  PP_CUDA(cudaSetDevice(c->device));
   const int NG = c->spec.NG;
   const long long a0 = c->h_struct_atom0[s];
   const int n = (int)(c->h_struct_atom0[s + 1] - a0);
@@ -742,6 +755,7 @@ extern "C" int pp_get_neighbors(pp_context* c, int s, int* neigh_offset, int* ne
                                 int* n_pairs, int* n_images)
 {
   PP_REQUIRE(c && s >= 0 && s < c->n_struct, "pp_get_neighbors: structure %d out of range", s);
+  PP_CUDA(cudaSetDevice(c->device));
   const long long a0 = c->h_struct_atom0[s];
   const int n = (int)(c->h_struct_atom0[s + 1] - a0);
   cudaStream_t st = c->stream;
@@ -1087,6 +1101,7 @@ extern "C" int pp_epoch_form(pp_context* c) { return c ? c->epoch_form : -1; }
 extern "C" int pp_epoch_result_dev(pp_context* c, double** result_dev, int* n)
 {
   PP_REQUIRE(c && result_dev && n, "pp_epoch_result_dev: bad arguments");
+  PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
   *result_dev = c->d_result.p;
   *n = c->P_total + 3;
@@ -1106,6 +1121,7 @@ extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out
 {
   const double t0 = now_us();
   if (nets_ready(c)) return 1;
+  PP_CUDA(cudaSetDevice(c->device));
   // pinned staging: [P_total + 3] results, then [P_total] parameters (a DMA each way whatever the caller's memory is)
   const size_t need = 2 * (size_t)c->P_total + 3;
   if (c->h_result_cap < need) {
@@ -1159,6 +1175,7 @@ extern "C" int pp_evaluate(pp_context* c, double* E_out)
 extern "C" int pp_get_atom_energies(pp_context* c, int s, double* E_atom_out)
 {
   PP_REQUIRE(c && s >= 0 && s < c->n_struct, "pp_get_atom_energies: structure %d out of range", s);
+  PP_CUDA(cudaSetDevice(c->device));
   const long long a0 = c->h_struct_atom0[s];
   const int n = (int)(c->h_struct_atom0[s + 1] - a0);
   PP_CUDA(cudaMemcpyAsync(E_atom_out, c->d_E_atom.p + a0, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -1341,6 +1358,7 @@ extern "C" int pp_md_build_neighbors(pp_context* c, const double* x, const int* 
 extern "C" int pp_md_get_neighbors(pp_context* c, long long* neigh_offsets, int* neigh_flat, long long* n_total)
 {
   PP_REQUIRE(c && c->md_list_resident, "pp_md_get_neighbors: no resident list (call pp_md_build_neighbors)");
+  PP_CUDA(cudaSetDevice(c->device));
   if (n_total) *n_total = c->md_nneigh;
   if (neigh_offsets) PP_CUDA(cudaMemcpyAsync(neigh_offsets, c->d_neigh_off.p, (c->md_nlocal + 1) * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
   if (neigh_flat && c->md_nneigh) PP_CUDA(cudaMemcpyAsync(neigh_flat, c->d_neigh.p, c->md_nneigh * sizeof(int), cudaMemcpyDeviceToHost, c->stream));

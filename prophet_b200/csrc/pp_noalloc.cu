@@ -72,6 +72,8 @@ extern "C" int pp_column_sums_static(int device, const double* matrix_dev, long 
   PP_REQUIRE(n_cols <= PP_STATIC_MAX_COLS,
              "pp_column_sums_static: %d columns exceed the fixed scratch capacity of %d columns; use pp_precondition "
              "(which allocates) for wider matrices", n_cols, PP_STATIC_MAX_COLS);
+  int caller_device = device;
+  PP_CUDA(cudaGetDevice(&caller_device));      // the caller's current device is put back before returning
   PP_CUDA(cudaSetDevice(device));
   if (g_static_partial_addr[device] == nullptr) {
     // one-time set-up on this GPU (with it current): resolve the array's device address
@@ -87,5 +89,6 @@ extern "C" int pp_column_sums_static(int device, const double* matrix_dev, long 
   PP_CUDA(cudaGetLastError());
   column_final_static_kernel<<<(n_cols + 127) / 128, 128, 0, st>>>(partial, PP_STATIC_BLOCKS, n_cols, sums_out_dev);
   PP_CUDA(cudaGetLastError());
+  if (caller_device != device) PP_CUDA(cudaSetDevice(caller_device));
   return 0;
 }

@@ -139,56 +139,85 @@ int transfer_id(const std::string& name);
 class Optimizer {
  public:
   Optimizer(Parallel* mpi, const FunctionalParams& params, int Nsystems);
-  void init(const std::vector<REAL>& x0);                 // internal_init (Optimizer.cpp:242-289)
-  // Optimizer::update_network (:884-1064).  Error/grad are already summed over ranks (the allreduce inside pp_epoch).
+  void init(const std::vector<REAL>& x0);                 // starting point + table header (Optimizer.cpp:242-289)
+  // one call per epoch (Optimizer.cpp:884-1064).  Error/grad are already summed over ranks (the sum inside pp_epoch).
   void update_network(REAL Error, const std::vector<REAL>& grad);
-  void set_val_sse(REAL sse, long long n) { SSE_val = sse; nval = n; }
-  void set_early_stop(bool e) { early_stop = e; }
-  bool is_converged() const { return my_is_converged; }
-  bool is_checkpoint() const { return my_is_checkpoint; }
-  bool is_backup() const { return my_is_backup; }
-  int iteration() const { return iteration_counter; }
-  REAL get_error() const { return Errors.back(); }
-  const std::vector<REAL>& parameters() const { return x.back(); }
-  REAL alpha() const { return my_alpha; }          // perturbation amplitude (Optimizer.h:130-137); unused by Potential::train
-  REAL dphi_dt() const { return my_dphi_dt; }
+  void set_val_sse(REAL sse, long long n) { val_sse = sse; val_count = n; }
+  void set_early_stop(bool e) { report_validation = e; }
+  bool is_converged() const { return done; }
+  bool is_checkpoint() const { return want_checkpoint; }
+  bool is_backup() const { return want_backup; }
+  int iteration() const { return epoch; }
+  REAL get_error() const { return *errors.newest(0); }
+  const std::vector<REAL>& parameters() const { return current; }
+  REAL alpha() const { return pt.alpha; }          // perturbation amplitude (Optimizer.h:130-137); unused by Potential::train
+  REAL dphi_dt() const { return pt.dphi; }
   bool do_print;
-  // the algorithms, exposed for tests
-  std::vector<REAL> rprop();
-  std::vector<REAL> steepest_descent();
-  std::vector<REAL> steepest_descent_with_line_opt();   // Optimizer.cpp:457-491
-  std::vector<REAL> LBFGS();                            // Optimizer.cpp:607-696
-  REAL brent_line_min(REAL tolerance);                  // Optimizer.cpp:709-869
 
  private:
-  std::vector<REAL> switch_to_sd();
-  std::vector<REAL> switch_to_rprop();
-  std::vector<REAL> switch_to_BFGS();
-  std::vector<REAL> next_x();
+  enum Method { kRprop = 0, kDescent = 1, kDescentLine = 2, kLbfgs = 3 };
+  // fixed-capacity FIFO of equal-length rows in one flat allocation: the kept part of the trajectory
+  struct Ring {
+    std::vector<REAL> buf;
+    int w, cap, first, n;
+    Ring() : w(0), cap(0), first(0), n(0) {}
+    void reset(int width, int capacity);
+    int size() const { return n; }
+    REAL* append();
+    void drop_oldest();
+    const REAL* oldest(int i) const;
+    const REAL* newest(int age) const;
+    REAL* newest_mut();
+  };
+  struct Pair { std::vector<REAL> s, y; REAL rho; };        // one L-BFGS correction pair
+  struct LineSearch {                                       // state of the line minimisation (see line_search)
+    enum Phase { kFresh, kExpanding, kBracketed } phase;
+    int npts;
+    REAL a[2], s[2];                   // distances along the line and directional slopes of the kept points
+    REAL ok_E, ok_a, ok_s;             // last accepted point while expanding
+    REAL c_a, c_s, d_a;                // previous best point and the one before it (interpolation / safeguards)
+    bool bisected;
+    REAL resolution;
+  };
+  struct Perturbation {                                     // lambda_max != 0 (Optimizer.cpp:915-938, 1008-1043)
+    REAL ceiling, amplitude_now, alpha, dphi, phase, rate, best_E, best_norm, floor_E;
+    bool enabled;
+    int cycles, t_on;
+    std::vector<REAL> best_x;
+  };
+  std::vector<REAL> step_rprop();
+  std::vector<REAL> step_descent();
+  std::vector<REAL> step_descent_line();
+  std::vector<REAL> step_lbfgs();
+  std::vector<REAL> dispatch();
+  std::vector<REAL> enter(Method m);
+  std::vector<REAL> along_line(REAL t) const;
+  void start_line_at_current(const REAL* direction_source);
+  REAL line_search(REAL tolerance);
+  void perturbation_tick(REAL shown_E);
+
   Parallel* mpi;
   FunctionalParams F;
-  enum Algo { RPROP, SD, SD_LINE, BFGS } algo;
-  bool allow_training_switch, early_stop;
-  int my_Nsystems, my_max_steps, my_Ncheckpoint, my_Nbackup, my_Nparameters, iteration_counter;
-  bool my_Tbackup, my_is_converged, my_is_checkpoint, my_is_backup, line_min;
-  REAL my_threshold, debug, lambda0, lambda, alpha1, SSE_val;
-  long long nval;
-  REAL rprop_weights_max, rprop_weights_min;
-  std::deque<std::vector<REAL> > x, gradient;
-  std::deque<REAL> Errors;
-  std::vector<REAL> search_direction, rprop_weights, rprop_step;
-  // perturbation ("global optimizer") scheme, lambda_max != 0 (Optimizer.cpp:915-938, 1008-1043)
-  bool global_optimizer;
-  REAL my_alpha, my_dphi_dt, alpha_max, current_alpha_max, phase_shift, dalpha_dt, E_best, g_best, E_min;
-  int cycles, t0;
-  std::vector<REAL> x_best;
-  // L-BFGS / Brent line minimisation state (Optimizer.h:215-234)
-  int BFGS_Nmax;
-  REAL convergence, line_last_E, line_last_alpha, line_last_g, brent_c, brent_g_c, brent_d;
-  bool brent_flag;
-  std::vector<REAL> BFGS_last_x, BFGS_last_gradient;
-  std::vector<std::vector<REAL> > s, y;
-  std::deque<REAL> rho, line_g, line_alpha;
+  Method method;
+  bool may_switch, report_validation, done, want_checkpoint, want_backup, line_done;
+  int n_structures, n_par, epoch;
+  REAL val_sse;
+  long long val_count;
+  Ring points, slopes, errors;
+  std::vector<REAL> current;
+  // Rprop
+  REAL first_size, size_ceiling, size_floor, restart_size;
+  std::vector<REAL> rp_size, rp_move;
+  std::vector<signed char> rp_live;
+  bool rp_started;
+  // descent / line methods
+  REAL step_len;
+  std::vector<REAL> dir, line_origin, line_origin_slope;
+  bool dir_set;
+  int lbfgs_memory;
+  std::vector<Pair> pairs;
+  LineSearch ls;
+  Perturbation pt;
 };
 
 REAL approximate_KS(const std::vector<REAL>& data1, const std::vector<REAL>& data2, REAL* p_out);   // Analysis.cpp:149-202

@@ -11,6 +11,9 @@
 #include <set>
 #include <sstream>
 
+#include <sys/stat.h>
+#include <ctime>
+
 #include "pph.h"
 
 namespace pph {
@@ -130,6 +133,7 @@ void Parallel::attach(pp_context* c)
   }
   unsigned char id[128];
   if (my_rank == 0) {
+    unlink(path.c_str());      // a file left behind by a run that died must not be taken for this run's
     PPH_CALL(pp_comm_unique_id(id));
     std::string tmp = path + ".tmp";
     std::ofstream f(tmp.c_str(), std::ios::binary);
@@ -138,8 +142,12 @@ void Parallel::attach(pp_context* c)
     rename(tmp.c_str(), path.c_str());
   } else {
     for (int tries = 0;; tries++) {
+      // only a file written recently counts: one older than ten minutes is the leftover of an earlier run that rank 0
+      // has not yet removed
+      struct stat sb;
+      const bool fresh = stat(path.c_str(), &sb) == 0 && difftime(time(NULL), sb.st_mtime) < 600.0;
       std::ifstream f(path.c_str(), std::ios::binary);
-      if (f.is_open() && f.read((char*)id, 128)) break;
+      if (fresh && f.is_open() && f.read((char*)id, 128)) break;
       if (tries > 6000) PPH_ERROR("timed out waiting for the rendezvous file " + path);
       usleep(10000);
     }

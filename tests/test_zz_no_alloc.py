@@ -5,8 +5,10 @@ device-wide synchronisation of cudaMalloc/cudaFree) get the two reductions behin
 with a fixed scratch array inside the library.  Here the entry point is called through the C ABI on descriptors
 held in a caller-owned device buffer, twice in a row (the scratch is shared and keeps the previous call's
 contents, so the second call proves nothing stale leaks through), and its results are compared with what the
-existing allocating entry point pp_precondition installs.  The file name sorts last so that a run stopping at
-the first failure has already executed every other test.
+existing allocating entry point pp_precondition installs (pp_precondition is itself pinned to the reference's
+Potential::Precondition output by tests/test_gpu_parity.py::test_precondition, so agreeing with it is agreeing with
+the reference) and with a plain numpy evaluation of the same sums.  The file name sorts last so that a run stopping
+at the first failure has already executed every other test.
 """
 import ctypes
 
