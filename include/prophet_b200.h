@@ -214,7 +214,9 @@ long long pp_kernel_launches(pp_context* ctx);
 /* device-side time (ms, CUDA events on the context's stream) of the last call's phases:
  * which: 0 = descriptors (pp_add_structures), 1 = epoch forward, 2 = epoch backward, 3 = reduction of the per-CTA
  *        partial gradients + sum over ranks,
- *        4 = md descriptors, 5 = md network, 6 = md forces, 7 = ghost-force exchange (pp_md_exchange_device) */
+ *        4 = md descriptors, 5 = md network, 6 = md forces (with PP_MD_FUSED=1 the step runs as ONE kernel per atom
+ *        shell -- slower than the three kernels on B200, kept as a measured alternative -- and phase 6 is that kernel),
+ *        7 = ghost-force exchange (pp_md_exchange_device) */
 double pp_last_phase_ms(pp_context* ctx, int which);
 void* pp_stream(pp_context* ctx);
 

@@ -83,6 +83,8 @@ struct pp_context {
   NetHost nets[PP_MAX_ELEM];
   int P_total = 0;
   DevBuf<double> d_params;          // all elements, concatenated
+  DevBuf<double> d_paramsT;         // the same with every weight layer transposed ([n_in + 1][n_out]): fused MD kernel
+  bool paramsT_dirty = true;
   double out_mean = 0.0, out_scale = 1.0;
   DevBuf<double> d_tanh_table;
 
@@ -130,6 +132,7 @@ struct pp_context {
   DevBuf<long long> d_cell_start, d_scan_sums, d_scan_total;
   DevBuf<double> d_sum_partial, d_etotal;
   bool md_list_resident = false;
+  bool md_fused_last = false;          // the last MD step ran the single fused kernel (its time is phase 6)
   // reverse communication of ghost forces (pp_md_exchange_*)
   struct SegList { int n_seg = 0; DevBuf<int> seg_off, seg_dst, idx; };
   struct MdPeer { int rank = 0; int n_send = 0, n_recv = 0; DevBuf<int> send_idx; DevBuf<double> sendbuf, recvbuf; SegList add; };
@@ -188,7 +191,7 @@ extern "C" void pp_destroy(pp_context* c)
   cudaStreamSynchronize(c->stream);
   c->comm.destroy();
   // DevBuf members are plain pointers: release explicitly
-  c->d_overflow.release(); c->d_params.release(); c->d_tanh_table.release();
+  c->d_overflow.release(); c->d_params.release(); c->d_paramsT.release(); c->d_tanh_table.release();
   c->d_struct_atom0.release(); c->d_FtoA.release(); c->d_target.release(); c->d_frac.release(); c->d_G.release();
   c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
   c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_err_scratch.release(); c->d_scratch2.release(); c->d_err_ticket.release();
@@ -400,6 +403,7 @@ static int rebuild_param_layout(pp_context* c)
     off += c->nets[e].P;
   }
   c->P_total = off;
+  c->paramsT_dirty = true;
   if (c->d_params.ensure((size_t)std::max(off, 1), 0, c->stream)) return 1;
   for (int e = 0; e < PP_MAX_ELEM; e++) {
     NetHost& n = c->nets[e];
@@ -521,6 +525,7 @@ extern "C" int pp_set_parameters(pp_context* c, const double* params)
 {
   if (nets_ready(c)) return 1;
   PP_CUDA(cudaSetDevice(c->device));
+  c->paramsT_dirty = true;
   for (int e = 0; e < c->spec.n_elem; e++) {
     NetHost& n = c->nets[e];
     std::copy(params + n.p_off, params + n.p_off + n.P, n.params.begin());
@@ -1132,6 +1137,7 @@ extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out
     c->h_result_cap = need;
   }
   if (params_in) {
+    c->paramsT_dirty = true;
     double* stage = c->h_result + c->P_total + 3;
     for (int e = 0; e < c->spec.n_elem; e++) {
       NetHost& n = c->nets[e];
@@ -1228,10 +1234,76 @@ static int md_upload_atoms(pp_context* c, const double* x, const int* type, int 
   return 0;
 }
 
-static int md_run(pp_context* c, const double* x_dev, double* f_dev)
+// transposed copy of every weight layer for the fused MD kernel's forward products (host transposition: P <= ~50k)
+static int md_refresh_transposed(pp_context* c)
+{
+  if (!c->paramsT_dirty) return 0;
+  std::vector<double> t((size_t)std::max(c->P_total, 1), 0.0);
+  for (int e = 0; e < c->spec.n_elem; e++) {
+    const NetHost& n = c->nets[e];
+    for (int l = 0; l < n.n_layers; l++) {
+      const int n_in = n.sizes[l], n_out = n.sizes[l + 1];
+      const double* src = n.params.data() + n.dev.w_off[l];
+      double* dst = t.data() + n.p_off + n.dev.w_off[l];
+      for (int r = 0; r < n_out; r++)
+        for (int k = 0; k <= n_in; k++) dst[(size_t)k * n_out + r] = src[(size_t)r * (n_in + 1) + k];
+    }
+  }
+  if (c->d_paramsT.ensure(t.size(), 0, c->stream)) return 1;
+  PP_CUDA(cudaMemcpyAsync(c->d_paramsT.p, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  PP_CUDA(cudaStreamSynchronize(c->stream));      // t is a local
+  c->paramsT_dirty = false;
+  return 0;
+}
+
+// The single-kernel MD step is opt-in (PP_MD_FUSED=1): measured on the 1 M-atom box it is SLOWER than the three kernels
+// (46.0 ms against 34.4 ms; 40.3 ms even with the network left out) although it builds the neighbour shell once -- the
+// shell set-up it saves is only 2.0 + 3.7 ms of the 12.0 + 21.3 ms the two pair-loop kernels take, and the combined
+// kernel pays for it with spills at the 128-register cap and a code footprint that no longer fits the instruction cache
+// with four warps per scheduler at different places in it; the per-atom network costs 5.7 ms in-warp against 1.06 ms
+// as a DMMA kernel over all atoms.  Kept because it is exact (tests) and documents the measurement.
+static bool md_fused(pp_context* c)
+{
+  if (getenv("PP_MD_FUSED") == nullptr) return false;
+  for (int e = 0; e < c->spec.n_elem; e++)
+    if (!ppk_md_fused_ok(c->nets[e].dev)) return false;
+  return true;
+}
+
+static int md_run(pp_context* c, const double* x_dev, double* f_dev, bool want_G = false, bool want_dEdG = false)
 {
   cudaStream_t st = c->stream;
   const int nlocal = c->md_nlocal;
+  if (md_fused(c)) {
+    // one launch: descriptors, the atom's network and the force chain rule per warp; G and dE/dG stay on the SM
+    if (md_refresh_transposed(c)) return 1;
+    MdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.spec = c->d_spec;
+    a.nlocal = nlocal;
+    a.x = x_dev;
+    a.elem = c->d_md_elem.p;
+    a.neigh_offsets = c->d_neigh_off.p;
+    a.neigh = c->d_neigh.p;
+    a.f = f_dev;
+    a.overflow = c->d_overflow.p;
+    MdNets nets;
+    memset(&nets, 0, sizeof(nets));
+    for (int e = 0; e < c->spec.n_elem; e++) { nets.net[e] = c->nets[e].dev; nets.WT[e] = c->d_paramsT.p + c->nets[e].p_off; }
+    nets.out_scale = c->out_scale;
+    nets.tanh_table = c->d_tanh_table.p;
+    nets.eatom = c->d_eatom.p;
+    nets.G_store = want_G ? c->d_Gmd.p : nullptr;
+    nets.dEdG_store = want_dEdG ? c->d_dEdG.p : nullptr;
+    if (tick(c, 0)) return 1;
+    if (tick(c, 1)) return 1;
+    if (tick(c, 2)) return 1;
+    if (ppk_md_fused(c->spec, a, nets, &c->md_cap, st, &c->launches)) return 1;
+    if (tick(c, 3)) return 1;
+    c->md_fused_last = true;
+    return 0;
+  }
+  c->md_fused_last = false;
   MdArgs a;
   memset(&a, 0, sizeof(a));
   a.spec = c->d_spec;
@@ -1287,7 +1359,7 @@ extern "C" int pp_md_compute(pp_context* c, const double* x, const int* type, in
   c->md_nneigh = nn;
   PP_CUDA(cudaMemsetAsync(c->d_f.p, 0, 3 * (size_t)ntotal * sizeof(double), st));
   c->md_list_resident = false;
-  if (md_run(c, c->d_x.p, c->d_f.p)) return 1;
+  if (md_run(c, c->d_x.p, c->d_f.p, G_out != nullptr, dEdG_out != nullptr)) return 1;
   std::vector<double> f(3 * (size_t)ntotal), ea(std::max(nlocal, 1));
   PP_CUDA(cudaMemcpyAsync(f.data(), c->d_f.p, f.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
   PP_CUDA(cudaMemcpyAsync(ea.data(), c->d_eatom.p, nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));

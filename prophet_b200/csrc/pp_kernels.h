@@ -56,6 +56,21 @@ struct NetDev {
 
 enum { PP_MLP_FORWARD = 0, PP_MLP_TRAIN = 1, PP_MLP_INPUT_GRAD = 2, PP_MLP_FUSED = 3 };
 
+// fused MD step (md_fused_kernel): the per-element networks of the atom-centred pass
+struct MdNets {
+  NetDev net[PP_MAX_ELEM];
+  const double* WT[PP_MAX_ELEM];   // per element: every weight layer transposed, [n_in + 1][n_out] at the layer's w_off
+  double out_scale;
+  const double* tanh_table;
+  double* eatom;                   // [nlocal] out
+  double* dEdG_store;              // [nlocal][NG] out, or nullptr (parity hook)
+  double* G_store;                 // [nlocal][NG] out, or nullptr (parity hook)
+  int cap_lo;                      // only atoms with cap_lo < neighbours <= cap are processed (re-run after an overflow)
+};
+bool ppk_md_fused_ok(const NetDev& net);
+int ppk_md_fused(const DescSpec& hs, MdArgs a, const MdNets& nets, int* cap_io, cudaStream_t st, long long* launches);
+
+
 struct MlpArgs {
   NetDev net;
   const double* G;                    // [atoms][NG]

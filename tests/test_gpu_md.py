@@ -89,3 +89,31 @@ def test_step_device_pointers():
         assert abs(float(ed.cpu()[0]) - ref["etotal"]) < 1e-10 * abs(ref["etotal"])
     finally:
         ctx.close()
+
+
+def test_single_kernel_md_step_matches_the_three_kernel_step(monkeypatch):
+    """PP_MD_FUSED=1: descriptors, the atom's network and the force chain rule in one kernel per atom shell (measured
+    slower on B200 and therefore opt-in; it must stay exact).  Two elements and the all-variants case (every transfer
+    function, G1 / G3 rows), parity hooks included."""
+    for name in ("tio2_md", "variants_md"):
+        c = MDCase(name)
+        res = {}
+        for fused in (False, True):
+            if fused:
+                monkeypatch.setenv("PP_MD_FUSED", "1")
+            else:
+                monkeypatch.delenv("PP_MD_FUSED", raising=False)
+            ctx = capi.Context(0)
+            try:
+                ctx.set_descriptors(len(c.elements), c.G1, c.G2, c.G3, c.G4, c.rcut)
+                for e, z in enumerate(c.elements):
+                    ctx.set_network(e, c.sizes, c.d["params.%d" % z], c.d["in_mean.%d" % z], c.d["in_scale.%d" % z],
+                                    node_transfer=c.node_transfer(z))
+                ctx.set_output_scaling(c.out_mean, c.out_scale)
+                ctx.md_set_types([0] + list(range(len(c.elements))))
+                res[fused] = ctx.md_compute(c.x, c.types, c.nlocal, c.offsets, c.neigh, want_G=True, want_dEdG=True)
+            finally:
+                ctx.close()
+        for k in ("f", "G", "dEdG", "eatom"):
+            assert rel_err(res[True][k], res[False][k]) < 1e-11, (name, k)
+        assert rel_err(res[True]["f"], c.d["f"]) < 1e-10
