@@ -35,15 +35,25 @@ def main():
         for key, label in WANT:
             if key in idx:
                 print("   %-26s %s %s" % (label, r[idx[key]], units[idx[key]]))
+        # warp-state samples (smsp__pcsamp_warps_issue_stalled_<reason>): share of all samples per reason
         stalls = []
         for h, i in idx.items():
-            if "issue_stalled" in h and h.endswith("_per_warp_active.pct"):
+            if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued"):
                 try:
-                    stalls.append((float(r[i].replace(",", "")), h.split("issue_stalled_")[1].replace("_per_warp_active.pct", "")))
+                    stalls.append((float(r[i].replace(",", "")), h[len("smsp__pcsamp_warps_issue_stalled_"):]))
                 except ValueError:
                     pass
+        tot = sum(v for v, _ in stalls) or 1.0
         stalls.sort(reverse=True)
-        print("   top stalls: " + ", ".join("%s %.0f%%" % (n, v) for v, n in stalls[:6]))
+        print("   top stalls: " + ", ".join("%s %.0f%%" % (n, 100 * v / tot) for v, n in stalls[:7]))
+        ops = []
+        for key, label in (("smsp__sass_thread_inst_executed_op_dfma_pred_on.sum", "dfma"), ("smsp__sass_thread_inst_executed_op_dmul_pred_on.sum", "dmul"),
+                           ("smsp__sass_thread_inst_executed_op_dadd_pred_on.sum", "dadd"), ("sm__sass_thread_inst_executed_op_dfma_pred_on.sum", "dfma"),
+                           ("sm__sass_thread_inst_executed_op_dmul_pred_on.sum", "dmul"), ("sm__sass_thread_inst_executed_op_dadd_pred_on.sum", "dadd")):
+            if key in idx and r[idx[key]]:
+                ops.append("%s %s" % (label, r[idx[key]]))
+        if ops:
+            print("   fp64 thread instructions: " + ", ".join(ops))
 
 
 if __name__ == "__main__":
