@@ -365,6 +365,43 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
       }
     }
   }
+  // evaluation order of the Gaussian factors (DescSpec::pair_order / rad_order): group by Rs, ascending eta, and chain an
+  // eta that is an integer multiple (<= 64) of its predecessor's; at most a 4096-th power of a computed exponential in all
+  {
+    auto chain_of = [](double eta, double eta_prev, long long& cum) {
+      if (!(eta_prev > 0.0) || !(eta > 0.0)) return 0;
+      const double m = nearbyint(eta / eta_prev);
+      if (m < 1.0 || m > 64.0 || fabs(eta - m * eta_prev) > 4e-16 * eta) return 0;
+      if (cum * (long long)m > 4096) return 0;
+      cum *= (long long)m;
+      return (int)m;
+    };
+    std::vector<int> ord;
+    for (int r = nG1; r < S.npair; r++) ord.push_back(r);
+    std::stable_sort(ord.begin(), ord.end(), [&](int x, int y) {
+      if (S.pair_rs[x] != S.pair_rs[y]) return S.pair_rs[x] < S.pair_rs[y];
+      return S.pair_eta[x] < S.pair_eta[y];
+    });
+    for (int r = 0; r < nG1; r++) { S.pair_order[r] = r; S.pair_chain[r] = 0; }
+    long long cum = 1;
+    for (size_t k = 0; k < ord.size(); k++) {
+      const int r = ord[k];
+      int m = 0;
+      if (k > 0 && S.pair_rs[ord[k - 1]] == S.pair_rs[r]) m = chain_of(S.pair_eta[r], S.pair_eta[ord[k - 1]], cum);
+      if (m == 0) cum = 1;
+      S.pair_order[nG1 + k] = r; S.pair_chain[nG1 + k] = m;
+    }
+    ord.clear();
+    for (int r = 0; r < S.NR; r++) ord.push_back(r);
+    std::stable_sort(ord.begin(), ord.end(), [&](int x, int y) { return S.rad_eta[x] < S.rad_eta[y]; });
+    cum = 1;
+    for (size_t k = 0; k < ord.size(); k++) {
+      int m = 0;
+      if (k > 0) m = chain_of(S.rad_eta[ord[k]], S.rad_eta[ord[k - 1]], cum);
+      if (m == 0) cum = 1;
+      S.rad_order[k] = ord[k]; S.rad_chain[k] = m;
+    }
+  }
   // squared-distance thresholds equivalent to the reference's tests on d = sqrt(d2) (Structure.cpp:1337)
   {
     auto thr = [](double r) {

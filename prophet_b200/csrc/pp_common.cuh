@@ -64,6 +64,13 @@ struct DescSpec {
   int basis_used[2];              // per lambda group: bit k set when some row uses power level k
   double basis_lam[2];
   int g4_bg[PP_MAX_G4_ROWS], g4_bb[PP_MAX_G4_ROWS];
+  // Evaluation order of the Gaussian factors exp(-eta (R - Rs)^2) of the pair rows and exp(-eta R^2) of the radial keys:
+  // entries sharing Rs sorted by eta, so that an eta which is an integer multiple m of its predecessor's costs the m-th
+  // power of the predecessor's exponential (two multiplies for the usual ratio-4 ladders) instead of another exp.
+  // chain[k] = 0: fresh exp; m >= 1: (exponential of order[k-1])^m.  The accumulated power is capped (pp_set_descriptors),
+  // which keeps the relative error below 1e-12.
+  int pair_order[PP_MAX_PAIR_ROWS], pair_chain[PP_MAX_PAIR_ROWS];
+  int rad_order[PP_MAX_RAD], rad_chain[PP_MAX_RAD];
   // slot of the first triplet row for element pair (e1,e2): Structure::init_type_G_map (Structure.cpp:1500-1510)
   int trip_base[PP_MAX_ELEM][PP_MAX_ELEM];
 };

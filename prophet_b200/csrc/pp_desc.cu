@@ -17,6 +17,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
 desc_periodic_kernel(PeriodicArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
+  const double* etab = pp_block_exp_table();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long rel = (long long)blockIdx.x * DESC_WARPS + warp;
   if (rel >= a.n_atoms) return;
@@ -25,6 +26,7 @@ desc_periodic_kernel(PeriodicArgs a)
   const size_t per_warp = pp_warp_smem_bytes(a.cap, S->NR, S->NG, false);
   WarpNbr w;
   pp_warp_views(w, smem + per_warp * warp, a.cap, S->NR, S->NG, false);
+  w.etab = etab;
   const int s = a.atom_struct[atom];
   const long long a0 = a.struct_atom0[s];
   const int natom = (int)(a.struct_atom0[s + 1] - a0);
@@ -86,6 +88,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
 md_desc_kernel(MdArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
+  const double* etab = pp_block_exp_table();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int i = blockIdx.x * DESC_WARPS + warp;
   if (i >= a.nlocal) return;
@@ -93,6 +96,7 @@ md_desc_kernel(MdArgs a)
   const size_t per_warp = pp_warp_smem_bytes(a.cap, S->NR, S->NG, false);
   WarpNbr w;
   pp_warp_views(w, smem + per_warp * warp, a.cap, S->NR, S->NG, false);
+  w.etab = etab;
   const long long p0 = a.neigh_offsets[i];
   const int nlist = (int)(a.neigh_offsets[i + 1] - p0);
   int n = pp_gather_list(w, a.cap, lane, a.x, a.elem, i, a.neigh + p0, nlist, S->Rcut);
@@ -114,6 +118,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_BLOCKS_PER_SM)
 md_force_kernel(MdArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
+  const double* etab = pp_block_exp_table();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int i = blockIdx.x * DESC_WARPS + warp;
   if (i >= a.nlocal) return;
@@ -121,6 +126,7 @@ md_force_kernel(MdArgs a)
   const size_t per_warp = pp_warp_smem_bytes(a.cap, S->NR, S->NG, true);
   WarpNbr w;
   pp_warp_views(w, smem + per_warp * warp, a.cap, S->NR, S->NG, true);
+  w.etab = etab;
   const long long p0 = a.neigh_offsets[i];
   const int nlist = (int)(a.neigh_offsets[i + 1] - p0);
   int n = pp_gather_list(w, a.cap, lane, a.x, a.elem, i, a.neigh + p0, nlist, S->Rcut);
@@ -280,6 +286,7 @@ md_fused_kernel(MdArgs a, MdNets nets)
   const size_t per_warp = pp_warp_smem_bytes(a.cap, S->NR, S->NG, true);
   WarpNbr w;
   pp_warp_views(w, smem + per_warp * warp, a.cap, S->NR, S->NG, true);
+  w.etab = exptab;
   const long long p0 = a.neigh_offsets[i];
   const int nlist = (int)(a.neigh_offsets[i + 1] - p0);
   int n = pp_gather_list(w, a.cap, lane, a.x, a.elem, i, a.neigh + p0, nlist, S->Rcut);

@@ -17,6 +17,7 @@
 //     element-pair block.
 #pragma once
 #include "pp_common.cuh"
+#include "pp_fastmath.cuh"
 
 // ---------------------------------------------------------------------------------------------------------
 // per-warp shared-memory views
@@ -31,6 +32,7 @@ struct WarpNbr {
   double *buf;                // [max(NG, ...)] G row (desc) or dE/dG row (force)
   double *cell;               // [PP_MAX_RAD*PP_MAX_ANG] reduced grid cells
   int n;                      // entries
+  const double* etab;         // 2^(j/64), j = 0..63 (per block, shared memory): table of pp_fast_exp_nonpos
   int* start;                 // [PP_MAX_ELEM + 1] element block boundaries after the sort.  Kept in shared memory:
                               // a run-time indexed array member would push the whole struct (and with it every
                               // pointer above) into local memory and turn all shared loads into generic ones.
@@ -66,6 +68,16 @@ __device__ inline void pp_warp_views(WarpNbr& w, unsigned char* base, int cap, i
   w.elem = q; q += cap; w.selem = q; q += cap; w.idx = q; q += cap; w.sidx = q; q += cap;
   w.start = q; q += 8;
   w.n = 0;
+  w.etab = nullptr;
+}
+
+// the block's table for pp_gauss_exp: call at the top of a kernel, before any thread leaves
+__device__ __forceinline__ const double* pp_block_exp_table()
+{
+  __shared__ double etab[64];
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) etab[i] = exp2((double)i * 0.015625);
+  __syncthreads();
+  return etab;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -134,31 +146,81 @@ __device__ inline int pp_gather_list(WarpNbr& w, int cap, int lane, const double
 {
   const double ix = x[3 * (size_t)i], iy = x[3 * (size_t)i + 1], iz = x[3 * (size_t)i + 2];
   int count = 0;
-  for (int p0 = 0; p0 < nlist; p0 += 32) {
-    int p = p0 + lane;
-    bool keep = false;
-    double dx = 0, dy = 0, dz = 0, d = 0;
-    int j = 0;
-    if (p < nlist) {
-      j = list[p];
-      dx = __dsub_rn(x[3 * (size_t)j], ix);
-      dy = __dsub_rn(x[3 * (size_t)j + 1], iy);
-      dz = __dsub_rn(x[3 * (size_t)j + 2], iz);
-      d = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
-      keep = (j != i) && !(d > Rcut);
+  // four chunks of 32 list entries in flight: all indices first, then all positions, then the tests in list order (the
+  // dependent global loads of one chunk at a time left the warp waiting on memory three times per atom)
+  constexpr int U = 4;
+  for (int p0 = 0; p0 < nlist; p0 += 32 * U) {
+    int j[U], el[U];
+    double dx[U], dy[U], dz[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int p = p0 + 32 * u + lane;
+      j[u] = (p < nlist) ? list[p] : -1;
     }
-    unsigned m = __ballot_sync(0xffffffffu, keep);
-    if (keep) {
-      int pos = count + __popc(m & ((1u << lane) - 1u));
-      if (pos < cap) {
-        w.sx[pos] = dx; w.sy[pos] = dy; w.sz[pos] = dz; w.sR[pos] = d;
-        w.selem[pos] = elem_of_atom[j];
-        w.sidx[pos] = j;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const bool ok = j[u] >= 0;
+      const size_t jj = ok ? (size_t)j[u] : (size_t)i;
+      dx[u] = x[3 * jj]; dy[u] = x[3 * jj + 1]; dz[u] = x[3 * jj + 2];
+      el[u] = elem_of_atom[jj];
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (p0 + 32 * u < nlist) {        // warp-uniform
+        const double ddx = __dsub_rn(dx[u], ix), ddy = __dsub_rn(dy[u], iy), ddz = __dsub_rn(dz[u], iz);
+        const double d = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz)));
+        const bool keep = (j[u] >= 0) && (j[u] != i) && !(d > Rcut);
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+          const int pos = count + __popc(m & ((1u << lane) - 1u));
+          if (pos < cap) {
+            w.sx[pos] = ddx; w.sy[pos] = ddy; w.sz[pos] = ddz; w.sR[pos] = d;
+            w.selem[pos] = el[u];
+            w.sidx[pos] = j[u];
+          }
+        }
+        count += __popc(m);
       }
     }
-    count += __popc(m);
   }
   return count;
+}
+
+// exp(x) of the Gaussian factors: x = -eta d^2 <= 0 for every sensible row; the table form costs about a third of exp()
+__device__ __forceinline__ double pp_gauss_exp(double x, const double* __restrict__ etab)
+{
+#ifdef PP_DESC_LIBM_EXP
+  return exp(x);
+#else
+  if (x > 0.0) return exp(x);        // negative eta: uniform over the warp, never taken by a physical row set
+  return pp_fast_exp_nonpos(x, etab);
+#endif
+}
+
+// x^e for a small non-negative integer e (square and multiply; e is warp-uniform wherever this is used)
+__device__ __forceinline__ double pp_ipow(double x, int e)
+{
+  double r = (e & 1) ? x : 1.0;
+  e >>= 1;
+  while (e) {
+    x *= x;
+    if (e & 1) r *= x;
+    e >>= 1;
+  }
+  return r;
+}
+
+// the same for two values (one walk over the exponent's bits)
+__device__ __forceinline__ void pp_ipow2(double& x0, double& x1, int e)
+{
+  double r0 = (e & 1) ? x0 : 1.0, r1 = (e & 1) ? x1 : 1.0;
+  e >>= 1;
+  while (e) {
+    x0 *= x0; x1 *= x1;
+    if (e & 1) { r0 *= x0; r1 *= x1; }
+    e >>= 1;
+  }
+  x0 = r0; x1 = r1;
 }
 
 // Stable counting sort of the staged entries by element, then unit vectors and radial factors.
@@ -193,25 +255,39 @@ __device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const 
   if (lane == 0)
     for (int e = n_elem; e <= PP_MAX_ELEM; e++) w.start[e] = base;
   __syncwarp();
-  // radial factors of the G4 grid: A_r = exp(-eta_r R^2) fc_r(R)  (0 beyond the row's own Rc: fc returns 0)
+  // radial factors of the G4 grid: A_r = exp(-eta_r R^2) fc_r(R)  (0 beyond the row's own Rc: fc returns 0).
+  // Two entries per lane at a time (p and p + 32): their exponentials are independent chains of dependent FP64 operations,
+  // and a shell of 33..64 neighbours would otherwise walk the keys twice, the second time with half the lanes idle.
   const int NR = S->NR;
-  for (int p = lane; p < n; p += 32) {
-    double R = w.R[p];
-    double key_rc = -1.0, f = 0.0, df = 0.0;      // cutoff factor and slope: once per (Rc, fc type), usually one key
+  for (int p0 = lane; p0 < n; p0 += 64) {
+    const int p1 = p0 + 32;
+    const bool two = p1 < n;
+    const double R0 = w.R[p0], R1 = two ? w.R[p1] : 1.0;
+    double key_rc = -1.0, f0 = 0.0, df0 = 0.0, f1 = 0.0, df1 = 0.0;      // cutoff factor and slope: once per (Rc, fc type), usually one key
     int key_fs = -1;
-    for (int r = 0; r < NR; r++) {
-      double rc = S->rad_rc[r], eta = S->rad_eta[r];
-      int fs = S->rad_fc[r];
-      double ex = exp(-eta * (R * R));
+    double ex0 = 1.0, ex1 = 1.0;
+    for (int k = 0; k < NR; k++) {
+      const int r = S->rad_order[k], pw = S->rad_chain[k];      // ascending eta; pw: integer power of the previous exponential
+      const double rc = S->rad_rc[r], eta = S->rad_eta[r];
+      const int fs = S->rad_fc[r];
+      if (pw) pp_ipow2(ex0, ex1, pw);
+      else { ex0 = pp_gauss_exp(-eta * (R0 * R0), w.etab); ex1 = pp_gauss_exp(-eta * (R1 * R1), w.etab); }
       if (rc != key_rc || fs != key_fs) {
         key_rc = rc; key_fs = fs;
-        f = pp_fc(R / rc, fs);
-        if (FORCE) df = pp_dfc(rc, R, fs);
+        f0 = pp_fc(R0 / rc, fs); f1 = pp_fc(R1 / rc, fs);
+        if (FORCE) { df0 = pp_dfc(rc, R0, fs); df1 = pp_dfc(rc, R1, fs); }
       }
-      w.A[(size_t)r * cap + p] = ex * f;
-      if (FORCE) w.dA[(size_t)r * cap + p] = ex * (df - 2.0 * R * eta * f);
+      w.A[(size_t)r * cap + p0] = ex0 * f0;
+      if (FORCE) w.dA[(size_t)r * cap + p0] = ex0 * (df0 - 2.0 * R0 * eta * f0);
+      if (two) {
+        w.A[(size_t)r * cap + p1] = ex1 * f1;
+        if (FORCE) w.dA[(size_t)r * cap + p1] = ex1 * (df1 - 2.0 * R1 * eta * f1);
+      }
     }
-    if (FORCE) { w.fx[p] = 0.0; w.fy[p] = 0.0; w.fz[p] = 0.0; w.sR[p] = 1.0 / R; }   // staging is free now: keep 1/R there
+    if (FORCE) {      // staging is free now: keep 1/R there
+      w.fx[p0] = 0.0; w.fy[p0] = 0.0; w.fz[p0] = 0.0; w.sR[p0] = 1.0 / R0;
+      if (two) { w.fx[p1] = 0.0; w.fy[p1] = 0.0; w.fz[p1] = 0.0; w.sR[p1] = 1.0 / R1; }
+    }
   }
   __syncwarp();
 }
@@ -220,18 +296,6 @@ __device__ inline void pp_finalize_entries(WarpNbr& w, int cap, int lane, const 
 // (1 + lam c)^xi for the angular keys [a0, a0+NA_T) of the grid (Structure.h:251-296).  Raw power, without
 // the 2^(1-xi) prefactor.  Integer xi: square-and-multiply with a warp-uniform exponent (no divergence);
 // non-integer xi: the reference's binomial series with its 1e-8 stopping rule and pow() fallback.
-__device__ __forceinline__ double pp_ipow(double x, int e)
-{
-  double r = (e & 1) ? x : 1.0;
-  e >>= 1;
-  while (e) {
-    x *= x;
-    if (e & 1) r *= x;
-    e >>= 1;
-  }
-  return r;
-}
-
 __device__ inline double pp_series_pow(double th, double xi)
 {
   // th = lam*c > -1
@@ -323,28 +387,43 @@ __device__ __forceinline__ void pp_angular(const AngKeys<NA_T>& K, double c, dou
 
 // ---------------------------------------------------------------------------------------------------------
 // G1/G2 rows of one central atom (Structure.cpp:1005-1014 / 1097-1106), accumulated into w.buf[slot].
+// Rows in the order of DescSpec::pair_order, one at a time, two entries per lane together (independent chains).  The
+// Gaussian of a row whose eta is an integer multiple of its predecessor's is a power of the predecessor's, kept per
+// neighbour in the staging array sy (each lane reads back its own entries).  Tried and dropped: eight rows per sweep with
+// eight partial sums reduced together (the unrolled sweep ran 20 % slower than this form).
 __device__ inline void pp_pair_rows_desc(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S)
 {
-  const int npair = S->npair;
+  const int npair = S->npair, nG1 = S->nG1;
   for (int e = 0; e < S->n_elem; e++) {
     const int s = w.start[e], m = w.start[e + 1] - s;
-    // the cutoff factor depends on (Rc, fc type) only, usually shared by all rows: evaluated when that key changes and
-    // kept in the staging array (free after pp_finalize_entries; each lane reads back only what it wrote)
     double key_rc = -1.0;
     int key_fs = -1;
-    for (int r = 0; r < npair; r++) {
-      double rc = S->pair_rc[r], eta = S->pair_eta[r], rs = S->pair_rs[r];
-      int fs = S->pair_fc[r];
-      bool g1 = r < S->nG1;
+    for (int k = 0; k < npair; k++) {
+      const int r = S->pair_order[k], pw = S->pair_chain[k];
+      const double rc = S->pair_rc[r], eta = S->pair_eta[r], rs = S->pair_rs[r];
+      const int fs = S->pair_fc[r];
+      const bool g1 = r < nG1;
       if (rc != key_rc || fs != key_fs) {
         key_rc = rc; key_fs = fs;
         for (int a = lane; a < m; a += 32) w.sx[s + a] = pp_fc(w.R[s + a] / rc, fs);
       }
       double acc = 0.0;
-      for (int a = lane; a < m; a += 32) {
-        double f = w.sx[s + a];
-        if (!g1) { double d = w.R[s + a] - rs; f *= exp(-eta * (d * d)); }
-        acc += f;
+      for (int a0 = lane; a0 < m; a0 += 64) {
+        const int a1 = a0 + 32;
+        const bool two = a1 < m;
+        double t0 = w.sx[s + a0], t1 = two ? w.sx[s + a1] : 0.0;
+        if (!g1) {
+          double ex0, ex1;
+          if (pw) { ex0 = w.sy[s + a0]; ex1 = two ? w.sy[s + a1] : 1.0; pp_ipow2(ex0, ex1, pw); }
+          else {
+            const double d0 = w.R[s + a0] - rs, d1 = (two ? w.R[s + a1] : 0.0) - rs;
+            ex0 = pp_gauss_exp(-eta * (d0 * d0), w.etab); ex1 = pp_gauss_exp(-eta * (d1 * d1), w.etab);
+          }
+          w.sy[s + a0] = ex0;
+          if (two) w.sy[s + a1] = ex1;
+          t0 *= ex0; t1 *= ex1;
+        }
+        acc += t0 + t1;
       }
       acc = pp_warp_sum(acc);
       if (lane == 0) w.buf[npair * e + r] = acc;
@@ -352,7 +431,6 @@ __device__ inline void pp_pair_rows_desc(WarpNbr& w, int cap, int lane, const De
   }
   __syncwarp();
 }
-
 // G4 rows for the element-pair block (e1 <= e2), grid chunk [r0,r0+NR_T) x [a0,a0+NA_T).
 // skip_rjk: the non-periodic branch skips the pair when G3 rows exist and Rjk > Rcut (Structure.cpp:1129-1132).
 template <int NR_T, int NA_T>
@@ -831,11 +909,14 @@ __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const De
 {
   for (int g = lane; g < S->NG; g += 32) w.buf[g] = 0.0;
   __syncwarp();
+#ifndef PP_SKIP_PAIR_ROWS      // timing experiments only
   if (S->npair) pp_pair_rows_desc(w, cap, lane, S);
+#endif
   if (S->nG3) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++) pp_g3_block_desc(w, cap, lane, S, e1, e2, skip_rjk);
   }
+#ifndef PP_SKIP_G4
   if (S->nG4) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++)
@@ -845,6 +926,7 @@ __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const De
             for (int a0 = 0; a0 < S->NA; a0 += NX) pp_g4_block_desc<NR_T, NX>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
         }
   }
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -852,32 +934,43 @@ __device__ inline void pp_descriptor_row(WarpNbr& w, int cap, int lane, const De
 // is (dE/dR) * u; accumulated into the lane's own entries fx/fy/fz.
 __device__ inline void pp_pair_rows_force(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S)
 {
-  const int npair = S->npair;
-  for (int p = lane; p < w.n; p += 32) {
-    double R = w.R[p];
-    int e = w.elem[p];
-    double dEdR = 0.0;
+  // two entries per lane at a time (p and p + 32): independent chains, and one walk over the rows for a shell of 33..64
+  const int npair = S->npair, nG1 = S->nG1;
+  for (int p0 = lane; p0 < w.n; p0 += 64) {
+    const int p1 = p0 + 32;
+    const bool two = p1 < w.n;
+    const double R0 = w.R[p0], R1 = two ? w.R[p1] : 1.0;
+    const double* wt0 = w.buf + npair * w.elem[p0];
+    const double* wt1 = w.buf + npair * (two ? w.elem[p1] : 0);
+    double dE0 = 0.0, dE1 = 0.0;
     // cutoff factor and slope depend on (Rc, fc type) only, usually shared by all rows: evaluated when that key changes
-    double key_rc = -1.0, f = 0.0, df = 0.0;
+    double key_rc = -1.0, f0 = 0.0, df0 = 0.0, f1 = 0.0, df1 = 0.0;
     int key_fs = -1;
-    for (int r = 0; r < npair; r++) {
-      double rc = S->pair_rc[r];
-      int fs = S->pair_fc[r];
+    double ex0 = 1.0, ex1 = 1.0;
+    for (int k = 0; k < npair; k++) {
+      const int r = S->pair_order[k], pw = S->pair_chain[k];      // see pp_pair_rows_desc
+      const double rc = S->pair_rc[r], eta = S->pair_eta[r], rs = S->pair_rs[r];
+      const int fs = S->pair_fc[r];
       if (rc != key_rc || fs != key_fs) {
         key_rc = rc; key_fs = fs;
-        f = pp_fc(R / rc, fs);
-        df = pp_dfc(rc, R, fs);
+        f0 = pp_fc(R0 / rc, fs); df0 = pp_dfc(rc, R0, fs);
+        f1 = pp_fc(R1 / rc, fs); df1 = pp_dfc(rc, R1, fs);
       }
-      if (R >= rc) continue;
-      double wt = w.buf[npair * e + r];
-      if (r < S->nG1) {
-        dEdR += wt * df;
+      const double w0 = wt0[r], w1 = wt1[r];
+      if (r < nG1) {
+        if (R0 < rc) dE0 += w0 * df0;
+        if (R1 < rc) dE1 += w1 * df1;
       } else {
-        double eta = S->pair_eta[r], d = R - S->pair_rs[r];
-        dEdR += wt * exp(-eta * d * d) * (df - 2.0 * eta * d * f);
+        const double d0 = R0 - rs, d1 = R1 - rs;
+        // also for an entry out of the row's range: a successor in the chain may build on the value
+        if (pw) pp_ipow2(ex0, ex1, pw);
+        else { ex0 = pp_gauss_exp(-eta * d0 * d0, w.etab); ex1 = pp_gauss_exp(-eta * d1 * d1, w.etab); }
+        if (R0 < rc) dE0 += w0 * ex0 * (df0 - 2.0 * eta * d0 * f0);
+        if (R1 < rc) dE1 += w1 * ex1 * (df1 - 2.0 * eta * d1 * f1);
       }
     }
-    w.fx[p] += dEdR * w.ux[p]; w.fy[p] += dEdR * w.uy[p]; w.fz[p] += dEdR * w.uz[p];
+    w.fx[p0] += dE0 * w.ux[p0]; w.fy[p0] += dE0 * w.uy[p0]; w.fz[p0] += dE0 * w.uz[p0];
+    if (two) { w.fx[p1] += dE1 * w.ux[p1]; w.fy[p1] += dE1 * w.uy[p1]; w.fz[p1] += dE1 * w.uz[p1]; }
   }
   __syncwarp();
 }
@@ -986,11 +1079,14 @@ __device__ inline void pp_g4_block_force(WarpNbr& w, int cap, int lane, const De
 template <int NR_T, int NX, bool BASIS>
 __device__ inline void pp_force_entries(WarpNbr& w, int cap, int lane, const DescSpec* __restrict__ S, bool skip_rjk)
 {
+#ifndef PP_SKIP_PAIR_ROWS
   if (S->npair) pp_pair_rows_force(w, cap, lane, S);
+#endif
   if (S->nG3) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++) pp_g3_block_force(w, cap, lane, S, e1, e2);
   }
+#ifndef PP_SKIP_G4
   if (S->nG4) {
     for (int e1 = 0; e1 < S->n_elem; e1++)
       for (int e2 = e1; e2 < S->n_elem; e2++)
@@ -1000,4 +1096,5 @@ __device__ inline void pp_force_entries(WarpNbr& w, int cap, int lane, const Des
             for (int a0 = 0; a0 < S->NA; a0 += NX) pp_g4_block_force<NR_T, NX>(w, cap, lane, S, e1, e2, r0, a0, skip_rjk);
         }
   }
+#endif
 }

@@ -440,3 +440,44 @@ def test_forty_distinct_g4_keys_the_optimize_search_on_c2_rows():
         assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_gaussian_factors_chained_as_integer_powers_vs_oracle():
+    """pp_set_descriptors orders the Gaussian factors of the G2 rows and of the G4 radial keys by (Rs, eta) and evaluates an
+    eta that is an integer multiple of its predecessor's as a power of the predecessor's exponential (DescSpec::pair_order).
+    Rows chosen to walk every branch: ratios 1 (same eta twice), 3, 4 and 64, a ratio of 65 (too large: fresh exp), a
+    non-integer ratio, chains interrupted by a different Rs, rows given in descending eta, different Rc inside one chain
+    (an entry beyond the smaller Rc must still feed its successor), and a G1 row in front.  Descriptors and forces against
+    the oracle, which calls exp() for every row as the reference does (Structure.h:351-360)."""
+    g1 = [[6.0, 0.0]]
+    g2 = [[6.0, 0.0, 0.9, 1.0], [6.0, 0.0, 0.3, 0.0], [4.5, 0.0, 0.1, 0.0], [6.0, 0.0, 0.3, 1.0], [6.0, 0.0, 0.1, 1.0],
+          [6.0, 0.0, 0.3, 0.0], [6.0, 0.0, 6.4, 0.0], [6.0, 0.0, 6.5 * 6.4, 2.0], [6.0, 0.0, 0.1 * 65.0, 2.0], [6.0, 0.0, 0.1, 2.0],
+          [6.0, 0.0, 0.25, 2.0]]
+    g4 = [[6.0, 0.0, eta, xi, lam] for eta in (0.27, 0.03, 0.09, 0.0301) for (xi, lam) in ((1.0, 1.0), (2.0, -1.0), (4.0, 1.0))]
+    cfg = synth.config_c2(1)
+    cell, cart, Z, _, _ = synth.make_structure(cfg, 931)
+    frac = capi.cart_to_frac(cell, cart)
+    elem = np.zeros(len(Z), dtype=np.int32)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(1, g1, g2, [], g4, cfg.rcut)
+        ctx.add_structures([len(Z)], cell[None], frac, elem, [0.0], [0])
+        G = ctx.get_descriptors(0)
+        Gref = oracle.descriptors_periodic(cell, frac, elem, 1, g1, g2, [], g4, cfg.rcut)
+        assert rel_err(G, Gref) < TOL, rel_err(G, Gref)
+        NG = len(g1) + len(g2) + len(g4)
+        x, Zall, nlocal = synth.expand_ghosts(cell, cart, Z, cfg.rcut + 1.0)
+        numneigh, offsets, flat = synth.brute_full_neighbor_list(x, nlocal, cfg.rcut + 1.0)
+        rng = np.random.RandomState(5)
+        sizes = [NG, 12, 1]
+        params = 0.3 * rng.randn(NG * 12 + 12 + 12 + 1)
+        ctx.set_network(0, sizes, params, 0.1 * synth.normal(14, NG, 3), 0.5 + np.abs(synth.normal(14, NG, 4)))
+        ctx.md_set_types([0, 0])
+        r = ctx.md_compute(x, np.ones(len(x), dtype=np.int32), nlocal, offsets, flat, want_G=True, want_dEdG=True)
+        Gmd = oracle.descriptors_md(x, np.zeros(len(x), dtype=np.int32), nlocal, offsets, flat, 1, g1, g2, [], g4, cfg.rcut)
+        assert rel_err(r["G"], Gmd) < TOL, rel_err(r["G"], Gmd)
+        fo = oracle.forces_md(x, np.zeros(len(x), dtype=np.int32), nlocal, offsets, flat, 1, g1, g2, [], g4, cfg.rcut, r["dEdG"])
+        assert rel_err(r["f"], fo) < TOL, rel_err(r["f"], fo)
+    finally:
+        ctx.close()
