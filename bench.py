@@ -149,6 +149,8 @@ FORM_NAMES = {
     3: "mlpw_forward_kernel + mlpw_backward_kernel (FP64 DMMA, activations kept in HBM between the phases, weights streamed "
        "into registers), one pair per element",
     0: "mlp_fused2_kernel<FORWARD> + <TRAIN> (FP64 DMMA, forward recomputed in the backward launch), one pair per element",
+    5: "mlp_fused2_kernel<FORWARD> + <TRAIN> (FP64 DMMA, two CTAs per SM; activations and their derivatives kept in HBM between the "
+       "two launches), one pair per element",
 }
 
 
@@ -187,6 +189,11 @@ def train_bench(torch, dist, capi, synth, name, ids, rank, world, local_rank, st
     if sampler is not None:
         sampler.start()
     ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        # the ranks leave the host barrier up to hundreds of microseconds apart; one more untimed epoch (whose sum over
+        # the ranks is a device-side rendezvous) lines the GPUs' timelines up, so that the K timed epochs that follow do
+        # not include the first rank's wait for the last one to start
+        ctx.epoch_device()
     launches_before = ctx.kernel_launches
     ev0.record(stream)
     for _ in range(steps):
@@ -210,6 +217,8 @@ def train_bench(torch, dist, capi, synth, name, ids, rank, world, local_rank, st
         opt = _host_optimizer(x0, ntrain)
         opt.impl.train_loop(ctx.handle, x_pin.data_ptr(), g_pin.data_ptr(), warmup)
         barrier()
+        if world > 1:
+            opt.impl.train_loop(ctx.handle, x_pin.data_ptr(), g_pin.data_ptr(), 1)      # lines the ranks up (see above)
         e2e_s, _ = opt.impl.train_loop(ctx.handle, x_pin.data_ptr(), g_pin.data_ptr(), steps)
         torch.cuda.synchronize()
         e2e_ms = e2e_s * 1e3
@@ -227,6 +236,8 @@ def train_bench(torch, dist, capi, synth, name, ids, rank, world, local_rank, st
         barrier()
         if sus_sampler:
             sus_sampler.start()
+        if world > 1:
+            ctx.epoch_device()
         ev0.record(stream)
         for _ in range(n_sus):
             ctx.epoch_device()
@@ -266,6 +277,8 @@ def roofline_of(res, peaks):
             "algorithmic_flops_per_atom": res["flops_atom"], "atoms_per_launch": res["atoms_local"], "kernel_ms": res["kernel_ms"],
             "traffic": _ncu_traffic(res["name"], res["n_local"], res["form"]),
             "hbm_view": {"algorithmic_bytes_per_atom": 8 * cfg.NG,
+                         # stored two-phase forms: H_l and T'_l of every hidden node written once and read once
+                         "stored_activation_bytes_per_atom": 32 * sum(res["sizes"][1:-1]) if res["form"] in (3, 5) else 0,
                          "achieved_gbs": 8 * cfg.NG * res["atoms_local"] / (res["kernel_ms"] * 1e-3) / 1e9, "peak_gbs": _measured_hbm()}}
 
 
@@ -334,7 +347,10 @@ def run_ours(args):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": "%s, %d structures per GPU, one epoch" % (WORKLOADS[name], n_local),
                        "structures_total": head["total_struct"], "parallelism": "dp%d" % world,
-                       "l2": "inputs (%.0f MB FP64 descriptors per GPU) larger than L2, no flush" % (head["atoms_local"] * cfg.NG * 8 / 1e6)},
+                       "l2": "inputs (%.0f MB FP64 descriptors per GPU) larger than L2, no flush" % (head["atoms_local"] * cfg.NG * 8 / 1e6),
+                       "timing": "CUDA events on the library's stream round exactly K epochs, max over ranks"
+                                 + ("; at N > 1 one untimed epoch follows the host barrier so that the ranks start the timed epochs together"
+                                    if world > 1 else "")},
             "e2e": {"value": head["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 8 * head["P"], "d2h_bytes_per_step": 8 * (head["P"] + 3),
                     "includes": "the host layer's C++ training loop: pp_epoch with pinned host buffers + Optimizer::update_network (Rprop) per step"},
             "gpu_launches": head["launches"],
@@ -520,6 +536,8 @@ def run_md_bench(torch, capi, synth, device, cells, steps, warmup, dist=None, ra
         one_step()
     barrier()
     ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        one_step()                 # lines the ranks' timelines up after the host barrier (the exchange is a rendezvous)
     l0 = ctx.kernel_launches
     ev0.record(stream)
     for _ in range(steps):
@@ -547,6 +565,8 @@ def run_md_bench(torch, capi, synth, device, cells, steps, warmup, dist=None, ra
     for _ in range(max(1, warmup - 1)):
         ctx.md_step_exchange_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())
     barrier()
+    if world > 1:
+        ctx.md_step_exchange_ptr(x_pin.data_ptr(), f_pin.data_ptr(), ea_pin.data_ptr())      # lines the ranks up, as above
     phases = []
     t0 = time.perf_counter()
     for _ in range(steps):
@@ -676,7 +696,8 @@ def _torch_nccl_path():
 def _ncu_traffic(name, n_struct, form=1):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel(s), per epoch, from the committed ncu captures
     (only valid for the workload they were taken on; null otherwise)."""
-    key = {2: "mlp_fused2_kernel_%s_%d", 1: "mlp_kernel_fused_%s_%d", 3: "mlpw_kernels_%s_%d", 0: "two_phase_recompute_%s_%d"}[form] % (name, n_struct)
+    key = {2: "mlp_fused2_kernel_%s_%d", 1: "mlp_kernel_fused_%s_%d", 3: "mlpw_kernels_%s_%d", 0: "two_phase_recompute_%s_%d",
+           5: "two_phase_stored2_%s_%d", 4: "mlp32_fused_kernel_%s_%d"}.get(form, "form%d_%%s_%%d" % form) % (name, n_struct)
     for fn in ("r02_traffic.json", "r01_traffic.json"):
         try:
             with open(os.path.join(ROOT, "profiles", fn)) as f:

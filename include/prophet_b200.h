@@ -121,9 +121,11 @@ int pp_epoch_result_dev(pp_context* ctx, double** result_dev, int* n);
  * forward pass recomputed: any system), 1 = single-pass fused kernel, one CTA per SM, 2 = single-pass fused kernel with
  * in-place deltas, two CTAs per SM (single element, tanh / tanh_spline hidden nodes), 3 = two launches per element with
  * the activations kept in HBM between them (several elements, or networks too large for the single-pass kernels; even
- * layer widths up to 64, at most four hidden layers), 4 = the single-precision single-pass kernel of fp_mode 32.
- * Same arithmetic in forms 0 - 3, different summation order.
- * -1 before the first epoch.  Environment: PP_MLP_ONE_CTA=1 keeps form 2 from being chosen, PP_MLP_NO_STORE=1 form 3.
+ * layer widths up to 64, at most four hidden layers), 4 = the single-precision single-pass kernel of fp_mode 32,
+ * 5 = form 0 through the two-CTA kernels with the activations kept in HBM between the two launches instead of the
+ * forward pass being run again (several elements, networks of one or two hidden layers up to 64 wide).
+ * Same arithmetic in forms 0 - 3 and 5, different summation order.
+ * -1 before the first epoch.  Environment: PP_MLP_ONE_CTA=1 keeps form 2 from being chosen, PP_MLP_NO_STORE=1 forms 3 and 5.
  * No reference counterpart. */
 int pp_epoch_form(pp_context* ctx);
 /* Potential::evaluate (Potential.cpp:515-551): E_out[n_struct] = sum_atoms E_i + out_mean (every tag) */

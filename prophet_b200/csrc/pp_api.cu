@@ -1005,7 +1005,15 @@ static int struct_errors_all(pp_context* c)
 
 // forward pass of every element + per-structure energies and errors.  stored: the kernels of pp_mlpw.cu, which also
 // keep H_l / T'_l for the backward pass when with_store is set.
-static int forward_all(pp_context* c, bool stored, bool with_store)
+// the two-CTA kernels' own stored form (epoch form 5): FORWARD writes, TRAIN reads the element's activation store
+static void with_store2(pp_context* c, int e, MlpArgs& a)
+{
+  a.hstore = c->d_hstore[e].p;
+  a.tstore = c->d_tstore[e].p;
+  a.store_w = ppk_mlpw_store_width(c->nets[e].dev);
+}
+
+static int forward_all(pp_context* c, bool stored, bool with_store, bool store2 = false)
 {
   const bool two = !stored && all_two_cta(c);
   for (int e = 0; e < c->spec.n_elem; e++) {
@@ -1014,6 +1022,7 @@ static int forward_all(pp_context* c, bool stored, bool with_store)
       if (ppk_mlpw_forward(a, store_of(c, e, with_store), c->stream, &c->launches)) return 1;
     } else {
       int n_cta = 0;
+      if (store2) with_store2(c, e, a);
       if (ppk_mlp_launch2(PP_MLP_FORWARD, two, a, c->stream, &c->launches, &n_cta)) return 1;
     }
   }
@@ -1052,7 +1061,11 @@ static int choose_epoch_form(pp_context* c)
     if (stored && n.tile_atoms < 64) return 3;
     return 1;
   }
-  return stored ? 3 : 0;
+  if (stored) return 3;
+  // small networks (the two-CTA kernels): their FORWARD launch keeps H_l and T'_l in HBM and the TRAIN launch reads them
+  // back instead of running the forward pass again; PP_MLP_NO_STORE=1 keeps the recomputing form
+  if (all_two_cta(c) && ppk_mlp2_available() && getenv("PP_MLP_NO_STORE") == nullptr) return 5;
+  return 0;
 }
 
 extern "C" int pp_epoch_device(pp_context* c)
@@ -1101,14 +1114,14 @@ extern "C" int pp_epoch_device(pp_context* c)
       c->epoch_form = (n_cta > ppk_mlp_single_ctas()) ? 2 : 1;
       red_rows = n_cta; red_cols = stride;
     } else {
-      const bool stored = (form == 3);
-      if (stored) {
+      const bool stored = (form == 3), store2 = (form == 5);
+      if (stored || store2) {
         for (int e = 0; e < c->spec.n_elem; e++) {
           const size_t need = c->h_rows[e].size() * (size_t)ppk_mlpw_store_width(c->nets[e].dev);
           if (c->d_hstore[e].ensure(std::max<size_t>(need, 2), 0, c->stream) || c->d_tstore[e].ensure(std::max<size_t>(need, 2), 0, c->stream)) return 1;
         }
       }
-      if (forward_all(c, stored, true)) return 1;
+      if (forward_all(c, stored, true, store2)) return 1;
       if (tick(c, 1)) return 1;
       const bool two = !stored && all_two_cta(c);
       int rows_e[PP_MAX_ELEM] = {0, 0, 0, 0}, n_max = 0;
@@ -1118,7 +1131,10 @@ extern "C" int pp_epoch_device(pp_context* c)
         if (stored) {
           a.dw_tiles2 = c->nets[e].d_dw_tiles3.p;
           if (ppk_mlpw_backward(a, store_of(c, e, true), c->stream, &c->launches, &rows_e[e])) return 1;
-        } else if (ppk_mlp_launch2(PP_MLP_TRAIN, two, a, c->stream, &c->launches, &rows_e[e])) return 1;
+        } else {
+          if (store2) with_store2(c, e, a);
+          if (ppk_mlp_launch2(PP_MLP_TRAIN, two, a, c->stream, &c->launches, &rows_e[e])) return 1;
+        }
         n_max = std::max(n_max, rows_e[e]);
       }
       if (n_max == 0) n_max = 1;

@@ -88,6 +88,12 @@ struct MlpArgs {
   const void* dw_tiles;               // device table of weight-gradient tiles (ppk_mlp_num_dw_tiles)
   const void* dw_tiles2;              // device work table of the two-CTA fused kernel (ppk_mlp2_table), or nullptr
   double* scratch2;                   // two-CTA form: derivative scratch, ppk_mlp2_scratch_doubles(net) doubles
+  // two-CTA form, two-phase epoch with stored activations (several elements): hidden activations and exact derivatives
+  // [M][store_w], layer l's n_l columns after those of the layers before it.  FORWARD writes them, TRAIN reads them
+  // instead of running the forward pass again; nullptr = recompute
+  double* hstore;
+  double* tstore;
+  int store_w;
   // fused single-pass epoch (single-element systems, tiles made of whole structures)
   int n_tiles;
   const int* tile_struct0;            // [n_tiles+1] first structure of each tile
@@ -110,6 +116,7 @@ int ppk_mlp2_table(const NetDev& net, void* host_out, int* n_entries);
 size_t ppk_mlp2_scratch_doubles(const NetDev& net);
 int ppk_mlp_launch_fused(const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta);
 bool ppk_mlp_two_cta_ok(const NetDev& net);
+bool ppk_mlp2_available(void);          // the driver entry point the two-CTA launches need was found
 int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta);
 int ppk_mlp_launch(int mode, const MlpArgs& a, cudaStream_t st, long long* launches);
 

@@ -930,6 +930,41 @@ static bool mlp2_make_plan(const NetDev& net, int NTW, Mlp2Plan& p, std::vector<
   return true;
 }
 
+// Stored TRAIN launch of mlp_fused2_kernel: this thread's entries of every H_l tile (row 8 warp + g, columns 8 nt + 2 q + h,
+// the ones it owns in the forward pass) by asynchronous 16-byte copies from the activation store, and the matching T'
+// lines pulled into L2 for the loads that follow later in the tile.  A function of its own, reached through `if constexpr`:
+// as a lambda inside the kernel its mere definition cost the single-pass instantiation 48 bytes of spills.
+template <int NTW>
+__device__ __forceinline__ void mlp2_issue_hidden(const MlpArgs& a, const Mlp2Plan& p, double* sm, int row0, int nvalid, int warp, int g, int q,
+                                                  int SW, bool store_vec)
+{
+  const int r = 8 * warp + g;
+  const bool rv = r < nvalid;
+  const size_t rowoff = (size_t)(row0 + r) * SW;
+  int off = 0;
+  for (int l = 1; l < p.L; l++) {
+    const int n_l = p.n[l];
+    double* Hr = sm + p.h_off[l] + (size_t)r * p.kp[l];
+    const bool vec = store_vec && ((off | n_l) & 1) == 0;
+#pragma unroll
+    for (int nt = 0; nt < NTW; nt++) {
+      const int n = 8 * nt + 2 * q;
+      if (n < n_l) {
+        if (!rv) { Hr[n] = 0.0; if (n + 1 < n_l) Hr[n + 1] = 0.0; }
+        else if (vec) {
+          cp_async16(Hr + n, a.hstore + rowoff + off + n);
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(a.tstore + rowoff + off + n));
+        } else {
+          cp_async8(Hr + n, a.hstore + rowoff + off + n);
+          if (n + 1 < n_l) cp_async8(Hr + n + 1, a.hstore + rowoff + off + n + 1);
+        }
+      }
+    }
+    off += n_l;
+  }
+  cp_async_commit();
+}
+
 // MODE: PP_MLP_FUSED (single pass over tiles of whole structures), PP_MLP_TRAIN (backward of the two-phase epoch: the
 // error factor of every atom's structure is given, rows may be gathered through a.rows), PP_MLP_FORWARD (energies).
 // NTW: n-tiles (8 columns) of the widest hidden layer; NLW: hidden-layer weight matrices (L - 1)
@@ -991,6 +1026,12 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   // recomputed as 1 - H^2, but that is 0 or 2e-16 for a saturated node: harmless for the 1e-10 tolerance, not for
   // Rprop, which follows the SIGN of a dead neuron's gradient, a sum of nothing but such terms.
   double* dsc = a.scratch2 + (size_t)blockIdx.x * (NLW * NTW * 2 * MLP2_THREADS);
+  // Two-phase epoch with STORED activations (several elements): FORWARD also writes H_l and T'_l to HBM, row-major
+  // [M][store_w]; TRAIN copies the H_l tiles back (cp.async, each thread the entries it owns in the forward pass) and takes
+  // T' from the store where it forms the deltas, so that the forward products and the transfer functions run once.
+  const bool stored = !FUSED && a.hstore != nullptr;
+  const int SW = a.store_w;
+  const bool store_vec = (SW & 1) == 0;      // 16-byte accesses need even offsets; every layer width is checked below
   double dW[NLW][6][2];                       // per hidden-layer matrix: slot 0 = tiles 0..3, slot 1 = tiles 4..5
   double dwout[2] = {0.0, 0.0};               // output node: this warp's rows, parameters lane and lane + 32
   double sse_w = 0.0, vsse_w = 0.0, nval_w = 0.0;
@@ -1052,7 +1093,10 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   fence_proxy_async();                         // staging stores (and the barrier's init) before the copy engine's writes
   __syncthreads();
   Geom g_cur = tile_geom(blockIdx.x), g_nxt = tile_geom(blockIdx.x + gridDim.x);
-  if ((int)blockIdx.x < n_tiles) issue_load(g_cur);
+  if ((int)blockIdx.x < n_tiles) {
+    issue_load(g_cur);
+    if constexpr (MODE == PP_MLP_TRAIN) { if (stored) mlp2_issue_hidden<NTW>(a, p, sm, g_cur.row0, g_cur.nvalid, warp, g, q, SW, store_vec); }
+  }
   st_fetch(g_cur);
 
   const int rb = 8 * warp;                     // this warp's rows
@@ -1091,9 +1135,40 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     }
 
     // ---- forward: this warp's rows through every hidden layer, no inter-warp synchronisation -------------------------
-    {
+    const size_t srow = (size_t)(row0 + rb + g) * SW;      // this thread's row of the activation store
+    const bool srow_ok = (rb + g) < nvalid;
+    auto store_pair = [&](double* base, int off, int n_l, int nt, double v0, double v1) {
+      const int n = 8 * nt + 2 * q;
+      if (!srow_ok || n >= n_l) return;
+      double* dst = base + srow + off + n;
+      if (store_vec && ((off | n_l) & 1) == 0) *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);
+      else { dst[0] = v0; if (n + 1 < n_l) dst[1] = v1; }
+    };
+    // T' of this thread's activations (nt, h = 0 / 1) of hidden layer lh (0-based): from the store, else from the scratch
+    auto tprime = [&](int lh, int off, int n_l, int nt, double& t0, double& t1) {
+      if (MODE == PP_MLP_TRAIN && stored) {
+        const int n = 8 * nt + 2 * q;
+        t0 = t1 = 0.0;
+        if (srow_ok && n < n_l) {
+          const double* src = a.tstore + srow + off + n;
+          if (store_vec && ((off | n_l) & 1) == 0) { const double2 v = *reinterpret_cast<const double2*>(src); t0 = v.x; t1 = v.y; }
+          else { t0 = src[0]; if (n + 1 < n_l) t1 = src[1]; }
+        }
+      } else {
+        t0 = dsc[(size_t)((lh * NTW + nt) * 2 + 0) * MLP2_THREADS + tid];
+        t1 = dsc[(size_t)((lh * NTW + nt) * 2 + 1) * MLP2_THREADS + tid];
+      }
+    };
+    int off_last = 0;                            // column offset of the last hidden layer in the store
+    if (MODE == PP_MLP_TRAIN)
+      for (int l = 1; l < L - 1; l++) off_last += p.n[l];
+    if (MODE == PP_MLP_TRAIN && stored) {
+      cp_async_wait_all();                      // this thread's entries of the H_l tiles have landed
+      __syncwarp();
+    } else {
       const double* wo = sm + p.w_off[L - 1];
       double yp = 0.0;
+      int soff = 0;
       for (int l = 0; l < L - 1; l++) {
         const int n_in = p.n[l], n_out = p.n[l + 1];
         double acc[NTW][2];
@@ -1102,7 +1177,15 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         double* Hn = sm + p.h_off[l + 1] + (size_t)(rb + g) * p.kp[l + 1];
         const bool spline_layer = SPLINE && p.spline[l + 1] != 0;      // uniform per layer: tanh_spline (the reference's default) or tanh
         double tv[NTW][2];
-        if (!spline_layer) {
+        if (MODE == PP_MLP_FORWARD) {           // energies only; the stored form keeps T' (and H, below) for the TRAIN launch
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) {
+            double dv0, dv1;
+            if (!spline_layer) { tv[nt][0] = pp_fast_tanh(acc[nt][0], dv0, exptab); tv[nt][1] = pp_fast_tanh(acc[nt][1], dv1, exptab); }
+            else { tv[nt][0] = pp_fast_tanh_spline(acc[nt][0], dv0, a.tanh_table); tv[nt][1] = pp_fast_tanh_spline(acc[nt][1], dv1, a.tanh_table); }
+            if (stored) store_pair(a.tstore, soff, n_out, nt, dv0, dv1);
+          }
+        } else if (!spline_layer) {
 #pragma unroll
           for (int nt = 0; nt < NTW; nt++) {
 #pragma unroll
@@ -1123,6 +1206,11 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
             }
           }
         }
+        if (MODE == PP_MLP_FORWARD && stored) {
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) store_pair(a.hstore, soff, n_out, nt, tv[nt][0], tv[nt][1]);
+        }
+        soff += n_out;
         const bool last = (l == L - 2);
 #pragma unroll
         for (int nt = 0; nt < NTW; nt++) {
@@ -1203,11 +1291,21 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       const double c = cvec[rb + g];
 #pragma unroll
       for (int nt = 0; nt < NTW; nt++) {
+        if (MODE == PP_MLP_TRAIN) {
+          double tp[2];
+          tprime(L - 2, off_last, n_h, nt, tp[0], tp[1]);
 #pragma unroll
-        for (int h = 0; h < 2; h++) {
-          const int n = 8 * nt + 2 * q + h;
-          const double tp = dsc[(size_t)(((L - 2) * NTW + nt) * 2 + h) * MLP2_THREADS + tid];
-          if (n < n_h) Hr[n] = c * wo[n] * tp;
+          for (int h = 0; h < 2; h++) {
+            const int n = 8 * nt + 2 * q + h;
+            if (n < n_h) Hr[n] = c * wo[n] * tp[h];
+          }
+        } else {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            const int n = 8 * nt + 2 * q + h;
+            const double tp = dsc[(size_t)(((L - 2) * NTW + nt) * 2 + h) * MLP2_THREADS + tid];
+            if (n < n_h) Hr[n] = c * wo[n] * tp;
+          }
         }
       }
       __syncwarp();
@@ -1249,20 +1347,36 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         __syncthreads();                                                               // every product reading H_l is done
         const int n_l = p.n[l];
         double* Hr = sm + p.h_off[l] + (size_t)(rb + g) * p.kp[l];
+        int off_l = 0;
+        if (MODE == PP_MLP_TRAIN)
+          for (int l2 = 1; l2 < l; l2++) off_l += p.n[l2];
 #pragma unroll
         for (int nt = 0; nt < NTW; nt++) {
+          if (MODE == PP_MLP_TRAIN) {
+            double tp[2];
+            tprime(l - 1, off_l, n_l, nt, tp[0], tp[1]);
 #pragma unroll
-          for (int h = 0; h < 2; h++) {
-            const int n = 8 * nt + 2 * q + h;
-            const double tp = dsc[(size_t)(((l - 1) * NTW + nt) * 2 + h) * MLP2_THREADS + tid];
-            if (n < n_l) Hr[n] = accb[nt][h] * tp;
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * nt + 2 * q + h;
+              if (n < n_l) Hr[n] = accb[nt][h] * tp[h];
+            }
+          } else {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int n = 8 * nt + 2 * q + h;
+              const double tp = dsc[(size_t)(((l - 1) * NTW + nt) * 2 + h) * MLP2_THREADS + tid];
+              if (n < n_l) Hr[n] = accb[nt][h] * tp;
+            }
           }
         }
         __syncwarp();
       }
     }
     __syncthreads();                                                                   // X is free: next tile's copy
-    if (tile + (int)gridDim.x < n_tiles) issue_load(g_nxt);
+    if (tile + (int)gridDim.x < n_tiles) {
+      issue_load(g_nxt);
+      if constexpr (MODE == PP_MLP_TRAIN) { if (stored) mlp2_issue_hidden<NTW>(a, p, sm, g_nxt.row0, g_nxt.nvalid, warp, g, q, SW, store_vec); }
+    }
     g_cur = g_nxt;
     g_nxt = g_nn;
   }
@@ -1382,6 +1496,8 @@ bool ppk_mlp_two_cta_ok(const NetDev& net)
   const CachedPlans& cp = cached_plans(net);
   return cp.TM == MLP2_TM && cp.ok2 && getenv("PP_MLP_ONE_CTA") == nullptr;
 }
+
+bool ppk_mlp2_available(void) { return encode_tiled() != nullptr; }
 
 int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t st, long long* launches, int* n_cta)
 {

@@ -83,7 +83,7 @@ def test_fp32_epoch_shapes_and_tile_fillings_against_oracle(hidden, reps):
         try:
             ctx.set_input_scaling(0, mean, scale)
             r64 = ctx.epoch(net["params"])
-            assert ctx.epoch_form() in (0, 1, 2, 3)
+            assert ctx.epoch_form() in (0, 1, 2, 3, 5)
             assert fp32_ran or np.array_equal(r64["gradient"], r["gradient"])
         finally:
             os.environ.pop("PP_FP32_OFF", None)
@@ -104,7 +104,7 @@ def test_fp32_mode_keeps_fp64_for_systems_it_does_not_cover():
         ctx.set_output_scaling(c.out_mean, c.out_scale)
         ctx.add_structures(c.natoms, np.stack(c.cells), np.concatenate(c.frac), c.elem_flat(), c.targets, c.tags)
         r = ctx.epoch(c.d["x_before.0"])
-        assert ctx.epoch_form() in (0, 3)
+        assert ctx.epoch_form() in (0, 3, 5)
         assert rel_err(r["gradient"], c.d["gradient.0"]) < 1e-10
     finally:
         ctx.close()
