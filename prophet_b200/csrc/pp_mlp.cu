@@ -1123,6 +1123,26 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         cvec[tid] = c;
       }
     }
+    // stored TRAIN: T' of the last hidden layer is needed right after barrier A; its loads fly while the tile's copies land
+    double tpl[(MODE == PP_MLP_TRAIN) ? NTW : 1][2];
+    if constexpr (MODE == PP_MLP_TRAIN) {
+      if (stored) {
+        int off_last0 = 0;
+        for (int l = 1; l < L - 1; l++) off_last0 += p.n[l];
+        const int n_h = p.n[L - 1];
+        const bool ok = (rb + g) < nvalid, vec = store_vec && ((off_last0 | n_h) & 1) == 0;
+        const double* src = a.tstore + (size_t)(row0 + rb + g) * SW + off_last0;
+#pragma unroll
+        for (int nt = 0; nt < NTW; nt++) {
+          const int n = 8 * nt + 2 * q;
+          tpl[nt][0] = tpl[nt][1] = 0.0;
+          if (ok && n < n_h) {
+            if (vec) { const double2 v = *reinterpret_cast<const double2*>(src + n); tpl[nt][0] = v.x; tpl[nt][1] = v.y; }
+            else { tpl[nt][0] = src[n]; if (n + 1 < n_h) tpl[nt][1] = src[n + 1]; }
+          }
+        }
+      }
+    }
     mbar_wait(mbar, (unsigned)n_done & 1u);
 
     // ---- normalise this warp's 8 rows in place (NN.cpp:647-651); column NG is the bias input ---------------------
@@ -1293,7 +1313,8 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       for (int nt = 0; nt < NTW; nt++) {
         if (MODE == PP_MLP_TRAIN) {
           double tp[2];
-          tprime(L - 2, off_last, n_h, nt, tp[0], tp[1]);
+          if (stored) { tp[0] = tpl[nt][0]; tp[1] = tpl[nt][1]; }
+          else tprime(L - 2, off_last, n_h, nt, tp[0], tp[1]);
 #pragma unroll
           for (int h = 0; h < 2; h++) {
             const int n = 8 * nt + 2 * q + h;
@@ -1354,7 +1375,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         for (int nt = 0; nt < NTW; nt++) {
           if (MODE == PP_MLP_TRAIN) {
             double tp[2];
-            tprime(l - 1, off_l, n_l, nt, tp[0], tp[1]);
+            tprime(l - 1, off_l, n_l, nt, tp[0], tp[1]);      // (loading these before the products above was tried: 528 bytes of spills)
 #pragma unroll
             for (int h = 0; h < 2; h++) {
               const int n = 8 * nt + 2 * q + h;
