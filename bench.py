@@ -127,8 +127,8 @@ def load_shard(ctx, capi, synth, cfg, ids, batch=1000):
     return t_desc, t_gen, t_lib
 
 
-def make_context(capi, synth, cfg, device):
-    ctx = capi.Context(device)
+def make_context(capi, synth, cfg, device, fp_mode=64):
+    ctx = capi.Context(device, fp_mode)
     ctx.set_descriptors(len(cfg.elements), cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
     nets = []
     for e, z in enumerate(cfg.elements):
@@ -282,6 +282,60 @@ def roofline_of(res, peaks):
                          "achieved_gbs": 8 * cfg.NG * res["atoms_local"] / (res["kernel_ms"] * 1e-3) / 1e9, "peak_gbs": _measured_hbm()}}
 
 
+def fp32_mode_bench(torch, capi, synth, device, steps, warmup, n_struct=10000, n_check=512):
+    """north_star's FP32 mode (pp_create(..., fp_mode = 32), tolerance relative 1e-5 against the FP64 path) on the headline
+    workload, one GPU: the epoch time of the FP32 kernel (FP32 descriptors in HBM, forward / delta products as 3xTF32 on
+    tcgen05.mma with TMEM accumulators, FP64 energies and sums) and, outside the timed region, its gradient and SSE
+    against the FP64 kernels on the same structures and parameters."""
+    cfg = synth.CONFIGS["C2"](n_struct)
+    ctx, nets = make_context(capi, synth, cfg, device, 32)
+    load_shard(ctx, capi, synth, cfg, np.arange(n_struct))
+    ctx.precondition(True)
+    x0 = np.concatenate([n["params"] for n in nets])
+    ctx.set_parameters(x0)
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    for _ in range(max(warmup, 3)):
+        ctx.epoch_device()
+    torch.cuda.synchronize()
+    ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(steps):
+        ctx.epoch_device()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / steps
+    form = ctx.epoch_form()
+    atoms = int(ctx.n_atoms)
+    ctx.close()
+    # parity on a subset: same structures, same parameters, the two modes
+    cfgc = synth.CONFIGS["C2"](n_check)
+    res = {}
+    for mode in (64, 32):
+        c, _ = make_context(capi, synth, cfgc, device, mode)
+        load_shard(c, capi, synth, cfgc, np.arange(n_check))
+        c.precondition(True)
+        res[mode] = c.epoch(x0)
+        c.close()
+    gmax = float(np.max(np.abs(res[64]["gradient"])))
+    grad_err = float(np.max(np.abs(res[32]["gradient"] - res[64]["gradient"])) / gmax)
+    sse_err = abs(res[32]["SSE"] - res[64]["SSE"]) / abs(res[64]["SSE"])
+    sizes = [int(v) for v in nets[0]["sizes"]]
+    F = 2 * sum(a * b for a, b in zip(sizes[:-1], sizes[1:]))
+    flops_atom = 3 * F - 2 * sizes[0] * sizes[1]
+    bytes_atom = 4 * ((cfg.NG + 3) // 4 * 4)
+    return {"workload": "%s, %d structures, fp_mode 32" % (WORKLOADS["C2"], n_struct), "dtype": "f32 (3xTF32 products, FP32 accumulation; FP64 energies, errors, sums)",
+            "ms_per_step": ms, "value": n_struct / (ms * 1e-3), "unit": "structures/s", "steps": steps, "epoch_form": form,
+            "kernel": "mlp32_umma_kernel (tcgen05.mma kind::tf32 from shared memory into TMEM for the forward and delta products, "
+                      "tcgen05.ld epilogues; weight gradients on mma.sync tf32)",
+            "parity_vs_fp64": {"structures": n_check, "gradient_rel_err": grad_err, "sse_rel_err": sse_err, "tolerance": 1e-5,
+                               "ok": bool(grad_err <= 1e-5 and sse_err <= 1e-5)},
+            "roofline": {"bound": "hbm", "achieved": bytes_atom * atoms / (ms * 1e-3) / 1e9, "peak": _measured_hbm(), "unit": "GB/s",
+                         "frac": bytes_atom * atoms / (ms * 1e-3) / 1e9 / _measured_hbm(), "algorithmic_bytes_per_atom": bytes_atom,
+                         "note": "FP32 descriptors are half the bytes; the epoch is far from the HBM bound -- it is bound by the legacy mma.sync "
+                                 "tf32 rate of the weight-gradient products and by the serial phases of one resident CTA per SM",
+                         "algorithmic_tflops": flops_atom * atoms / (ms * 1e-3) / 1e12}}
+
+
 def multirank_parity(torch, dist, capi, synth, rank, world, local_rank, name="C2", n_union=64):
     """N > 1 only, outside every timed region: a small union of structures sharded s mod N (Setup.cpp:582) must give, after
     the all-reduce, the [gradient, SSE, vSSE, nval] of a single-rank epoch over the same structures."""
@@ -389,6 +443,10 @@ def run_ours(args):
                                            "structures_per_s_load": r["n_local"] / max(r["lib_s"], 1e-9)}}
         if rank == 0:
             out["other_configs"] = others
+    if world == 1 and not args.no_fp32:
+        fp32 = fp32_mode_bench(torch, capi, synth, local_rank, args.steps, args.warmup)
+        assert fp32["parity_vs_fp64"]["ok"], "FP32 mode differs from the FP64 path by more than 1e-5: %r" % (fp32["parity_vs_fp64"],)
+        out["fp32"] = fp32
     if world > 1:
         par = multirank_parity(torch, dist, capi, synth, rank, world, local_rank)
         if rank == 0:
@@ -834,6 +892,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=24, help="structures per host core for the CPU arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-md", action="store_true", help="skip the pair_nn (MD) section")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the fp32 object (FP32 mode on the headline workload, N = 1 only)")
     ap.add_argument("--md-cells", type=int, default=50, help="diamond-Si supercell edge in unit cells (C5 = 50 -> 1M atoms)")
     ap.add_argument("--md-steps", type=int, default=5)
     args = ap.parse_args()

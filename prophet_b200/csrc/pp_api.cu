@@ -69,6 +69,7 @@ struct pp_context {
   DevBuf<float> d_G32;                 // FP32 mode: normalised descriptors [atoms][NGp]
   DevBuf<double> d_ms32;               // FP32 mode: mean and scale of every element, [2][n_elem][NG]
   bool g32_dirty = true;
+  bool fp32_umma_ran = false;          // a tcgen05 FP32 launch is in flight / unchecked (its error flag is read at the next host sync)
   cudaStream_t stream = nullptr;
   long long launches = 0;
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -936,7 +937,7 @@ static bool fp32_epoch(pp_context* c)
 
 static int prepare_fused_tiles(pp_context* c)
 {
-  const int TM = (c->spec.n_elem == 1 && c->nets[0].set) ? (fp32_epoch(c) ? ppk_mlp32_tile_atoms() : c->nets[0].tile_atoms) : 0;
+  const int TM = (c->spec.n_elem == 1 && c->nets[0].set) ? (fp32_epoch(c) ? (ppk_mlp32u_ok(c->nets[0].dev) ? ppk_mlp32u_tile_atoms() : ppk_mlp32_tile_atoms()) : c->nets[0].tile_atoms) : 0;
   if (!c->tiles_dirty && c->tiles_tm == TM) return 0;
   c->tiles_dirty = false;
   c->tiles_tm = TM;
@@ -1103,7 +1104,10 @@ extern "C" int pp_epoch_device(pp_context* c)
       MlpArgs a = mlp_args_train(c, 0);
       a.dw_tiles2 = c->nets[0].d_dw_tiles32.p;
       int n_cta = 0;
-      if (ppk_mlp32_launch_fused(a, c->d_G32.p, c->n_atoms, c->stream, &c->launches, &n_cta)) return 1;
+      if (ppk_mlp32u_ok(c->nets[0].dev)) {          // forward and delta products on tcgen05.mma (pp_mlp32u.cu)
+        if (ppk_mlp32u_launch_fused(a, c->d_G32.p, c->n_atoms, c->stream, &c->launches, &n_cta)) return 1;
+        c->fp32_umma_ran = true;
+      } else if (ppk_mlp32_launch_fused(a, c->d_G32.p, c->n_atoms, c->stream, &c->launches, &n_cta)) return 1;
       red_rows = n_cta; red_cols = stride;
     } else if (form == 1 || form == 2) {
       // one pass: forward, per-structure error and backward in the same kernel; loss terms ride in the partials' tail
@@ -1203,6 +1207,10 @@ extern "C" int pp_epoch(pp_context* c, const double* params_in, double* grad_out
   PP_CUDA(cudaMemcpyAsync(c->h_result, c->d_result.p, ((size_t)c->P_total + 3) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   const double t1 = now_us();
   PP_CUDA(cudaStreamSynchronize(c->stream));
+  if (c->fp32_umma_ran) {
+    c->fp32_umma_ran = false;
+    PP_REQUIRE(!ppk_mlp32u_failed(c->stream), "pp_epoch: a tensor-core batch of the FP32 kernel did not complete (internal error)");
+  }
   const double t2 = now_us();
   c->epoch_phases_pending = true;
   const double t3 = now_us();

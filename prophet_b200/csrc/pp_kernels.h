@@ -147,6 +147,13 @@ int ppk_mlp32_table(const NetDev& net, void* host_out, int* n_entries);      // 
 int ppk_g_to_f32(const double* G, int NG, int NGp, long long n_atoms, const int* elem, const double* mean, const double* scale, float* out,
                  cudaStream_t st, long long* launches);
 int ppk_mlp32_launch_fused(const MlpArgs& a, const float* G32, long long n_atoms, cudaStream_t st, long long* launches, int* n_cta);
+// the same epoch with the forward and delta products on tcgen05.mma (pp_mlp32u.cu): eligibility (PP_FP32_NO_UMMA=1 switches
+// it off), tile size, launch (same work table as ppk_mlp32_table), and the flag a launch raises when a tensor-pipe batch
+// never completed (reading it synchronises the stream)
+bool ppk_mlp32u_ok(const NetDev& net);
+int ppk_mlp32u_tile_atoms(void);
+int ppk_mlp32u_launch_fused(const MlpArgs& a, const float* G32, long long n_atoms, cudaStream_t st, long long* launches, int* n_cta);
+int ppk_mlp32u_failed(cudaStream_t st);
 
 // per-structure energies / errors (Potential.cpp:641-668)
 struct StructArgs {

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Epoch time of any synthetic configuration (C2 / C3 / C4) at a chosen structure count (tuning aid).
-    python tools/epoch_timing.py C3 2000"""
+    python tools/epoch_timing.py C3 2000 [transfer]        PP_FP_MODE=32 selects the FP32 mode of pp_create"""
 import os
 import sys
 
@@ -17,7 +17,7 @@ def main():
     cfg = synth.CONFIGS[name](n_struct)
     if len(sys.argv) > 3:
         cfg.transfer = sys.argv[3]          # e.g. tanh_spline (the reference's default transfer function)
-    ctx = capi.Context(0)
+    ctx = capi.Context(0, int(os.environ.get("PP_FP_MODE", "64")))
     ctx.set_descriptors(len(cfg.elements), cfg.G1, cfg.G2, cfg.G3, cfg.G4, cfg.rcut)
     zmap = {z: i for i, z in enumerate(cfg.elements)}
     for e, z in enumerate(cfg.elements):

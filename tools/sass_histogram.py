@@ -10,9 +10,9 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "prophet_b200", "libprophet_b200.so")
-HOT = ["mlp_fused2_kernel", "mlpw_forward_kernel", "mlpw_backward_kernel", "mlp32_fused_kernel", "mlp_kernel", "md_desc_kernel", "md_force_kernel",
+HOT = ["mlp_fused2_kernel", "mlpw_forward_kernel", "mlpw_backward_kernel", "mlp32_fused_kernel", "mlp32_umma_kernel", "mlp_kernel", "md_desc_kernel", "md_force_kernel",
        "md_fused_kernel", "desc_periodic_kernel", "reduce_partials_kernel", "reduce_push_kernel", "wait_sum_kernel", "struct_errors_kernel"]
-WATCH = ["DMMA", "HMMA", "DFMA", "DMUL", "DADD", "FFMA", "MUFU", "UTMALDG", "UBLKCP", "SYNCS", "LDS", "STS", "LDG", "STG", "LDL", "STL", "RED", "ATOM",
+WATCH = ["DMMA", "HMMA", "UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTCATOMSWS", "DFMA", "DMUL", "DADD", "FFMA", "MUFU", "UTMALDG", "UBLKCP", "SYNCS", "LDS", "STS", "LDG", "STG", "LDL", "STL", "RED", "ATOM",
          "BAR", "SHFL", "LDSM", "LDC", "NOP", "BRA"]
 
 

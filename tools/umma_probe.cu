@@ -59,7 +59,7 @@ __host__ __device__ inline int kmajor_off(int r, int k, int K) { return ((r >> 3
 // A: a_mn == 0: [M][K] (K-major operand); a_mn == 1: [K][M] (MN-major operand over the row-major-by-atom storage)
 // B: b_mn == 0: [64][K];                     b_mn == 1: [K][64]
 __global__ void __launch_bounds__(128) probe_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D, int K, int M,
-                                                    int a_mn, int b_mn)
+                                                    int a_mn, int b_mn, int variant)
 {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ unsigned tmem_base_s;
@@ -87,9 +87,12 @@ __global__ void __launch_bounds__(128) probe_kernel(const float* __restrict__ A,
     for (int s = 0; s < K / 8; s++) {
       // K-major: LBO = distance between the two 16-byte K chunks of one instruction (128 B), SBO = between 8-row groups.
       // MN-major over [K][cols] storage: MN chunks (4 columns) 128 B apart (SBO); a group of 8 atoms is (cols / 4) * 128 B (LBO)
-      const unsigned long long da = a_mn ? umma_desc(smem_u32(As) + s * (M >> 2) * 128, (M >> 2) * 128, 128)
+      // variant 1: leading / stride offsets of the MN-major descriptors swapped
+      const unsigned a_l = variant ? 128u : (unsigned)(M >> 2) * 128u, a_s = variant ? (unsigned)(M >> 2) * 128u : 128u;
+      const unsigned b_l = variant ? 128u : (unsigned)(N >> 2) * 128u, b_s = variant ? (unsigned)(N >> 2) * 128u : 128u;
+      const unsigned long long da = a_mn ? umma_desc(smem_u32(As) + s * (M >> 2) * 128, a_l, a_s)
                                          : umma_desc(smem_u32(As) + s * 256, 128, (K >> 2) * 128);
-      const unsigned long long db = b_mn ? umma_desc(smem_u32(Bs) + s * (N >> 2) * 128, (N >> 2) * 128, 128)
+      const unsigned long long db = b_mn ? umma_desc(smem_u32(Bs) + s * (N >> 2) * 128, b_l, b_s)
                                          : umma_desc(smem_u32(Bs) + s * 256, 128, (K >> 2) * 128);
       umma_tf32(tmem, da, db, idesc, s > 0);
     }
@@ -122,7 +125,7 @@ static float tf32r(float x)
   return y;
 }
 
-static void run_case(int M, int K, int a_mn, int b_mn, float* dA, float* dB, float* dD, size_t smem)
+static void run_case(int M, int K, int a_mn, int b_mn, float* dA, float* dB, float* dD, size_t smem, int variant = 0)
 {
   std::vector<float> A(M * K), B(64 * K), D(128 * 64);
   for (auto& v : A) v = tf32r((float)rand() / RAND_MAX - 0.5f);       // logical A[m][k], B[n][k]
@@ -133,7 +136,7 @@ static void run_case(int M, int K, int a_mn, int b_mn, float* dA, float* dB, flo
   CK(cudaMemcpy(dA, As.data(), As.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(dB, Bs.data(), Bs.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemset(dD, 0, 128 * 64 * 4));
-  probe_kernel<<<1, 128, smem>>>(dA, dB, dD, K, M, a_mn, b_mn);
+  probe_kernel<<<1, 128, smem>>>(dA, dB, dD, K, M, a_mn, b_mn, variant);
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost));
   std::vector<double> R(M * 64);
@@ -151,7 +154,7 @@ static void run_case(int M, int K, int a_mn, int b_mn, float* dA, float* dB, flo
       for (int n = 0; n < 64; n++) e = fmax(e, fabs(R[m * 64 + n] - D[l * 64 + n]));
       if (e < 1e-4) { lane_of_row[m] = l; found++; break; }
     }
-  printf("M=%d K=%d A %s B %s: %d of %d rows found; lanes of rows 0,1,15,16,17,31,32,48,63: %d %d %d %d %d %d %d %d %d\n", M, K, a_mn ? "MN" : "K",
+  printf("variant %d M=%d K=%d A %s B %s: %d of %d rows found; lanes of rows 0,1,15,16,17,31,32,48,63: %d %d %d %d %d %d %d %d %d\n", variant, M, K, a_mn ? "MN" : "K",
          b_mn ? "MN" : "K", found, M, lane_of_row[0], lane_of_row[1], lane_of_row[15], lane_of_row[16], lane_of_row[17], lane_of_row[31],
          lane_of_row[32], lane_of_row[48], lane_of_row[63]);
   if (found == 0) printf("   D[lane 0][0..3] = %g %g %g %g ; R[0][0..3] = %g %g %g %g\n", D[0], D[1], D[2], D[3], R[0], R[1], R[2], R[3]);
@@ -170,5 +173,13 @@ int main()
   run_case(128, 128, 1, 1, dA, dB, dD, smem);
   run_case(64, 64, 0, 0, dA, dB, dD, smem);
   run_case(64, 128, 1, 1, dA, dB, dD, smem);
+  run_case(128, 64, 1, 0, dA, dB, dD, smem, 1);
+  run_case(128, 64, 0, 1, dA, dB, dD, smem, 1);
+  run_case(128, 128, 1, 1, dA, dB, dD, smem, 1);
+  run_case(64, 128, 1, 1, dA, dB, dD, smem, 1);
+  run_case(128, 8, 1, 0, dA, dB, dD, smem, 0);
+  run_case(128, 8, 1, 0, dA, dB, dD, smem, 1);
+  run_case(128, 8, 0, 1, dA, dB, dD, smem, 0);
+  run_case(128, 8, 0, 1, dA, dB, dD, smem, 1);
   return 0;
 }
