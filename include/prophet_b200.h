@@ -46,7 +46,9 @@ int pp_version(void);
  * fp_mode 32: the reference's USE_FLOAT switch (Common.h:53-61; its own float build does not compile, so the FP64
  *   reference at relative 1e-5 is the yardstick).  Training epochs of single-element systems with tanh hidden layers
  *   (one or two, up to 64 wide, structures of up to 256 atoms) run in single precision: the descriptors are kept as
- *   normalised FP32 and the layer products are 3xTF32 tensor-core products accumulated in FP32; structure energies,
+ *   normalised FP32 and the layer products are 3xTF32 tensor-core products accumulated in FP32 (forward and delta
+ *   products on tcgen05.mma with TMEM accumulators when every structure has at most 128 atoms and the layers are at most
+ *   63 wide, mma.sync otherwise; PP_FP32_NO_UMMA=1 keeps mma.sync); structure energies,
  *   errors, loss terms and the final gradient sum stay FP64 (pp_epoch_form == 4).  Descriptors, neighbour lists,
  *   evaluation, MD and every other system keep the FP64 kernels in this mode. */
 int pp_create(int device, int fp_mode, pp_context** out);

@@ -69,6 +69,7 @@ struct pp_context {
   DevBuf<float> d_G32;                 // FP32 mode: normalised descriptors [atoms][NGp]
   DevBuf<double> d_ms32;               // FP32 mode: mean and scale of every element, [2][n_elem][NG]
   bool g32_dirty = true;
+  bool fp32_umma = false;              // FP32 epochs run the tcgen05 kernel (decided with the tile list)
   bool fp32_umma_ran = false;          // a tcgen05 FP32 launch is in flight / unchecked (its error flag is read at the next host sync)
   cudaStream_t stream = nullptr;
   long long launches = 0;
@@ -937,7 +938,17 @@ static bool fp32_epoch(pp_context* c)
 
 static int prepare_fused_tiles(pp_context* c)
 {
-  const int TM = (c->spec.n_elem == 1 && c->nets[0].set) ? (fp32_epoch(c) ? (ppk_mlp32u_ok(c->nets[0].dev) ? ppk_mlp32u_tile_atoms() : ppk_mlp32_tile_atoms()) : c->nets[0].tile_atoms) : 0;
+  int TM = 0;
+  if (c->spec.n_elem == 1 && c->nets[0].set) {
+    TM = c->nets[0].tile_atoms;
+    if (fp32_epoch(c)) {
+      // the tcgen05 kernel works on 128-atom tiles; a structure of 129 .. 256 atoms sends the system to the mma.sync kernel
+      int largest = 0;
+      for (int s = 0; s < c->n_struct; s++) largest = std::max(largest, (int)(c->h_struct_atom0[s + 1] - c->h_struct_atom0[s]));
+      c->fp32_umma = ppk_mlp32u_ok(c->nets[0].dev) && largest <= ppk_mlp32u_tile_atoms();
+      TM = c->fp32_umma ? ppk_mlp32u_tile_atoms() : ppk_mlp32_tile_atoms();
+    }
+  }
   if (!c->tiles_dirty && c->tiles_tm == TM) return 0;
   c->tiles_dirty = false;
   c->tiles_tm = TM;
@@ -1104,7 +1115,7 @@ extern "C" int pp_epoch_device(pp_context* c)
       MlpArgs a = mlp_args_train(c, 0);
       a.dw_tiles2 = c->nets[0].d_dw_tiles32.p;
       int n_cta = 0;
-      if (ppk_mlp32u_ok(c->nets[0].dev)) {          // forward and delta products on tcgen05.mma (pp_mlp32u.cu)
+      if (c->fp32_umma) {          // forward and delta products on tcgen05.mma (pp_mlp32u.cu)
         if (ppk_mlp32u_launch_fused(a, c->d_G32.p, c->n_atoms, c->stream, &c->launches, &n_cta)) return 1;
         c->fp32_umma_ran = true;
       } else if (ppk_mlp32_launch_fused(a, c->d_G32.p, c->n_atoms, c->stream, &c->launches, &n_cta)) return 1;
