@@ -128,17 +128,7 @@ reduce_push_kernel(const double* __restrict__ partial, int n_cta, int stride, in
   const int col = threadIdx.x & 31, grp = threadIdx.x >> 5;
   const int p = blockIdx.x * 32 + col;
   // fixed order: group g adds rows g, g + 32, g + 64, ... (two chains), then the 32 group sums are added in order
-  double s0 = 0.0, s1 = 0.0;
-  if (p < ncols_partial) {
-    const double* src = partial + p;
-    int c = grp;
-    for (; c + PP_RED_GROUPS < n_cta; c += 2 * PP_RED_GROUPS) {
-      s0 += src[(size_t)c * stride];
-      s1 += src[(size_t)(c + PP_RED_GROUPS) * stride];
-    }
-    if (c < n_cta) s0 += src[(size_t)c * stride];
-  }
-  part[grp][col] = s0 + s1;
+  part[grp][col] = (p < ncols_partial) ? pp_group_column_sum(partial + p, grp, n_cta, stride) : 0.0;
   __syncthreads();
   if (grp == 0 && p < ncols) {
     double s = part[0][col];

@@ -124,3 +124,21 @@ __device__ __forceinline__ double pp_warp_sum(double v)
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+
+// One row group's share of a column sum over the per-CTA partial rows (reduce_partials_kernel, reduce_push_kernel): rows
+// grp, grp + 32, grp + 64, ... of one column, ten at a time with all ten loads in flight, added in a FIXED order (a
+// balanced tree over the ten, chunks in sequence), so that the sum is bit-reproducible.
+__device__ __forceinline__ double pp_group_column_sum(const double* __restrict__ src, int grp, int n_cta, int stride)
+{
+  double total = 0.0;
+  for (int c0 = grp; c0 < n_cta; c0 += 320) {
+    double v[10];
+#pragma unroll
+    for (int j = 0; j < 10; j++) {
+      const int c = c0 + 32 * j;
+      v[j] = (c < n_cta) ? src[(size_t)c * stride] : 0.0;
+    }
+    total += (((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]))) + (v[8] + v[9]);
+  }
+  return total;
+}
