@@ -69,6 +69,10 @@ struct pp_context {
   DevBuf<float> d_G32;                 // FP32 mode: normalised descriptors [atoms][NGp]
   DevBuf<double> d_ms32;               // FP32 mode: mean and scale of every element, [2][n_elem][NG]
   bool g32_dirty = true;
+  // normalised FP64 copy of the descriptors, (x - mean) * (1 / scale) per atom's element: the training kernels then skip
+  // the per-tile normalisation pass (NN.cpp:647-651).  Refreshed when descriptors or input scalings change.
+  DevBuf<double> d_Gn, d_msn;
+  bool gn_dirty = true, gn_ready = false;
   bool fp32_umma = false;              // FP32 epochs run the tcgen05 kernel (decided with the tile list)
   bool fp32_umma_ran = false;          // a tcgen05 FP32 launch is in flight / unchecked (its error flag is read at the next host sync)
   cudaStream_t stream = nullptr;
@@ -196,7 +200,7 @@ extern "C" void pp_destroy(pp_context* c)
   c->d_overflow.release(); c->d_params.release(); c->d_paramsT.release(); c->d_tanh_table.release();
   c->d_struct_atom0.release(); c->d_FtoA.release(); c->d_target.release(); c->d_frac.release(); c->d_G.release();
   c->d_E_atom.release(); c->d_E_struct.release(); c->d_cstruct.release(); c->d_mxyz.release(); c->d_tag.release();
-  c->d_elem.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_err_scratch.release(); c->d_scratch2.release(); c->d_err_ticket.release();
+  c->d_elem.release(); c->d_Gn.release(); c->d_msn.release(); c->d_atom_struct.release(); c->d_partial.release(); c->d_result.release(); c->d_err_scratch.release(); c->d_scratch2.release(); c->d_err_ticket.release();
   if (c->h_result) { cudaFreeHost(c->h_result); c->h_result = nullptr; c->h_result_cap = 0; }
 
   c->d_stat_partial.release(); c->d_stat_sums.release(); c->d_count.release();
@@ -427,6 +431,7 @@ extern "C" int pp_set_descriptors(pp_context* c, int n_elem, int nG1, const doub
   c->spec = S;
   c->spec_set = true;
   c->g32_dirty = true;
+  c->gn_dirty = true;
   return 0;
 }
 
@@ -539,6 +544,7 @@ extern "C" int pp_set_network(pp_context* c, int elem, int n_layers, const int* 
   }
   c->tiles_dirty = true;
   c->g32_dirty = true;
+  c->gn_dirty = true;
   n.set = true;
   return rebuild_param_layout(c);
 }
@@ -592,6 +598,7 @@ extern "C" int pp_set_input_scaling(pp_context* c, int elem, const double* in_me
   n.mean.assign(in_mean, in_mean + NG);
   n.scale.assign(in_scale, in_scale + NG);
   c->g32_dirty = true;
+  c->gn_dirty = true;
   PP_CUDA(cudaMemcpy(n.d_mean.p, n.mean.data(), NG * sizeof(double), cudaMemcpyHostToDevice));
   PP_CUDA(cudaMemcpy(n.d_scale.p, n.scale.data(), NG * sizeof(double), cudaMemcpyHostToDevice));
   return 0;
@@ -726,6 +733,7 @@ extern "C" int pp_add_structures(pp_context* c, int n_struct, const int* natoms,
   c->n_atoms = na;
   c->tiles_dirty = true;
   c->g32_dirty = true;
+  c->gn_dirty = true;
   // per-element row lists (structure-major)
   for (int e = 0; e < S.n_elem; e++) {
     size_t before = c->h_rows[e].size();
@@ -757,6 +765,7 @@ extern "C" int pp_recompute_descriptors(pp_context* c)
   a.n_atoms = c->n_atoms;
   a.atom_begin = 0;
   c->g32_dirty = true;
+  c->gn_dirty = true;
   if (tick(c, 0)) return 1;
   if (ppk_desc_periodic(c->spec, a, &c->desc_cap, c->stream, &c->launches)) return 1;
   if (tick(c, 1)) return 1;
@@ -905,7 +914,9 @@ static MlpArgs mlp_args_train(pp_context* c, int e)
   MlpArgs a;
   memset(&a, 0, sizeof(a));
   a.net = c->nets[e].dev;
-  a.G = c->d_G.p;
+  const bool gn = c->gn_ready && !c->gn_dirty;      // never a copy that descriptors or scalings have moved away from
+  a.G = gn ? c->d_Gn.p : c->d_G.p;
+  a.prenorm = gn ? 1 : 0;
   a.rows = c->spec.n_elem == 1 ? nullptr : c->d_rows[e].p;
   a.M = (int)c->h_rows[e].size();
   a.atom_struct = c->d_atom_struct.p;
@@ -1017,6 +1028,38 @@ static int struct_errors_all(pp_context* c)
 
 // forward pass of every element + per-structure energies and errors.  stored: the kernels of pp_mlpw.cu, which also
 // keep H_l / T'_l for the backward pass when with_store is set.
+// Bring the normalised copy of the descriptors up to date (or switch it off: PP_MLP_NO_PRENORM=1, or no memory for it).
+static int ensure_normalised(pp_context* c)
+{
+  c->gn_ready = false;
+  if (getenv("PP_MLP_NO_PRENORM") != nullptr || c->n_atoms == 0) return 0;
+  const int NG = c->spec.NG, ne = c->spec.n_elem;
+  if (c->gn_dirty) {
+    double* p = nullptr;
+    const size_t need = (size_t)c->n_atoms * NG;
+    if (c->d_Gn.cap < need) {               // a failed allocation only costs the optimisation
+      c->d_Gn.release();
+      if (cudaMalloc((void**)&p, need * sizeof(double)) != cudaSuccess) { cudaGetLastError(); return 0; }
+      c->d_Gn.p = p; c->d_Gn.cap = need;
+    }
+    std::vector<double> ms(2 * (size_t)ne * NG);
+    for (int e = 0; e < ne; e++)
+      for (int k = 0; k < NG; k++) {
+        ms[(size_t)e * NG + k] = c->nets[e].mean[k];
+        ms[(size_t)(ne + e) * NG + k] = 1.0 / c->nets[e].scale[k];
+      }
+    if (c->d_msn.ensure(ms.size(), 0, c->stream)) return 1;
+    PP_CUDA(cudaMemcpyAsync(c->d_msn.p, ms.data(), ms.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    PP_CUDA(cudaStreamSynchronize(c->stream));      // `ms` is a local
+    if (ppk_g_normalise(c->d_G.p, NG, c->n_atoms, ne == 1 ? nullptr : c->d_elem.p, c->d_msn.p, c->d_msn.p + (size_t)ne * NG, c->d_Gn.p, c->stream,
+                        &c->launches))
+      return 1;
+    c->gn_dirty = false;
+  }
+  c->gn_ready = true;
+  return 0;
+}
+
 // the two-CTA kernels' own stored form (epoch form 5): FORWARD writes, TRAIN reads the element's activation store
 static void with_store2(pp_context* c, int e, MlpArgs& a)
 {
@@ -1089,6 +1132,7 @@ extern "C" int pp_epoch_device(pp_context* c)
   PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
   if (prepare_fused_tiles(c)) return 1;
+  if (ensure_normalised(c)) return 1;
   if (tick(c, 0)) return 1;
   const int stride = c->P_total + 3;
   // what the reduction at the end sums: the partial rows' columns [0, red_cols), then d_result's own [red_cols, stride)
@@ -1244,6 +1288,7 @@ extern "C" int pp_evaluate(pp_context* c, double* E_out)
   PP_REQUIRE(c->n_struct > 0, "pp_evaluate: no structures");
   PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
+  if (ensure_normalised(c)) return 1;
   if (forward_all(c, all_stored(c) && !all_two_cta(c), false)) return 1;
   PP_CUDA(cudaMemcpyAsync(E_out, c->d_E_struct.p, c->n_struct * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   PP_CUDA(cudaStreamSynchronize(c->stream));

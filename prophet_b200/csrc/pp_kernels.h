@@ -75,6 +75,7 @@ struct MlpArgs {
   NetDev net;
   const double* G;                    // [atoms][NG]
   const int* rows;                    // [M] atom indices of this element (nullptr = identity)
+  int prenorm;                        // 1: G holds (x - mean) / scale already (pp_api.cu: normalised copy), the kernels skip NN.cpp:647-651
   int M;
   const int* atom_struct;             // [atoms]                    (train)
   const double* cstruct;              // [n_struct] 2*Err*out_scale (train)
@@ -144,6 +145,9 @@ bool ppk_mlp32_ok(const NetDev& net);
 int ppk_mlp32_pitch(const NetDev& net);                 // row pitch (floats) of the FP32 descriptor array
 int ppk_mlp32_tile_atoms(void);
 int ppk_mlp32_table(const NetDev& net, void* host_out, int* n_entries);      // returns the entry size in bytes (0: not eligible)
+// FP64 descriptors -> their normalised FP64 copy (x - mean[e]) * inv_scale[e], the arithmetic the kernels apply per tile
+int ppk_g_normalise(const double* G, int NG, long long n_atoms, const int* elem, const double* mean, const double* inv_scale, double* out,
+                     cudaStream_t st, long long* launches);
 int ppk_g_to_f32(const double* G, int NG, int NGp, long long n_atoms, const int* elem, const double* mean, const double* scale, float* out,
                  cudaStream_t st, long long* launches);
 int ppk_mlp32_launch_fused(const MlpArgs& a, const float* G32, long long n_atoms, cudaStream_t st, long long* launches, int* n_cta);

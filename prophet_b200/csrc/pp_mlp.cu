@@ -375,8 +375,10 @@ mlp_kernel(MlpArgs a, MlpPlan p, const __grid_constant__ CUtensorMap tmap)
     // rewrites them, so the layer-0 product and the layer-0 weight gradients read plain operands
     if (mt < TM / 8) {
       double* xr = sm + p.x_off[buf] + (size_t)(8 * mt + g) * kp0;
+      if (!a.prenorm) {
 #pragma unroll 4
-      for (int c = 4 * half + q; c < NG; c += 8) xr[c] = (xr[c] - mu[c]) * is[c];
+        for (int c = 4 * half + q; c < NG; c += 8) xr[c] = (xr[c] - mu[c]) * is[c];
+      }
       if (bulk && half == 0 && q == 0) xr[NG] = 1.0;      // the tensor copy zero-fills the padding; column NG is the bias input
       pair_barrier(mt);
     }
@@ -1029,6 +1031,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   // Two-phase epoch with STORED activations (several elements): FORWARD also writes H_l and T'_l to HBM, row-major
   // [M][store_w]; TRAIN copies the H_l tiles back (cp.async, each thread the entries it owns in the forward pass) and takes
   // T' from the store where it forms the deltas, so that the forward products and the transfer functions run once.
+  const bool prenorm_ = FUSED && a.prenorm != 0;
   const bool stored = !FUSED && a.hstore != nullptr;
   const int SW = a.store_w;
   const bool store_vec = (SW & 1) == 0;      // 16-byte accesses need even offsets; every layer width is checked below
@@ -1148,8 +1151,13 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     // ---- normalise this warp's 8 rows in place (NN.cpp:647-651); column NG is the bias input ---------------------
     {
       double* xr = X + (size_t)(rb + g) * kp0;
+      // (a normalised copy of the descriptors, when the caller keeps one, saves this pass.  The flag is read once at the top
+      // of the single-pass instantiation and at this point in the others: each placement is the one ptxas does not answer
+      // with spills -- 112 bytes per tile and 4 % of the epoch in the single-pass kernel otherwise)
+      if (FUSED ? !prenorm_ : !a.prenorm) {
 #pragma unroll 4
-      for (int c = q; c < NG; c += 4) xr[c] = (xr[c] - mu[c]) * is[c];
+        for (int c = q; c < NG; c += 4) xr[c] = (xr[c] - mu[c]) * is[c];
+      }
       if (q == 0) xr[NG] = 1.0;
       __syncwarp();
     }

@@ -403,6 +403,30 @@ g_to_f32_kernel(const double* __restrict__ G, int NG, int NGp, long long n_atoms
   out[i] = (k < NG) ? (float)((G[atom * NG + k] - mean[(size_t)e * NG + k]) * (1.0 / scale[(size_t)e * NG + k])) : 0.0f;
 }
 
+// FP64 -> normalised FP64: exactly the per-tile arithmetic of the training kernels, (x - mean) * (1 / scale), done once
+__global__ void __launch_bounds__(256)
+g_normalise_kernel(const double* __restrict__ G, int NG, long long n_atoms, const int* __restrict__ elem, const double* __restrict__ mean,
+                   const double* __restrict__ inv_scale, double* __restrict__ out)
+{
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_atoms * NG) return;
+  const long long atom = i / NG;
+  const int k = (int)(i - atom * NG);
+  const int e = elem ? elem[atom] : 0;
+  out[i] = (G[i] - mean[(size_t)e * NG + k]) * inv_scale[(size_t)e * NG + k];
+}
+
+int ppk_g_normalise(const double* G, int NG, long long n_atoms, const int* elem, const double* mean, const double* inv_scale, double* out,
+                    cudaStream_t st, long long* launches)
+{
+  if (n_atoms == 0) return 0;
+  const long long n = n_atoms * NG;
+  g_normalise_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(G, NG, n_atoms, elem, mean, inv_scale, out);
+  (*launches)++;
+  PP_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // mean / scale: [n_elem][NG] on the device
 int ppk_g_to_f32(const double* G, int NG, int NGp, long long n_atoms, const int* elem, const double* mean, const double* scale, float* out,
                  cudaStream_t st, long long* launches)

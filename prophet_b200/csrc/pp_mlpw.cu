@@ -309,6 +309,7 @@ mlpw_forward_kernel(MlpArgs a, MlpwPlan p, MlpwStore st, const __grid_constant__
     // ---- normalise the rows in place (NN.cpp:647-651); column NG is the bias input ---------------------------------
     for (int r = j; r < TMG; r += NTW) {
       double* xr = X + (size_t)r * kp0;
+      if (!a.prenorm)
       for (int c = 2 * lane; c < NG; c += 64) {             // NG is even, rows and tables are 16-byte aligned
         const double2 x = *reinterpret_cast<const double2*>(xr + c);
         const double2 m = *reinterpret_cast<const double2*>(mu + c);
@@ -528,6 +529,7 @@ mlpw_backward_kernel(MlpArgs a, MlpwPlan p, MlpwStore st, const __grid_constant_
   };
   auto normalise_x = [&](unsigned ph) {     // NN.cpp:647-651 on this tile's rows, in place
     mbar_wait(mbar, ph);
+    if (a.prenorm) return;                  // the descriptors come normalised (pp_api.cu keeps such a copy)
     for (int r = warp; r < TM; r += MLPW_WARPS) {
       double* xr = X + (size_t)r * kp0;
       for (int c = 2 * lane; c < NG; c += 64) {

@@ -125,3 +125,42 @@ def test_tanh_spline_networks_and_an_absent_element():
         _check(r, _oracle_epoch(ctx, cfg, natoms, elem, targets, tags, nets, scal, transfer="tanh_spline"))
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("name", ["si_train", "tio2_train", "abo4_train"])
+def test_normalised_descriptor_copy_changes_nothing(name):
+    """The library keeps a normalised FP64 copy of the descriptors, (x - mean) * (1 / scale) -- the arithmetic the training
+    kernels otherwise apply to every tile (NN.cpp:647-651) -- and refreshes it when descriptors or scalings change.
+    PP_MLP_NO_PRENORM=1 switches it off: gradients, SSE and energies must be bit-identical either way, also after the
+    input scaling was changed between two epochs."""
+    c = TrainCase(name)
+    ctx = capi.Context(0)
+    try:
+        ctx.set_descriptors(len(c.elements), c.G1, c.G2, c.G3, c.G4, c.rcut)
+        params = c.params_at(0)
+        for e, z in enumerate(c.elements):
+            ctx.set_network(e, c.sizes, params[e], c.mean(z), c.scale(z), node_transfer=c.node_transfer(z))
+        ctx.set_output_scaling(c.out_mean, c.out_scale)
+        ctx.add_structures(c.natoms, np.stack(c.cells), np.concatenate(c.frac), c.elem_flat(), c.targets, c.tags)
+        x = c.d["x_before.0"]
+
+        def both():
+            r = ctx.epoch(x)
+            E = ctx.evaluate()
+            os.environ["PP_MLP_NO_PRENORM"] = "1"
+            try:
+                r0 = ctx.epoch(x)
+                E0 = ctx.evaluate()
+            finally:
+                os.environ.pop("PP_MLP_NO_PRENORM", None)
+            assert np.array_equal(r["gradient"], r0["gradient"]) and r["SSE"] == r0["SSE"] and np.array_equal(E, E0)
+            return r
+
+        r = both()
+        assert rel_err(r["gradient"], c.d["gradient.0"]) < TOL
+        for e, z in enumerate(c.elements):      # a new scaling must reach the copy
+            ctx.set_input_scaling(e, c.mean(z) + 0.01, c.scale(z) * 1.1)
+        r2 = both()
+        assert not np.array_equal(r2["gradient"], r["gradient"])
+    finally:
+        ctx.close()
