@@ -309,12 +309,13 @@ mlpw_forward_kernel(MlpArgs a, MlpwPlan p, MlpwStore st, const __grid_constant__
     // ---- normalise the rows in place (NN.cpp:647-651); column NG is the bias input ---------------------------------
     for (int r = j; r < TMG; r += NTW) {
       double* xr = X + (size_t)r * kp0;
-      if (!a.prenorm)
-      for (int c = 2 * lane; c < NG; c += 64) {             // NG is even, rows and tables are 16-byte aligned
-        const double2 x = *reinterpret_cast<const double2*>(xr + c);
-        const double2 m = *reinterpret_cast<const double2*>(mu + c);
-        const double2 v = *reinterpret_cast<const double2*>(is + c);
-        *reinterpret_cast<double2*>(xr + c) = make_double2((x.x - m.x) * v.x, (x.y - m.y) * v.y);
+      if (!a.prenorm) {                                       // (skipped when the descriptors come normalised, pp_api.cu)
+        for (int c = 2 * lane; c < NG; c += 64) {             // NG is even, rows and tables are 16-byte aligned
+          const double2 x = *reinterpret_cast<const double2*>(xr + c);
+          const double2 m = *reinterpret_cast<const double2*>(mu + c);
+          const double2 v = *reinterpret_cast<const double2*>(is + c);
+          *reinterpret_cast<double2*>(xr + c) = make_double2((x.x - m.x) * v.x, (x.y - m.y) * v.y);
+        }
       }
       if (lane == 0) xr[NG] = 1.0;
     }
