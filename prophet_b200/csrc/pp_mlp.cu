@@ -1074,6 +1074,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   // One tensor copy per tile when the rows are consecutive atoms; gathered rows (an element of a multi-element system)
   // come as one bulk copy per row, issued by the warp that owns the row (lanes 0..7), all counted on the same mbarrier.
   const bool gather = !FUSED && (a.rows != nullptr);      // fused tiles are whole structures of consecutive atoms
+  int pf_row = -1;                            // gathered rows: atom index of this lane's row of the NEXT tile
   auto issue_load = [&](const Geom& gm) {
     if (!gather) {
       if (tid == 0) {
@@ -1088,7 +1089,8 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       fence_proxy_async();              // this lane's row was rewritten in place through the generic proxy
       const int r = 8 * warp + lane;
       double* dst = X + (size_t)r * kp0;
-      if (r < gm.nvalid) bulk_copy_g2s(dst, a.G + (size_t)a.rows[gm.row0 + r] * NG, (unsigned)NG * 8u, mbar);
+      // the row's atom index was fetched a tile ago (pf_row): the copy does not wait on a dependent global load
+      if (r < gm.nvalid) bulk_copy_g2s(dst, a.G + (size_t)(pf_row >= 0 ? pf_row : a.rows[gm.row0 + r]) * NG, (unsigned)NG * 8u, mbar);
       else for (int c = 0; c < NG; c++) dst[c] = 0.0;
     }
   };
@@ -1108,6 +1110,12 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     const int row0 = g_cur.row0, nvalid = g_cur.nvalid;
     const int s_first = g_cur.s0, s_last = g_cur.s1;
     const Geom g_nn = tile_geom(tile + 2 * gridDim.x);
+    if constexpr (MODE == PP_MLP_FORWARD) {       // (in the TRAIN launch one more live value costs 200 bytes of spills per tile)
+      if (gather && lane < 8) {
+        const int r = 8 * warp + lane;
+        pf_row = (r < g_nxt.nvalid) ? a.rows[g_nxt.row0 + r] : -1;
+      }
+    }
     if (FUSED) {
       // structure table of this tile (read after barrier A); then the next tile's entries start their flight
       if (tid <= s_last - s_first) {
