@@ -54,7 +54,8 @@ struct NetDev {
   const double* scale;                // device [NG]
 };
 
-enum { PP_MLP_FORWARD = 0, PP_MLP_TRAIN = 1, PP_MLP_INPUT_GRAD = 2, PP_MLP_FUSED = 3 };
+enum { PP_MLP_FORWARD = 0, PP_MLP_TRAIN = 1, PP_MLP_INPUT_GRAD = 2, PP_MLP_FUSED = 3,
+       PP_MLP_TRAIN_STORED = 4 };      // template mode of mlp_fused2_kernel only: TRAIN reading the activation store
 
 // fused MD step (md_fused_kernel): the per-element networks of the atom-centred pass
 struct MdNets {

@@ -976,6 +976,10 @@ __global__ void __launch_bounds__(MLP2_THREADS, 2)
 mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tmap)
 {
   constexpr bool FUSED = (MODE == PP_MLP_FUSED);
+  // PP_MLP_TRAIN_STORED: the TRAIN launch of the stored form as an instantiation of its own -- the forward products and
+  // transfer functions are not compiled in, which frees the registers the early loads of T' and of the row indices need
+  constexpr bool TRAIN_ = (MODE == PP_MLP_TRAIN || MODE == PP_MLP_TRAIN_STORED);
+  constexpr bool ST_ = (MODE == PP_MLP_TRAIN_STORED);
   constexpr bool GRADW = (MODE != PP_MLP_FORWARD);
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sm = reinterpret_cast<double*>(smem_raw);
@@ -1032,7 +1036,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   // [M][store_w]; TRAIN copies the H_l tiles back (cp.async, each thread the entries it owns in the forward pass) and takes
   // T' from the store where it forms the deltas, so that the forward products and the transfer functions run once.
   const bool prenorm_ = FUSED && a.prenorm != 0;
-  const bool stored = !FUSED && a.hstore != nullptr;
+  const bool stored = ST_ || (MODE == PP_MLP_FORWARD && a.hstore != nullptr);      // compile-time in the gradient launches
   const int SW = a.store_w;
   const bool store_vec = (SW & 1) == 0;      // 16-byte accesses need even offsets; every layer width is checked below
   double dW[NLW][6][2];                       // per hidden-layer matrix: slot 0 = tiles 0..3, slot 1 = tiles 4..5
@@ -1100,7 +1104,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
   Geom g_cur = tile_geom(blockIdx.x), g_nxt = tile_geom(blockIdx.x + gridDim.x);
   if ((int)blockIdx.x < n_tiles) {
     issue_load(g_cur);
-    if constexpr (MODE == PP_MLP_TRAIN) { if (stored) mlp2_issue_hidden<NTW>(a, p, sm, g_cur.row0, g_cur.nvalid, warp, g, q, SW, store_vec); }
+    if constexpr (TRAIN_) { if (stored) mlp2_issue_hidden<NTW>(a, p, sm, g_cur.row0, g_cur.nvalid, warp, g, q, SW, store_vec); }
   }
   st_fetch(g_cur);
 
@@ -1110,7 +1114,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     const int row0 = g_cur.row0, nvalid = g_cur.nvalid;
     const int s_first = g_cur.s0, s_last = g_cur.s1;
     const Geom g_nn = tile_geom(tile + 2 * gridDim.x);
-    if constexpr (MODE == PP_MLP_FORWARD) {       // (in the TRAIN launch one more live value costs 200 bytes of spills per tile)
+    if constexpr (MODE == PP_MLP_FORWARD || ST_) {      // (in the recomputing TRAIN launch one more live value costs 200 bytes of spills per tile)
       if (gather && lane < 8) {
         const int r = 8 * warp + lane;
         pf_row = (r < g_nxt.nvalid) ? a.rows[g_nxt.row0 + r] : -1;
@@ -1123,7 +1127,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         if (tid < s_last - s_first) { st_tgt[tid] = pf_tgt; st_tag[tid] = pf_tag; }
       }
       st_fetch(g_nxt);
-    } else if (MODE == PP_MLP_TRAIN) {
+    } else if (TRAIN_) {
       // error factor of each row's structure (struct_errors_kernel); read after barrier A
       if (tid < TM) {
         double c = 0.0;
@@ -1135,8 +1139,8 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       }
     }
     // stored TRAIN: T' of the last hidden layer is needed right after barrier A; its loads fly while the tile's copies land
-    double tpl[(MODE == PP_MLP_TRAIN) ? NTW : 1][2];
-    if constexpr (MODE == PP_MLP_TRAIN) {
+    double tpl[(TRAIN_) ? NTW : 1][2];
+    if constexpr (TRAIN_) {
       if (stored) {
         int off_last0 = 0;
         for (int l = 1; l < L - 1; l++) off_last0 += p.n[l];
@@ -1182,7 +1186,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     };
     // T' of this thread's activations (nt, h = 0 / 1) of hidden layer lh (0-based): from the store, else from the scratch
     auto tprime = [&](int lh, int off, int n_l, int nt, double& t0, double& t1) {
-      if (MODE == PP_MLP_TRAIN && stored) {
+      if (TRAIN_ && stored) {
         const int n = 8 * nt + 2 * q;
         t0 = t1 = 0.0;
         if (srow_ok && n < n_l) {
@@ -1196,9 +1200,9 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       }
     };
     int off_last = 0;                            // column offset of the last hidden layer in the store
-    if (MODE == PP_MLP_TRAIN)
+    if (TRAIN_)
       for (int l = 1; l < L - 1; l++) off_last += p.n[l];
-    if (MODE == PP_MLP_TRAIN && stored) {
+    if (TRAIN_ && stored) {
       cp_async_wait_all();                      // this thread's entries of the H_l tiles have landed
       __syncwarp();
     } else {
@@ -1327,7 +1331,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       const double c = cvec[rb + g];
 #pragma unroll
       for (int nt = 0; nt < NTW; nt++) {
-        if (MODE == PP_MLP_TRAIN) {
+        if (TRAIN_) {
           double tp[2];
           if (stored) { tp[0] = tpl[nt][0]; tp[1] = tpl[nt][1]; }
           else tprime(L - 2, off_last, n_h, nt, tp[0], tp[1]);
@@ -1354,9 +1358,27 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
       const int l = NLW - 1 - li;
       __syncthreads();                                                                 // delta_{l+1} complete in all rows
       double accb[NTW][2];
+      // stored TRAIN: T' of layer l is fetched from the store while the product below runs and multiplied in right after it:
+      // its latency hides behind the product and only the deltas stay live across the weight-gradient blocks
+      double tpm[ST_ ? NTW : 1][2];
+      if constexpr (ST_) {
+        if (l >= 1) {
+          int off_l0 = 0;
+          for (int l2 = 1; l2 < l; l2++) off_l0 += p.n[l2];
+          const int n_l = p.n[l];
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) tprime(l - 1, off_l0, n_l, nt, tpm[nt][0], tpm[nt][1]);
+        }
+      }
       if (l >= 1)      // (delta_{l+1} W_l) for this warp's rows, kept in registers until the barrier below
         tile_gemm<true, false, NTW>(accb, sm + p.h_off[l + 1], p.kp[l + 1], sm + p.w_off[l], p.kp[l], warp, round_up(p.n[l + 1], 4), 0,
                                     NTW, lane);
+      if constexpr (ST_) {
+        if (l >= 1) {
+#pragma unroll
+          for (int nt = 0; nt < NTW; nt++) { accb[nt][0] *= tpm[nt][0]; accb[nt][1] *= tpm[nt][1]; }
+        }
+      }
       {
         const DwTile d = tab[(l * MLP2_WARPS + warp) * 2];
         if (d.nm) {
@@ -1385,13 +1407,13 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
         const int n_l = p.n[l];
         double* Hr = sm + p.h_off[l] + (size_t)(rb + g) * p.kp[l];
         int off_l = 0;
-        if (MODE == PP_MLP_TRAIN)
+        if (TRAIN_)
           for (int l2 = 1; l2 < l; l2++) off_l += p.n[l2];
 #pragma unroll
         for (int nt = 0; nt < NTW; nt++) {
-          if (MODE == PP_MLP_TRAIN) {
-            double tp[2];
-            tprime(l - 1, off_l, n_l, nt, tp[0], tp[1]);      // (loading these before the products above was tried: 528 bytes of spills)
+          if (TRAIN_) {
+            double tp[2] = {1.0, 1.0};                     // stored form: T' is in the deltas already (multiplied in above)
+            if (!ST_) tprime(l - 1, off_l, n_l, nt, tp[0], tp[1]);
 #pragma unroll
             for (int h = 0; h < 2; h++) {
               const int n = 8 * nt + 2 * q + h;
@@ -1412,7 +1434,7 @@ mlp_fused2_kernel(MlpArgs a, Mlp2Plan p, const __grid_constant__ CUtensorMap tma
     __syncthreads();                                                                   // X is free: next tile's copy
     if (tile + (int)gridDim.x < n_tiles) {
       issue_load(g_nxt);
-      if constexpr (MODE == PP_MLP_TRAIN) { if (stored) mlp2_issue_hidden<NTW>(a, p, sm, g_nxt.row0, g_nxt.nvalid, warp, g, q, SW, store_vec); }
+      if constexpr (TRAIN_) { if (stored) mlp2_issue_hidden<NTW>(a, p, sm, g_nxt.row0, g_nxt.nvalid, warp, g, q, SW, store_vec); }
     }
     g_cur = g_nxt;
     g_nxt = g_nn;
@@ -1569,7 +1591,7 @@ int ppk_mlp_launch2(int mode, bool allow_two_cta, const MlpArgs& a, cudaStream_t
     else PP_LAUNCH2(MODE_, 8, 2)                                 \
   }
   if (mode == PP_MLP_FUSED) PP_LAUNCH2_SHAPE(PP_MLP_FUSED)
-  else if (mode == PP_MLP_TRAIN) PP_LAUNCH2_SHAPE(PP_MLP_TRAIN)
+  else if (mode == PP_MLP_TRAIN) { if (a.hstore != nullptr) PP_LAUNCH2_SHAPE(PP_MLP_TRAIN_STORED) else PP_LAUNCH2_SHAPE(PP_MLP_TRAIN) }
   else PP_LAUNCH2_SHAPE(PP_MLP_FORWARD)
 #undef PP_LAUNCH2_SHAPE
 #undef PP_LAUNCH2
