@@ -1132,7 +1132,7 @@ extern "C" int pp_epoch_device(pp_context* c)
   PP_CUDA(cudaSetDevice(c->device));
   if (epoch_buffers(c)) return 1;
   if (prepare_fused_tiles(c)) return 1;
-  if (ensure_normalised(c)) return 1;
+  if (!(fp32_epoch(c) && c->fused_ok) && ensure_normalised(c)) return 1;      // (the FP32 epoch reads its own FP32 copy)
   if (tick(c, 0)) return 1;
   const int stride = c->P_total + 3;
   // what the reduction at the end sums: the partial rows' columns [0, red_cols), then d_result's own [red_cols, stride)
