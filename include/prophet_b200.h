@@ -127,7 +127,10 @@ int pp_epoch_result_dev(pp_context* ctx, double** result_dev, int* n);
  * 5 = form 0 through the two-CTA kernels with the activations kept in HBM between the two launches instead of the
  * forward pass being run again (several elements, networks of one or two hidden layers up to 64 wide).
  * Same arithmetic in forms 0 - 3 and 5, different summation order.
- * -1 before the first epoch.  Environment: PP_MLP_ONE_CTA=1 keeps form 2 from being chosen, PP_MLP_NO_STORE=1 forms 3 and 5.
+ * -1 before the first epoch.  Environment: PP_MLP_ONE_CTA=1 keeps form 2 from being chosen, PP_MLP_NO_STORE=1 forms 3 and 5;
+ * PP_MLP_NO_PRENORM=1 makes the kernels normalise the descriptors per tile instead of reading the library's normalised
+ * copy (same results bit for bit; the copy costs NG doubles per atom of device memory and is dropped by itself when that
+ * allocation fails).
  * No reference counterpart. */
 int pp_epoch_form(pp_context* ctx);
 /* Potential::evaluate (Potential.cpp:515-551): E_out[n_struct] = sum_atoms E_i + out_mean (every tag) */
